@@ -1,0 +1,100 @@
+/*
+ * llmfp8_b200.h — C ABI of libllmfp8_b200.so: the B200 (sm_100a) FP8 / MXFP8 linear-layer hot path.
+ *
+ * This is the boundary a Transformer-Engine-style framework binds: the reference (xuanvinh1997/llm-fp8) reaches
+ * these operations through `transformer_engine.pytorch` modules constructed at te_llama.py:45-63 and executed under
+ * `te.pytorch.fp8_autocast` at te_llama.py:76-80 (hybrid: te_llama_hybrid.py:75-79, MXFP8: te_llama_mxfp8.py:86-94).
+ * TE's own binding layer for them is its `transformer_engine_torch` (tex) extension; each entry point below names
+ * the tex operation it stands in for.  INTEGRATION.md shows the ctypes stubs.
+ *
+ * Conventions
+ *   - plain pointers and sizes only; every pointer is a CUDA device pointer owned by the caller unless noted;
+ *   - `stream` is a cudaStream_t passed as void*; every call is asynchronous on it, nothing synchronises;
+ *   - return 0 = ok, <0 = contract violation (alignment, shape, format), >0 = cudaError_t;
+ *     llmfp8_last_error() returns a thread-local description of the last failure;
+ *   - no CPU fallback and no library (cuBLASLt) fallback: an unsupported call is an error;
+ *   - re-entrant: no mutable global state besides immutable per-process caches, safe from the autograd thread;
+ *   - fp8 format enum: 0 = E4M3 (e4m3fn, max 448), 1 = E5M2 (max 57344);
+ *   - bf16 tensors are row-major, 16 B aligned, inner dimension a multiple of 8 (16 for the flat cast).
+ */
+#ifndef LLMFP8_B200_H
+#define LLMFP8_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LLMFP8_E4M3 0
+#define LLMFP8_E5M2 1
+#define LLMFP8_ABI_VERSION 1
+
+int llmfp8_abi_version(void);
+const char* llmfp8_last_error(void);
+/* number of SMs of the current device (cached) */
+int llmfp8_sm_count(void);
+
+/* ---- per-tensor (DelayedScaling) quantise kernels ------------------------------------------------------------ */
+
+/* K2: q = sat_rne_fp8(x * *scale), *amax = max(*amax, max|x|).   [tex.cast_to_fp8 / quantize]
+ * x bf16 [n] (n % 16 == 0), q u8 [n]; scale, amax fp32 device scalars (amax may be NULL). */
+int llmfp8_quant_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* scale, float* amax, void* stream);
+
+/* K2b: as K2 on a [rows, cols] matrix, plus bgrad[c] = sum_r x[r, c] (bf16 out).   [tex.fp8_cast_transpose_bgrad_fused]
+ * colsum_ws: fp32 [cols] scratch. */
+int llmfp8_quant_cast_amax_bgrad(const void* x, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax,
+                                 float* colsum_ws, void* bgrad, void* stream);
+
+/* K1: y = (x * rsigma) * gamma with rsigma = 1/sqrt(mean(x^2) + eps); q = sat_rne_fp8(y * *scale); amax over |y|.
+ * [tex.rmsnorm_fwd with fp8 output, inside LayerNormLinear / LayerNormMLP]   x bf16 [M, H], gamma bf16 [H], H % 8 == 0, H <= 8192. */
+int llmfp8_rmsnorm_quant_fwd(const void* x, const void* gamma, void* q, float* rsigma, int64_t M, int64_t H, float eps, int fmt,
+                             const float* scale, float* amax, void* stream);
+
+/* K5: RMSNorm backward.   [tex.rmsnorm_bwd]   dx bf16 [M, H], dgamma bf16 [H]; ws fp32 [llmfp8_rmsnorm_bwd_ws_rows(M) * H]. */
+int llmfp8_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma, float* ws, int64_t M,
+                       int64_t H, void* stream);
+int llmfp8_rmsnorm_bwd_ws_rows(int64_t M);
+
+/* K3: a = silu(gate) * up over fc1_out bf16 [M, 2I] (gate = [:, :I], up = [:, I:]); q u8 [M, I].   [tex.swiglu + cast] */
+int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream);
+
+/* K3 bwd: d_fc1 = dswiglu(da, fc1_out) quantised to q u8 [M, 2I]; dbias bf16 [2I] = column sums (dbias_ws fp32 [2I]; both NULL = skip).
+ * [tex.dswiglu + fp8_cast_transpose_bgrad_dgelu-style fusion] */
+int llmfp8_dswiglu_quant_bwd(const void* da, const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax,
+                             float* dbias_ws, void* dbias, void* stream);
+
+/* K4: for every fp8 tensor slot t: amax = max_l hist[l, t]; scale = fmax[t] / amax / 2^margin (unchanged when amax is 0 or
+ * non-finite); scale_inv = 1 / scale; roll the history by one and zero row 0.   [tex.fused_amax_and_scale_update_after_reduction] */
+int llmfp8_amax_scale_update(float* amax_history, float* scale, float* scale_inv, const float* fmax, int history_len, int num_tensors,
+                             int margin, void* stream);
+
+/* ---- MXFP8 (MXFP8BlockScaling) quantiser ---------------------------------------------------------------------- */
+
+/* K2m / K1m: x bf16 [rows, cols] -> rowwise copy (1x32 blocks along cols) and/or colwise copy (32x1 blocks along rows), e4m3 data in
+ * the layout of x, E8M0 scales in the 128x4-tile swizzled layout (llmfp8_mx_scale_bytes).  A NULL q pointer skips that copy.
+ * rsigma/gamma non-NULL: quantise y = (x * rsigma[r]) * gamma[c] instead (RMSNorm fused; rsigma from llmfp8_rmsnorm_rsigma).
+ * [tex.quantize with an MXFP8 quantizer; rmsnorm_fwd with MXFP8 output] */
+int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
+                       const void* gamma, void* stream);
+int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream);
+/* bytes of the swizzled scale tensor of a matrix with `rows` rows and `k` elements along the blocked dimension */
+int64_t llmfp8_mx_scale_bytes(int64_t rows, int64_t k);
+
+/* ---- GEMMs ------------------------------------------------------------------------------------------------------ */
+
+/* D[M, N] = (a_scale_inv * b_scale_inv) * sum_k A[m, k] B[n, k] (+ bias[n]) (+ D if accumulate).   [tex.generic_gemm -> cuBLASLt]
+ *  a_mn = 0: A stored [M, K] (k contiguous, lda >= K bytes);  a_mn = 1: A stored [K, M] (m contiguous, lda >= M).  Likewise b / N.
+ *  out_fp32 = 0: D bf16, 1: D fp32; ldd in elements.  max_ctas <= 0: one CTA per SM. */
+int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd,
+                    int out_fp32, int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, int accumulate,
+                    int max_ctas, void* stream);
+
+/* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */
+int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
+                      int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* LLMFP8_B200_H */

@@ -1,0 +1,150 @@
+// extern "C" surface of libllmfp8_b200.so (declared in include/llmfp8_b200.h) + process-wide plumbing:
+// thread-local error string, SM-count cache, TMA descriptor encoder resolved through the runtime.
+#include <cstdarg>
+#include <cstdio>
+#include <mutex>
+
+#include "../../include/llmfp8_b200.h"
+#include "common.cuh"
+#include "tensormap.cuh"
+
+namespace llmfp8 {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char* fmt, ...) {
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int sm_count() {
+    static int cached[64] = {0};
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) return kNumSMsDefault;
+    if (cached[dev] == 0) {
+        int n = 0;
+        if (cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || n <= 0) n = kNumSMsDefault;
+        cached[dev] = n;
+    }
+    return cached[dev];
+}
+
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                  CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn encode_fn() {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    return fn;
+}
+
+int make_tensor_map_2d(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int elem_bytes, int64_t dim0, int64_t dim1,
+                       int64_t pitch_bytes, int box0, int box1, CUtensorMapSwizzle swizzle) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+        return -2;
+    }
+    cuuint64_t dims[2] = {static_cast<cuuint64_t>(dim0), static_cast<cuuint64_t>(dim1)};
+    cuuint64_t strides[1] = {static_cast<cuuint64_t>(pitch_bytes)};
+    cuuint32_t box[2] = {static_cast<cuuint32_t>(box0), static_cast<cuuint32_t>(box1)};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(map, dtype, 2, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled failed (%d): base=%p dims=(%lld,%lld) pitch=%lld box=(%d,%d) elem=%d", (int)r, base, (long long)dim0,
+                  (long long)dim1, (long long)pitch_bytes, box0, box1, elem_bytes);
+        return -3;
+    }
+    return 0;
+}
+
+// kernels (defined in the other translation units)
+int launch_cast_amax(const void*, void*, int64_t, int, const float*, float*, cudaStream_t);
+int launch_cast_amax_bgrad(const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
+int launch_amax_scale_update(float*, float*, float*, const float*, int, int, int, cudaStream_t);
+int launch_rmsnorm_quant_fwd(const void*, const void*, void*, float*, int64_t, int64_t, float, int, const float*, float*, cudaStream_t);
+int launch_rmsnorm_rsigma(const void*, float*, int64_t, int64_t, float, cudaStream_t);
+int launch_rmsnorm_bwd(const void*, const void*, const void*, const float*, void*, void*, float*, int64_t, int64_t, cudaStream_t);
+int rmsnorm_bwd_grid(int64_t);
+int launch_swiglu_quant_fwd(const void*, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
+int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
+int launch_mx_quantize(const void*, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
+int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
+                    const void*, const void*, const void*, int, int, cudaStream_t);
+
+}  // namespace llmfp8
+
+using namespace llmfp8;
+#define S(stream) static_cast<cudaStream_t>(stream)
+
+extern "C" {
+
+int llmfp8_abi_version(void) { return LLMFP8_ABI_VERSION; }
+const char* llmfp8_last_error(void) { return g_err; }
+int llmfp8_sm_count(void) { return sm_count(); }
+
+int llmfp8_quant_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* scale, float* amax, void* stream) {
+    return launch_cast_amax(x, q, n, fmt, scale, amax, S(stream));
+}
+int llmfp8_quant_cast_amax_bgrad(const void* x, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax, float* colsum_ws,
+                                 void* bgrad, void* stream) {
+    return launch_cast_amax_bgrad(x, q, rows, cols, fmt, scale, amax, colsum_ws, bgrad, S(stream));
+}
+int llmfp8_rmsnorm_quant_fwd(const void* x, const void* gamma, void* q, float* rsigma, int64_t M, int64_t H, float eps, int fmt, const float* scale,
+                             float* amax, void* stream) {
+    return launch_rmsnorm_quant_fwd(x, gamma, q, rsigma, M, H, eps, fmt, scale, amax, S(stream));
+}
+int llmfp8_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma, float* ws, int64_t M, int64_t H,
+                       void* stream) {
+    return launch_rmsnorm_bwd(dy, x, gamma, rsigma, dx, dgamma, ws, M, H, S(stream));
+}
+int llmfp8_rmsnorm_bwd_ws_rows(int64_t M) { return rmsnorm_bwd_grid(M); }
+int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream) {
+    return launch_swiglu_quant_fwd(fc1_out, q, M, I, fmt, scale, amax, S(stream));
+}
+int llmfp8_dswiglu_quant_bwd(const void* da, const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax,
+                             float* dbias_ws, void* dbias, void* stream) {
+    return launch_dswiglu_quant_bwd(da, fc1_out, q, M, I, fmt, scale, amax, dbias_ws, dbias, S(stream));
+}
+int llmfp8_amax_scale_update(float* amax_history, float* scale, float* scale_inv, const float* fmax, int history_len, int num_tensors, int margin,
+                             void* stream) {
+    return launch_amax_scale_update(amax_history, scale, scale_inv, fmax, history_len, num_tensors, margin, S(stream));
+}
+int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
+                       const void* gamma, void* stream) {
+    return launch_mx_quantize(x, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+}
+int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream) {
+    return launch_rmsnorm_rsigma(x, rsigma, M, H, eps, S(stream));
+}
+int64_t llmfp8_mx_scale_bytes(int64_t rows, int64_t k) {
+    const int64_t kb = (k + 31) / 32;
+    return ((rows + 127) / 128 * 128) * ((kb + 3) / 4 * 4);
+}
+int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd, int out_fp32,
+                    int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, int accumulate, int max_ctas,
+                    void* stream) {
+    return launch_fp8_gemm(a, lda, a_fmt, a_mn, b, ldb, b_fmt, b_mn, d, ldd, out_fp32, M, N, K, a_scale_inv, b_scale_inv, nullptr, nullptr, bias,
+                           accumulate, max_ctas, S(stream));
+}
+int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
+                      int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream) {
+    if (!sfa || !sfb) {
+        set_error("mxfp8_gemm: scale tensors are required");
+        return -1;
+    }
+    return launch_fp8_gemm(a, lda, LLMFP8_E4M3, a_mn, b, ldb, LLMFP8_E4M3, b_mn, d, ldd, out_fp32, M, N, K, nullptr, nullptr, sfa, sfb, bias,
+                           accumulate, max_ctas, S(stream));
+}
+
+}  // extern "C"

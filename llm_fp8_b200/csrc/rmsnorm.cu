@@ -1,0 +1,233 @@
+// RMSNorm kernels for sm_100a (row per 128-thread CTA, persistent over rows, 16 B loads).
+//   K1   rmsnorm_quant_fwd : x bf16 [M,H], gamma -> fp8 [M,H] (per-tensor scale), rsigma[M], amax   (~3*M*H bytes)
+//   K1r  rmsnorm_rsigma    : x -> rsigma[M] only (first pass of the MXFP8 variant, see mx_quantize.cu)
+//   K5   rmsnorm_bwd       : dy, x, gamma, rsigma -> dx bf16, dgamma bf16 (two-stage column reduction)
+// Replaces TE's rmsnorm_fwd(+fp8 cast)/rmsnorm_bwd reached from LayerNormLinear / LayerNormMLP
+// (te_llama.py:45-63).  The sum-of-squares reduction ORDER is the one oracle_c.c:orc_rms_rsigma fixes:
+// chunk c (8 elements) -> thread c % 128, in-thread fma chain, xor butterfly, ((w0+w1)+w2)+w3.
+#include "common.cuh"
+
+namespace llmfp8 {
+
+constexpr int RMS_T = 128;
+
+template <int NIT>
+__device__ __forceinline__ float rms_row_rsigma(const uint4 (&v)[NIT], int t, int nchunk, int H, float eps, float* red /*[4]*/) {
+    float acc = 0.f;
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
+        if (it * RMS_T + t < nchunk) {
+            float f[8];
+            unpack8(v[it], f);
+#pragma unroll
+            for (int j = 0; j < 8; j++) acc = __fmaf_rn(f[j], f[j], acc);
+        }
+    }
+    acc = warp_sum_pinned(acc);
+    if ((t & 31) == 0) red[t >> 5] = acc;
+    __syncthreads();
+    const float total = __fadd_rn(__fadd_rn(__fadd_rn(red[0], red[1]), red[2]), red[3]);
+    const float mean = __fdiv_rn(total, static_cast<float>(H));
+    return __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+}
+
+// OUT_MODE: 0 = fp8 quantised output (+amax), 1 = rsigma only
+template <int FMT, int NIT, int OUT_MODE>
+__global__ void __launch_bounds__(RMS_T) rmsnorm_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gamma, uint2* __restrict__ q,
+                                                            float* __restrict__ rsigma, int64_t M, int H, float eps,
+                                                            const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    __shared__ float red[2][4];
+    __shared__ float red_amax[4];
+    const int t = threadIdx.x;
+    const int nchunk = H / 8;
+    const float scale = (OUT_MODE == 0 && scale_ptr) ? __ldg(scale_ptr) : 1.0f;
+    uint4 g[NIT];
+    if (OUT_MODE == 0) {
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + t < nchunk) g[it] = __ldg(gamma + it * RMS_T + t);
+    }
+    float m = 0.f;
+    int par = 0;
+    for (int64_t row = blockIdx.x; row < M; row += gridDim.x, par ^= 1) {
+        uint4 v[NIT];
+        const uint4* xr = x + row * nchunk;
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + t < nchunk) v[it] = ldg_stream(xr + it * RMS_T + t);
+        const float rs = rms_row_rsigma<NIT>(v, t, nchunk, H, eps, red[par]);
+        if (t == 0) rsigma[row] = rs;
+        if (OUT_MODE == 0) {
+            uint2* qr = q + row * nchunk;
+#pragma unroll
+            for (int it = 0; it < NIT; it++) {
+                if (it * RMS_T + t < nchunk) {
+                    float f[8], gf[8];
+                    unpack8(v[it], f);
+                    unpack8(g[it], gf);
+#pragma unroll
+                    for (int j = 0; j < 8; j++) f[j] = __fmul_rn(__fmul_rn(f[j], rs), gf[j]);
+                    m = amax8(f, m);
+                    qr[it * RMS_T + t] = quant8<FMT>(f, scale);
+                }
+            }
+        }
+    }
+    if (OUT_MODE == 0 && amax) block_amax_to_global(m, red_amax, amax);
+}
+
+template <int FMT, int OUT_MODE>
+static int dispatch_rms_fwd(int nit, int grid, cudaStream_t s, const uint4* x, const uint4* g, uint2* q, float* rs, int64_t M, int H, float eps,
+                            const float* scale, float* amax) {
+#define RMS_CASE(N)                                                                                              \
+    case N:                                                                                                      \
+        rmsnorm_fwd_kernel<FMT, N, OUT_MODE><<<grid, RMS_T, 0, s>>>(x, g, q, rs, M, H, eps, scale, amax);        \
+        break;
+    switch (nit) {
+        RMS_CASE(1) RMS_CASE(2) RMS_CASE(3) RMS_CASE(4) RMS_CASE(5) RMS_CASE(6) RMS_CASE(7) RMS_CASE(8)
+        default: set_error("rmsnorm: hidden size %d too large (max 8192)", H); return -1;
+    }
+#undef RMS_CASE
+    return 0;
+}
+
+int launch_rmsnorm_quant_fwd(const void* x, const void* gamma, void* q, float* rsigma, int64_t M, int64_t H, float eps, int fmt,
+                             const float* scale, float* amax, cudaStream_t stream) {
+    LLMFP8_REQUIRE(H % 8 == 0 && H > 0 && H <= 8192, "rmsnorm_quant_fwd: hidden size %lld must be a multiple of 8 and <= 8192", (long long)H);
+    LLMFP8_REQUIRE(fmt == FMT_E4M3 || fmt == FMT_E5M2, "rmsnorm_quant_fwd: bad fp8 format %d", fmt);
+    LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma)) % 16 == 0 && reinterpret_cast<uintptr_t>(q) % 8 == 0,
+                   "rmsnorm_quant_fwd: misaligned pointers");
+    if (M == 0) return 0;
+    const int nit = static_cast<int>((H / 8 + RMS_T - 1) / RMS_T);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    const int grid = static_cast<int>(M < cap ? M : cap);
+    int rc = fmt == FMT_E4M3
+                 ? dispatch_rms_fwd<FMT_E4M3, 0>(nit, grid, stream, (const uint4*)x, (const uint4*)gamma, (uint2*)q, rsigma, M, (int)H, eps, scale, amax)
+                 : dispatch_rms_fwd<FMT_E5M2, 0>(nit, grid, stream, (const uint4*)x, (const uint4*)gamma, (uint2*)q, rsigma, M, (int)H, eps, scale, amax);
+    if (rc) return rc;
+    LLMFP8_LAUNCH_CHECK("rmsnorm_quant_fwd");
+    return 0;
+}
+
+int launch_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, cudaStream_t stream) {
+    LLMFP8_REQUIRE(H % 8 == 0 && H > 0 && H <= 8192, "rmsnorm_rsigma: hidden size %lld must be a multiple of 8 and <= 8192", (long long)H);
+    LLMFP8_REQUIRE(reinterpret_cast<uintptr_t>(x) % 16 == 0, "rmsnorm_rsigma: misaligned pointer");
+    if (M == 0) return 0;
+    const int nit = static_cast<int>((H / 8 + RMS_T - 1) / RMS_T);
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
+    const int grid = static_cast<int>(M < cap ? M : cap);
+    int rc = dispatch_rms_fwd<FMT_E4M3, 1>(nit, grid, stream, (const uint4*)x, nullptr, nullptr, rsigma, M, (int)H, eps, nullptr, nullptr);
+    if (rc) return rc;
+    LLMFP8_LAUNCH_CHECK("rmsnorm_rsigma");
+    return 0;
+}
+
+// ------------------------------------------------------------------------------------------- K5
+// dx = rs * (dy*g - xhat * mean(dy*g*xhat)),  dgamma = sum_rows dy * xhat   (xhat = x * rs), fp32 math.
+template <int NIT>
+__global__ void __launch_bounds__(RMS_T) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
+                                                            const float* __restrict__ rsigma, uint4* __restrict__ dx, float* __restrict__ dgamma_part,
+                                                            int64_t M, int H) {
+    __shared__ float red[2][4];
+    const int t = threadIdx.x;
+    const int nchunk = H / 8;
+    float dg[NIT][8];
+    uint4 g[NIT];
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
+#pragma unroll
+        for (int j = 0; j < 8; j++) dg[it][j] = 0.f;
+        if (it * RMS_T + t < nchunk) g[it] = __ldg(gamma + it * RMS_T + t);
+    }
+    int par = 0;
+    for (int64_t row = blockIdx.x; row < M; row += gridDim.x, par ^= 1) {
+        uint4 vx[NIT], vdy[NIT];
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + t < nchunk) {
+                vx[it] = ldg_stream(x + row * nchunk + it * RMS_T + t);
+                vdy[it] = ldg_stream(dy + row * nchunk + it * RMS_T + t);
+            }
+        const float rs = rsigma[row];
+        float dot = 0.f;
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + t < nchunk) {
+                float fx[8], fdy[8], fg[8];
+                unpack8(vx[it], fx);
+                unpack8(vdy[it], fdy);
+                unpack8(g[it], fg);
+#pragma unroll
+                for (int j = 0; j < 8; j++) {
+                    const float xh = fx[j] * rs;
+                    dot = fmaf(fdy[j] * fg[j], xh, dot);
+                    dg[it][j] = fmaf(fdy[j], xh, dg[it][j]);
+                }
+            }
+        dot = warp_sum(dot);
+        if ((t & 31) == 0) red[par][t >> 5] = dot;
+        __syncthreads();
+        const float c = (red[par][0] + red[par][1] + red[par][2] + red[par][3]) / static_cast<float>(H);
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + t < nchunk) {
+                float fx[8], fdy[8], fg[8], o[8];
+                unpack8(vx[it], fx);
+                unpack8(vdy[it], fdy);
+                unpack8(g[it], fg);
+#pragma unroll
+                for (int j = 0; j < 8; j++) o[j] = rs * (fdy[j] * fg[j] - (fx[j] * rs) * c);
+                uint4 ov;
+                ov.x = pack_bf16x2(o[0], o[1]); ov.y = pack_bf16x2(o[2], o[3]);
+                ov.z = pack_bf16x2(o[4], o[5]); ov.w = pack_bf16x2(o[6], o[7]);
+                dx[row * nchunk + it * RMS_T + t] = ov;
+            }
+    }
+    float* out = dgamma_part + static_cast<int64_t>(blockIdx.x) * H;
+#pragma unroll
+    for (int it = 0; it < NIT; it++)
+        if (it * RMS_T + t < nchunk) {
+            float4* o4 = reinterpret_cast<float4*>(out + (it * RMS_T + t) * 8);
+            o4[0] = make_float4(dg[it][0], dg[it][1], dg[it][2], dg[it][3]);
+            o4[1] = make_float4(dg[it][4], dg[it][5], dg[it][6], dg[it][7]);
+        }
+}
+
+__global__ void colreduce_bf16_kernel(const float* __restrict__ part, int nparts, int H, uint16_t* __restrict__ out) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= H) return;
+    float s = 0.f;
+    for (int p = 0; p < nparts; p++) s += part[static_cast<int64_t>(p) * H + c];
+    out[c] = static_cast<uint16_t>(pack_bf16x2(s, 0.f) & 0xffffu);
+}
+
+int rmsnorm_bwd_grid(int64_t M) {
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 3;
+    return static_cast<int>(M < cap ? M : cap);
+}
+
+// ws: fp32 [rmsnorm_bwd_grid(M) * H]
+int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma_bf16, float* ws,
+                       int64_t M, int64_t H, cudaStream_t stream) {
+    LLMFP8_REQUIRE(H % 8 == 0 && H > 0 && H <= 8192, "rmsnorm_bwd: hidden size %lld must be a multiple of 8 and <= 8192", (long long)H);
+    LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(dx) |
+                    reinterpret_cast<uintptr_t>(ws)) % 16 == 0, "rmsnorm_bwd: misaligned pointers");
+    if (M == 0) return 0;
+    const int nit = static_cast<int>((H / 8 + RMS_T - 1) / RMS_T);
+    const int grid = rmsnorm_bwd_grid(M);
+#define RMSB_CASE(N)                                                                                                                           \
+    case N:                                                                                                                                    \
+        rmsnorm_bwd_kernel<N><<<grid, RMS_T, 0, stream>>>((const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (uint4*)dx, ws, M, (int)H); \
+        break;
+    switch (nit) {
+        RMSB_CASE(1) RMSB_CASE(2) RMSB_CASE(3) RMSB_CASE(4) RMSB_CASE(5) RMSB_CASE(6) RMSB_CASE(7) RMSB_CASE(8)
+        default: set_error("rmsnorm_bwd: hidden size too large"); return -1;
+    }
+#undef RMSB_CASE
+    LLMFP8_LAUNCH_CHECK("rmsnorm_bwd");
+    colreduce_bf16_kernel<<<static_cast<unsigned>((H + 255) / 256), 256, 0, stream>>>(ws, grid, (int)H, static_cast<uint16_t*>(dgamma_bf16));
+    LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
+    return 0;
+}
+
+}  // namespace llmfp8

@@ -1,0 +1,170 @@
+"""fp8_autocast and the delayed-scaling state (mirrors te.pytorch.fp8_autocast as used at te_llama.py:76,79).
+
+State layout: every fp8 tensor of every module owns one *slot* in a flat per-(recipe, direction,
+device) pool: amax_history[L, CAP], scale[CAP], scale_inv[CAP], fmax[CAP].  Quantise kernels atomically max into
+amax_history[0, slot]; one K4 launch (llmfp8_amax_scale_update) updates the whole pool after ONE all-reduce(MAX) of row 0
+over the data-parallel group — once per direction per step instead of once per autocast exit:
+
+  * leaving the outermost fp8_autocast (grad enabled) marks the forward pools *pending*;
+  * the backward of a module marks its backward pool pending;
+  * a pool is flushed (all-reduce + K4) lazily, right before a module whose slots are pending quantises again.
+
+For a module that runs once per step this is exactly TE's schedule (the scale a tensor is quantised with at step t was
+computed from amaxes of steps < t), with 2 collectives per step instead of 2 per decoder layer.
+"""
+from __future__ import annotations
+
+import threading
+from contextlib import contextmanager
+from typing import Dict, List, Optional
+
+import torch
+
+from . import _lib
+from .recipe import DelayedScaling, Format, MXFP8BlockScaling, Recipe, get_default_fp8_recipe
+
+_POOL_CAP = 4096
+
+
+class ScalePool:
+    """Flat delayed-scaling state for one (recipe, direction, device)."""
+
+    def __init__(self, recipe: DelayedScaling, forward: bool, device: torch.device):
+        self.recipe, self.forward, self.device = recipe, forward, device
+        L = recipe.amax_history_len
+        self.amax_history = torch.zeros(L, _POOL_CAP, dtype=torch.float32, device=device)
+        self.scale = torch.ones(_POOL_CAP, dtype=torch.float32, device=device)
+        self.scale_inv = torch.ones(_POOL_CAP, dtype=torch.float32, device=device)
+        fmax = recipe.fp8_format.value.max_fwd if forward else recipe.fp8_format.value.max_bwd
+        self.fmax = torch.full((_POOL_CAP,), fmax, dtype=torch.float32, device=device)
+        self.used = 0
+        self.pending = False          # amaxes recorded and their region closed, update not yet applied
+        self.epoch = 0                # number of flushes
+        self.group = None
+
+    def claim(self, n: int) -> int:
+        if self.used + n > _POOL_CAP:
+            raise RuntimeError(f"fp8 scale pool exhausted ({_POOL_CAP} slots)")
+        off = self.used
+        self.used += n
+        return off
+
+    # device pointers of a slot
+    def scale_ptr(self, slot: int) -> int:
+        return self.scale.data_ptr() + 4 * slot
+
+    def scale_inv_ptr(self, slot: int) -> int:
+        return self.scale_inv.data_ptr() + 4 * slot
+
+    def amax_ptr(self, slot: int) -> int:
+        return self.amax_history.data_ptr() + 4 * slot      # row 0
+
+    def flush(self):
+        """all-reduce(MAX) of this step's amaxes over the data-parallel group, then K4 over the used slots."""
+        if not self.pending or self.used == 0:
+            self.pending = False
+            return
+        T = self.used
+        if self.recipe.reduce_amax and torch.distributed.is_available() and torch.distributed.is_initialized():
+            group = self.group
+            if torch.distributed.get_world_size(group) > 1:
+                torch.distributed.all_reduce(self.amax_history[0, :T], op=torch.distributed.ReduceOp.MAX, group=group)
+        amax_scale_update(self.amax_history, self.scale, self.scale_inv, self.fmax, T, self.recipe.margin)
+        self.pending = False
+        self.epoch += 1
+
+    def state(self) -> dict:
+        T = self.used
+        return {"amax_history": self.amax_history[:, :T].clone(), "scale": self.scale[:T].clone(), "scale_inv": self.scale_inv[:T].clone()}
+
+
+def amax_scale_update(hist: torch.Tensor, scale: torch.Tensor, scale_inv: torch.Tensor, fmax: torch.Tensor, T: int, margin: int):
+    """K4 over a pool laid out [L, CAP] / [CAP].  The kernel indexes hist densely as [L, width], so the full CAP width is
+    updated in one launch: unused slots hold amax 0 and keep scale 1 (the amax > 0 guard)."""
+    L, cap = hist.shape
+    stream = torch.cuda.current_stream(hist.device).cuda_stream
+    rc = _lib.load().llmfp8_amax_scale_update(hist.data_ptr(), scale.data_ptr(), scale_inv.data_ptr(), fmax.data_ptr(), L, cap, margin, stream)
+    _lib.check(rc, "amax_scale_update")
+
+
+class _State(threading.local):
+    def __init__(self):
+        self.stack: List[tuple] = []     # (enabled, recipe, group)
+        self.touched_fwd: List[ScalePool] = []
+
+
+_state = _State()
+_pools: Dict[tuple, ScalePool] = {}
+_pools_lock = threading.Lock()
+
+
+def get_pool(recipe: DelayedScaling, forward: bool, device: torch.device) -> ScalePool:
+    key = (recipe.key(), forward, device.index if device.index is not None else torch.cuda.current_device())
+    with _pools_lock:
+        p = _pools.get(key)
+        if p is None:
+            p = _pools[key] = ScalePool(recipe, forward, device)
+        return p
+
+
+def all_pools() -> List[ScalePool]:
+    return list(_pools.values())
+
+
+def reset_fp8_state():
+    """Drop every delayed-scaling pool (tests)."""
+    with _pools_lock:
+        _pools.clear()
+
+
+def flush_all():
+    """Apply every pending amax reduction + scale update now (e.g. before checkpointing the scaling state)."""
+    for p in all_pools():
+        p.flush()
+
+
+def is_fp8_enabled() -> bool:
+    return bool(_state.stack) and _state.stack[-1][0]
+
+
+def get_fp8_recipe() -> Recipe:
+    if _state.stack and _state.stack[-1][1] is not None:
+        return _state.stack[-1][1]
+    return get_default_fp8_recipe()
+
+
+def get_fp8_group():
+    return _state.stack[-1][2] if _state.stack else None
+
+
+def note_forward_pool(pool: ScalePool):
+    if pool not in _state.touched_fwd:
+        _state.touched_fwd.append(pool)
+
+
+@contextmanager
+def fp8_autocast(enabled: bool = True, calibrating: bool = False, fp8_recipe: Optional[Recipe] = None, fp8_group=None, _graph: bool = False):
+    """Context manager selecting the FP8 recipe for the modules called inside it.  Nestable; the innermost recipe wins
+    (the reference nests its per-block autocasts inside accelerate's outer one: train_fp8.py:184-188)."""
+    if enabled and not torch.cuda.is_available():
+        raise RuntimeError("fp8_autocast(enabled=True) needs a CUDA device: llm_fp8_b200 has no CPU path")
+    _state.stack.append((enabled, fp8_recipe, fp8_group))
+    try:
+        yield
+    finally:
+        _state.stack.pop()
+        if not _state.stack:
+            if torch.is_grad_enabled():
+                for p in _state.touched_fwd:
+                    p.pending = True
+            _state.touched_fwd = []
+
+
+def is_fp8_available(return_reason: bool = False):
+    ok = torch.cuda.is_available() and torch.cuda.get_device_capability()[0] >= 10
+    reason = "" if ok else "llm_fp8_b200 needs an sm_100a (B200) device"
+    return (ok, reason) if return_reason else ok
+
+
+def is_mxfp8_available(return_reason: bool = False):
+    return is_fp8_available(return_reason)

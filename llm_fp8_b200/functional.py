@@ -1,0 +1,259 @@
+"""Autograd functions of the FP8 linear path: every forward / backward below is a fixed sequence of C-ABI calls
+(ops.py).  The sequences follow SURVEY.md §3.2:
+
+  Linear           fwd: K2(x) K2(W) G1            bwd: K2b(dY) G2 G3
+  LayerNormLinear  fwd: K1(x) K2(W) G1            bwd: K2b(dY) G2 G3 K5
+  LayerNormMLP     fwd: K1 K2(W1) G1+b K3 K2(W2) G1+b
+                   bwd: K2b(dY) G2(fc2) K3b G3(fc2) G2(fc1) G3(fc1) K5
+and their MXFP8 counterparts (K1m/K2m quantisers, block-scaled GEMMs).
+"""
+from __future__ import annotations
+
+from typing import Optional
+
+import torch
+
+from . import ops
+from .fp8 import ScalePool, get_pool, note_forward_pool
+from .recipe import DelayedScaling, MXFP8BlockScaling, Recipe, bwd_fmt, fwd_fmt
+
+
+class Fp8Meta:
+    """Slot bookkeeping of one module inside the per-recipe pools (claimed lazily, per recipe key)."""
+
+    def __init__(self, n_fwd: int, n_bwd: int):
+        self.n_fwd, self.n_bwd = n_fwd, n_bwd
+        self._slots = {}          # (recipe key, device index) -> dict
+
+    def get(self, recipe: DelayedScaling, device: torch.device):
+        key = (recipe.key(), device.index)
+        s = self._slots.get(key)
+        if s is None:
+            pf, pb = get_pool(recipe, True, device), get_pool(recipe, False, device)
+            s = self._slots[key] = {"pf": pf, "pb": pb, "f0": pf.claim(self.n_fwd), "b0": pb.claim(self.n_bwd), "ef": -1, "eb": -1}
+        return s
+
+    @staticmethod
+    def begin_fwd(s, training: bool):
+        pf: ScalePool = s["pf"]
+        if pf.pending and s["ef"] == pf.epoch:
+            pf.flush()
+        if training:
+            s["ef"] = pf.epoch
+            note_forward_pool(pf)
+
+    @staticmethod
+    def begin_bwd(s):
+        pb: ScalePool = s["pb"]
+        if pb.pending and s["eb"] == pb.epoch:
+            pb.flush()
+        s["eb"] = pb.epoch
+
+    @staticmethod
+    def end_bwd(s):
+        s["pb"].pending = True
+
+
+def _2d(x: torch.Tensor) -> torch.Tensor:
+    return x.reshape(-1, x.shape[-1])
+
+
+def _wgrad(dyq, xq, N, K, T, weight):
+    """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
+    return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
+
+
+# ====================================================================================== per-tensor (DelayedScaling)
+class LinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, meta: Fp8Meta, recipe: DelayedScaling, ln_weight, eps, is_grad_enabled):
+        """ln_weight None: plain Linear; else LayerNormLinear (RMSNorm fused into the input cast)."""
+        dev = x.device
+        s = meta.get(recipe, dev)
+        Fp8Meta.begin_fwd(s, is_grad_enabled)
+        pf, f0 = s["pf"], s["f0"]
+        ff = fwd_fmt(recipe.fp8_format)
+        x2 = _2d(x).contiguous()
+        M, K = x2.shape
+        N = weight.shape[0]
+        rsigma = None
+        if ln_weight is not None:
+            xq, rsigma = ops.rmsnorm_quant(x2, ln_weight, eps, ff, pf, f0 + 0)
+        else:
+            xq = ops.quantize(x2, ff, pf, f0 + 0)
+        wq = ops.quantize(weight, ff, pf, f0 + 1)
+        y = ops.fp8_gemm(xq, False, wq, False, M, N, K, bias=bias)
+        if is_grad_enabled:
+            ctx.save_for_backward(xq.data, wq.data, x2 if ln_weight is not None else None, ln_weight, rsigma)
+            ctx.meta, ctx.recipe, ctx.slots = meta, recipe, s
+            ctx.has_bias = bias is not None
+            ctx.shape = x.shape
+            ctx.dims = (M, N, K)
+            ctx.wdtype = weight.dtype
+            ctx.needs = (x.requires_grad, weight.requires_grad)
+        return y.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        xq_d, wq_d, x2, ln_weight, rsigma = ctx.saved_tensors
+        s, recipe = ctx.slots, ctx.recipe
+        M, N, K = ctx.dims
+        Fp8Meta.begin_bwd(s)
+        pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
+        ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
+        xq = ops.QTensor(xq_d, ff, pf.scale_inv, f0 + 0)
+        wq = ops.QTensor(wq_d, ff, pf.scale_inv, f0 + 1)
+        dy2 = _2d(dy).contiguous()
+        dbias = None
+        if ctx.has_bias:
+            dyq, dbias = ops.quantize_bgrad(dy2, bf, pb, b0 + 0)
+        else:
+            dyq = ops.quantize(dy2, bf, pb, b0 + 0)
+        dx = ops.fp8_gemm(dyq, False, wq, True, M, K, N)                  # dgrad: contraction over N, W read MN-major
+        dw = ops.fp8_gemm(dyq, True, xq, True, N, K, M, out_dtype=ctx.wdtype)   # wgrad: contraction over tokens
+        dgamma = None
+        if ln_weight is not None:
+            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma)
+        Fp8Meta.end_bwd(s)
+        return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None
+
+
+class LayerNormMLPFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, meta: Fp8Meta, recipe: DelayedScaling, eps, is_grad_enabled):
+        dev = x.device
+        s = meta.get(recipe, dev)
+        Fp8Meta.begin_fwd(s, is_grad_enabled)
+        pf, f0 = s["pf"], s["f0"]
+        ff = fwd_fmt(recipe.fp8_format)
+        x2 = _2d(x).contiguous()
+        M, H = x2.shape
+        I2 = w1.shape[0]
+        I = I2 // 2
+        lnq, rsigma = ops.rmsnorm_quant(x2, ln_weight, eps, ff, pf, f0 + 0)
+        w1q = ops.quantize(w1, ff, pf, f0 + 1)
+        fc1 = ops.fp8_gemm(lnq, False, w1q, False, M, I2, H, bias=b1)
+        aq = ops.swiglu_quant(fc1, ff, pf, f0 + 3)
+        w2q = ops.quantize(w2, ff, pf, f0 + 4)
+        y = ops.fp8_gemm(aq, False, w2q, False, M, H, I, bias=b2)
+        if is_grad_enabled:
+            ctx.save_for_backward(x2, ln_weight, rsigma, lnq.data, w1q.data, fc1, aq.data, w2q.data)
+            ctx.recipe, ctx.slots = recipe, s
+            ctx.has_bias = b1 is not None
+            ctx.shape = x.shape
+            ctx.dims = (M, H, I)
+            ctx.wdtype = w1.dtype
+        return y.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, ln_weight, rsigma, lnq_d, w1q_d, fc1, aq_d, w2q_d = ctx.saved_tensors
+        s, recipe = ctx.slots, ctx.recipe
+        M, H, I = ctx.dims
+        Fp8Meta.begin_bwd(s)
+        pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
+        ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
+        lnq = ops.QTensor(lnq_d, ff, pf.scale_inv, f0 + 0)
+        w1q = ops.QTensor(w1q_d, ff, pf.scale_inv, f0 + 1)
+        aq = ops.QTensor(aq_d, ff, pf.scale_inv, f0 + 3)
+        w2q = ops.QTensor(w2q_d, ff, pf.scale_inv, f0 + 4)
+        dy2 = _2d(dy).contiguous()
+        db2 = db1 = None
+        if ctx.has_bias:
+            dyq, db2 = ops.quantize_bgrad(dy2, bf, pb, b0 + 2)
+        else:
+            dyq = ops.quantize(dy2, bf, pb, b0 + 2)
+        da = ops.fp8_gemm(dyq, False, w2q, True, M, I, H)                        # fc2 dgrad
+        dfc1q, db1 = ops.dswiglu_quant(da, fc1, bf, pb, b0 + 0, want_dbias=ctx.has_bias)
+        dw2 = ops.fp8_gemm(dyq, True, aq, True, H, I, M, out_dtype=ctx.wdtype)   # fc2 wgrad
+        dln = ops.fp8_gemm(dfc1q, False, w1q, True, M, H, 2 * I)                 # fc1 dgrad
+        dw1 = ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype)   # fc1 wgrad
+        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma)
+        Fp8Meta.end_bwd(s)
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None
+
+
+# ====================================================================================== MXFP8
+def _mx_bgrad(dy2: torch.Tensor) -> torch.Tensor:
+    """bias gradient for the MXFP8 path: the per-tensor K2b kernel's column sums, its fp8 output discarded."""
+    _, bgrad = ops.quantize_bgrad_raw(dy2, 0, None, None)
+    return bgrad
+
+
+class MXLinearFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, weight, bias, ln_weight, eps, is_grad_enabled):
+        x2 = _2d(x).contiguous()
+        M, K = x2.shape
+        N = weight.shape[0]
+        rsigma = None
+        if ln_weight is not None:
+            rsigma = ops.rmsnorm_rsigma(x2, eps)
+            xq = ops.mx_quantize(x2, True, is_grad_enabled, rsigma, ln_weight)
+        else:
+            xq = ops.mx_quantize(x2, True, is_grad_enabled)
+        wq = ops.mx_quantize(weight, True, is_grad_enabled)
+        y = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, bias=bias)
+        if is_grad_enabled:
+            ctx.save_for_backward(xq.col, xq.sf_col, wq.col, wq.sf_col, x2 if ln_weight is not None else None, ln_weight, rsigma)
+            ctx.has_bias = bias is not None
+            ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, N, K), weight.dtype
+        return y.reshape(*x.shape[:-1], N)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x_col, x_sfc, w_col, w_sfc, x2, ln_weight, rsigma = ctx.saved_tensors
+        M, N, K = ctx.dims
+        dy2 = _2d(dy).contiguous()
+        dbias = _mx_bgrad(dy2) if ctx.has_bias else None
+        dyq = ops.mx_quantize(dy2, True, True)
+        # dgrad: dX[M,K] = dY[M,N] W[N,K]: dY rowwise (blocks along N), W colwise (blocks along N), W read MN-major
+        dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N)
+        # wgrad: dW[N,K] = dY^T X: both colwise (blocks along tokens), both MN-major
+        dw = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out_dtype=ctx.wdtype)
+        dgamma = None
+        if ln_weight is not None:
+            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma)
+        return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None
+
+
+class MXLayerNormMLPFn(torch.autograd.Function):
+    """MXFP8 LayerNormMLP.  SwiGLU / dSwiGLU run in our pinned-exp kernel with a bf16 result that the block quantiser then
+    reads (one extra bf16 round trip compared with a fully fused activation+MX quantiser: DESIGN.md 'next')."""
+
+    @staticmethod
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, eps, is_grad_enabled):
+        x2 = _2d(x).contiguous()
+        M, H = x2.shape
+        I2 = w1.shape[0]
+        I = I2 // 2
+        g = is_grad_enabled
+        rsigma = ops.rmsnorm_rsigma(x2, eps)
+        lnq = ops.mx_quantize(x2, True, g, rsigma, ln_weight)
+        w1q = ops.mx_quantize(w1, True, g)
+        fc1 = ops.mxfp8_gemm(lnq.row, lnq.sf_row, False, w1q.row, w1q.sf_row, False, M, I2, H, bias=b1)
+        a = ops.swiglu_bf16(fc1)
+        aq = ops.mx_quantize(a, True, g)
+        w2q = ops.mx_quantize(w2, True, g)
+        y = ops.mxfp8_gemm(aq.row, aq.sf_row, False, w2q.row, w2q.sf_row, False, M, H, I, bias=b2)
+        if g:
+            ctx.save_for_backward(x2, ln_weight, rsigma, lnq.col, lnq.sf_col, w1q.col, w1q.sf_col, fc1, aq.col, aq.sf_col, w2q.col, w2q.sf_col)
+            ctx.has_bias = b1 is not None
+            ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, H, I), w1.dtype
+        return y.reshape(x.shape)
+
+    @staticmethod
+    def backward(ctx, dy):
+        x2, ln_weight, rsigma, ln_col, ln_sfc, w1_col, w1_sfc, fc1, a_col, a_sfc, w2_col, w2_sfc = ctx.saved_tensors
+        M, H, I = ctx.dims
+        dy2 = _2d(dy).contiguous()
+        db2 = _mx_bgrad(dy2) if ctx.has_bias else None
+        dyq = ops.mx_quantize(dy2, True, True)
+        da = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w2_col, w2_sfc, True, M, I, H)                       # fc2 dgrad
+        dfc1, db1 = ops.dswiglu_bf16(da, fc1, want_dbias=ctx.has_bias)
+        dfq = ops.mx_quantize(dfc1, True, True)
+        dw2 = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype)      # fc2 wgrad
+        dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad
+        dw1 = ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype)  # fc1 wgrad
+        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma)
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None

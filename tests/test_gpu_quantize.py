@@ -1,0 +1,234 @@
+"""Bit-exact parity of the quantise kernels (through the C ABI) with the CPU oracle."""
+import pytest
+import torch
+
+from oracle import c_oracle as co
+from oracle import fp8_oracle as fo
+
+pytestmark = pytest.mark.gpu
+E4M3, E5M2 = fo.E4M3, fo.E5M2
+FMT = {E4M3: 0, E5M2: 1}
+
+
+def _ops():
+    from llm_fp8_b200 import ops
+    return ops
+
+
+def dev(x):
+    return x.cuda()
+
+
+def gen(shape, seed, kind="normal"):
+    g = torch.Generator().manual_seed(seed)
+    x = torch.randn(shape, generator=g)
+    if kind == "heavy":
+        x = x * torch.exp(torch.randn(shape, generator=g))
+    if kind == "outlier":
+        mask = torch.rand(shape, generator=g) < 1e-3
+        x = torch.where(mask, x * 100, x)
+    return x.bfloat16()
+
+
+def assert_fp8_equal(got_u8, want_u8, dtype):
+    """bytes equal; NaN positions only need to be NaN on both sides."""
+    got_u8, want_u8 = got_u8.cpu().reshape(-1), want_u8.cpu().reshape(-1)
+    nan_w = torch.isnan(want_u8.view(dtype).float())
+    nan_g = torch.isnan(got_u8.view(dtype).float())
+    assert torch.equal(nan_w, nan_g)
+    bad = (got_u8 != want_u8) & ~nan_w
+    assert not bad.any(), f"{int(bad.sum())} of {bad.numel()} bytes differ; first at {int(bad.nonzero()[0])}"
+
+
+@pytest.mark.parametrize("dtype", [E4M3, E5M2])
+def test_cast_all_bf16_values(dtype):
+    ops = _ops()
+    x = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
+    for scale in (1.0, 0.37, 448.0 / 3.1, 2.0 ** -20, 3.0e38):
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q = ops.quantize_raw(dev(x), FMT[dtype], s, amax)
+        qo, ao = fo.quantize(x, scale, dtype)
+        assert_fp8_equal(q, qo.view(torch.uint8), dtype)
+        assert amax.item() == ao.item()
+
+
+@pytest.mark.parametrize("kind", ["normal", "heavy", "outlier"])
+@pytest.mark.parametrize("shape", [(6144, 4096), (48, 16), (1, 16), (333, 80)])
+def test_cast_amax(shape, kind):
+    ops = _ops()
+    x = gen(shape, 1, kind)
+    am0 = fo.amax_of(x).item()
+    scale = 448.0 / am0
+    for dtype in (E4M3, E5M2):
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q = ops.quantize_raw(dev(x), FMT[dtype], s, amax)
+        qo, ao = fo.quantize(x, scale, dtype)
+        assert_fp8_equal(q, qo.view(torch.uint8), dtype)
+        assert amax.item() == ao.item()
+    # amax accumulates (atomic max), never lowers
+    amax = torch.full((1,), 1e30, dtype=torch.float32).cuda()
+    ops.quantize_raw(dev(x), 0, s, amax)
+    assert amax.item() == pytest.approx(1e30)
+
+
+def test_cast_empty_and_contract():
+    ops = _ops()
+    x = torch.empty(0, 16, dtype=torch.bfloat16).cuda()
+    assert ops.quantize_raw(x, 0, None, None).numel() == 0
+    with pytest.raises(RuntimeError, match="multiple of 16"):
+        ops.quantize_raw(torch.zeros(3, 8, dtype=torch.bfloat16).cuda(), 0, None, None)
+    with pytest.raises(RuntimeError, match="CUDA"):
+        ops.quantize_raw(torch.zeros(16, dtype=torch.bfloat16), 0, None, None)
+
+
+@pytest.mark.parametrize("shape", [(8192, 4096), (100, 264), (7, 8), (513, 2048)])
+def test_cast_bgrad(shape):
+    ops = _ops()
+    x = gen(shape, 2) * 1e-3
+    x = x.bfloat16()
+    scale = 57344.0 / fo.amax_of(x).item()
+    s = torch.tensor([scale], dtype=torch.float32).cuda()
+    amax = torch.zeros(1, dtype=torch.float32).cuda()
+    q, bgrad = ops.quantize_bgrad_raw(dev(x), 1, s, amax)
+    qo, ao = fo.quantize(x, scale, E5M2)
+    assert_fp8_equal(q, qo.view(torch.uint8), E5M2)
+    assert amax.item() == ao.item()
+    want = co.colsum_bf16(x)
+    tol = 1e-2 * want.abs().max().item() + 1e-6
+    assert (bgrad.float().cpu() - want).abs().max().item() <= tol
+
+
+@pytest.mark.parametrize("H", [2048, 3072, 4096, 5120, 136, 8192])
+def test_rmsnorm_quant(H):
+    ops = _ops()
+    M = 6144 if H == 4096 else 67
+    g = torch.Generator().manual_seed(H)
+    x = gen((M, H), 3, "heavy" if H == 4096 else "normal")
+    gamma = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+    eps = 1e-5
+    _, _, am, _ = co.rmsnorm_quant(x, gamma, eps, 1.0, E4M3)
+    scale = 448.0 / am
+    for dtype in (E4M3, E5M2):
+        qo, rso, amo, _ = co.rmsnorm_quant(x, gamma, eps, scale, dtype)
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q, rs = ops.rmsnorm_quant_raw(dev(x), dev(gamma), eps, FMT[dtype], s, amax)
+        assert torch.equal(rs.cpu(), rso), "rsigma must match the pinned reduction order bit for bit"
+        assert_fp8_equal(q, qo, dtype)
+        assert amax.item() == amo
+    rs2 = ops.rmsnorm_rsigma(dev(x), eps)
+    assert torch.equal(rs2.cpu(), rso)
+
+
+def test_rmsnorm_bwd():
+    ops = _ops()
+    for M, H in ((300, 2048), (64, 4096), (33, 5120)):
+        x, dy = gen((M, H), 4), gen((M, H), 5)
+        g = torch.Generator().manual_seed(9)
+        gamma = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+        rs = ops.rmsnorm_rsigma(dev(x), 1e-5)
+        dx, dgamma = ops.rmsnorm_bwd(dev(dy), dev(x), dev(gamma), rs)
+        xf = x.float().requires_grad_(True)
+        gf = gamma.float().requires_grad_(True)
+        y, _ = fo.rmsnorm_ref(xf, gf, 1e-5)
+        y.backward(dy.float())
+        assert torch.allclose(dx.float().cpu(), xf.grad, rtol=2e-2, atol=2e-2 * xf.grad.abs().max().item())
+        assert torch.allclose(dgamma.float().cpu(), gf.grad, rtol=2e-2, atol=2e-2 * gf.grad.abs().max().item())
+
+
+@pytest.mark.parametrize("shape", [(6144, 2 * 1024), (50, 2 * 264), (3, 16)])
+def test_swiglu_quant(shape):
+    ops = _ops()
+    fc1 = (gen(shape, 6) * 3).bfloat16()
+    a = co.swiglu_f32(fc1)
+    scale = 448.0 / a.abs().max().item()
+    for dtype in (E4M3, E5M2):
+        qo, amo = co.swiglu_quant(fc1, scale, dtype)
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q = ops.swiglu_quant_raw(dev(fc1), FMT[dtype], s, amax)
+        assert_fp8_equal(q, qo, dtype)
+        assert amax.item() == amo
+    ab = ops.swiglu_bf16(dev(fc1))
+    assert torch.equal(ab.cpu(), a.bfloat16())
+
+
+@pytest.mark.parametrize("shape", [(4096, 1024), (77, 264), (5, 8)])
+def test_dswiglu_quant(shape):
+    ops = _ops()
+    M, I = shape
+    fc1 = (gen((M, 2 * I), 7) * 3).bfloat16()
+    da = (gen((M, I), 8) * 1e-2).bfloat16()
+    d = co.dswiglu_f32(da, fc1)
+    scale = 57344.0 / d.abs().max().item()
+    for dtype in (E5M2, E4M3):
+        qo = co.cast_f32(d * torch.tensor(scale, dtype=torch.float32), dtype)
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q, dbias = ops.dswiglu_quant_raw(dev(da), dev(fc1), FMT[dtype], s, amax)
+        assert_fp8_equal(q, qo, dtype)
+        assert amax.item() == d.abs().max().item()
+        want = d.double().sum(0).float()
+        assert (dbias.float().cpu() - want).abs().max().item() <= 1e-2 * want.abs().max().item() + 1e-6
+    db, dbias2 = ops.dswiglu_bf16(dev(da), dev(fc1))
+    assert torch.equal(db.cpu(), d.bfloat16())
+
+
+def test_amax_scale_update_history_wrap():
+    from llm_fp8_b200 import fp8
+    T, L = 7, 16
+    fmax = torch.tensor([448.0, 448.0, 57344.0, 448.0, 57344.0, 448.0, 448.0])
+    hist = torch.zeros(L, T)
+    scale, sinv = torch.ones(T), torch.ones(T)
+    dh, ds, di, df = hist.cuda(), scale.cuda(), sinv.cuda(), fmax.cuda()
+    g = torch.Generator().manual_seed(5)
+    for step in range(40):
+        am = torch.rand(T, generator=g) * 10 ** float(torch.randint(-3, 4, (1,), generator=g))
+        if step == 7:
+            am[1] = float("inf")
+        if step in (20, 21):
+            am[3] = 0.0
+        hist[0] = am
+        dh[0] = am.cuda()
+        co.amax_scale_update(hist, scale, sinv, fmax, 0)
+        fp8.amax_scale_update(dh, ds, di, df, T, 0)
+        assert torch.equal(dh.cpu(), hist) and torch.equal(ds.cpu(), scale) and torch.equal(di.cpu(), sinv)
+
+
+@pytest.mark.parametrize("shape", [(6144, 4096), (256, 384), (128, 128), (96, 160), (4096, 28672 // 8)])
+def test_mx_quantize(shape):
+    ops = _ops()
+    R, C = shape
+    x = gen(shape, 10, "heavy")
+    x[5 % R, 32:64] = 0.0
+    if R > 130:
+        x[130, 7] = 3.0e38
+    x[:, 100] = (x[:, 100].float() * 1e-30).bfloat16()
+    want = co.mx_quantize_f32(x.float())
+    out = ops.mx_quantize(dev(x), True, True)
+    assert_fp8_equal(out.row, want["q_row"], E4M3)
+    assert torch.equal(out.sf_row.cpu(), want["sf_row"])
+    assert_fp8_equal(out.col, want["q_col"], E4M3)
+    assert torch.equal(out.sf_col.cpu(), want["sf_col"])
+    only_row = ops.mx_quantize(dev(x), True, False)
+    assert only_row.col is None and torch.equal(only_row.row.cpu(), out.row.cpu())
+
+
+@pytest.mark.parametrize("shape", [(6144, 4096), (160, 2048), (64, 5120)])
+def test_mx_rmsnorm_quantize(shape):
+    ops = _ops()
+    M, H = shape
+    x = gen(shape, 11)
+    g = torch.Generator().manual_seed(12)
+    gamma = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+    y, rso = co.rmsnorm_y(x, gamma, 1e-5)
+    want = co.mx_quantize_f32(y)
+    rs = ops.rmsnorm_rsigma(dev(x), 1e-5)
+    assert torch.equal(rs.cpu(), rso)
+    out = ops.mx_quantize(dev(x), True, True, rs, dev(gamma))
+    assert_fp8_equal(out.row, want["q_row"], E4M3)
+    assert torch.equal(out.sf_row.cpu(), want["sf_row"])
+    assert_fp8_equal(out.col, want["q_col"], E4M3)
+    assert torch.equal(out.sf_col.cpu(), want["sf_col"])

@@ -1,0 +1,156 @@
+"""Per-kernel microbenchmarks on one B200: quantise kernels in GB/s (algorithmic bytes), GEMMs in TFLOP/s,
+next to on-GPU comparison points (torch bf16 matmul, torch._scaled_mm = cuBLASLt FP8) — comparison points only, never a fallback.
+
+    python tools/microbench.py [--model llama8b] [--out gpurun_out/micro.jsonl]
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+
+import torch
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+import llm_fp8_b200 as te  # noqa: E402
+from llm_fp8_b200 import ops  # noqa: E402
+
+SHAPES = {  # H, I, qkv_out, M
+    "llama1b": (2048, 8192, 3072, 8192),
+    "llama3b": (3072, 8192, 5120, 8192),
+    "llama8b": (4096, 14336, 6144, 6144),
+    "qwen14b": (5120, 13824, 7168, 8192),
+}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return d["hbm_gbs"], d["bf16_tflops"], "measured"
+    return 6650.0, 1590.0, "fallback"
+
+
+_flush = None
+
+
+def flush_l2():
+    global _flush
+    if _flush is None:
+        _flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")
+    _flush.zero_()
+
+
+def timeit(fn, iters=10, warm=3, flush=True):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    ts = []
+    for _ in range(iters):
+        if flush:
+            flush_l2()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        fn()
+        b.record()
+        torch.cuda.synchronize()
+        ts.append(a.elapsed_time(b))
+    ts.sort()
+    return ts[len(ts) // 2], ts[0]
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--model", default="llama8b")
+    ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "micro.jsonl"))
+    ap.add_argument("--only", default="")
+    args = ap.parse_args()
+    H, I, QKV, M = SHAPES[args.model]
+    hbm, bf16_tf, src = peaks()
+    os.makedirs(os.path.dirname(args.out), exist_ok=True)
+    out = open(args.out, "a")
+
+    def emit(rec):
+        rec["model"] = args.model
+        print(json.dumps(rec), flush=True)
+        out.write(json.dumps(rec) + "\n")
+        out.flush()
+
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(1234)
+    scale = torch.tensor([32.0], device=dev)
+    amax = torch.zeros(1, device=dev)
+
+    def mem(name, fn, nbytes):
+        med, best = timeit(fn)
+        emit({"kernel": name, "ms": med, "ms_best": best, "GBps": nbytes / med / 1e6, "frac_hbm": nbytes / med / 1e6 / hbm, "peak": src, "bytes": nbytes})
+
+    if not args.only or "quant" in args.only:
+        x = torch.randn(M, H, device=dev, generator=g).bfloat16()
+        gamma = torch.ones(H, device=dev, dtype=torch.bfloat16)
+        w1 = torch.randn(2 * I, H, device=dev, generator=g).bfloat16() * 0.02
+        fc1 = torch.randn(M, 2 * I, device=dev, generator=g).bfloat16()
+        da = torch.randn(M, I, device=dev, generator=g).bfloat16()
+        mem("K2 cast_amax x[M,H]", lambda: ops.quantize_raw(x, 0, scale, amax), 3 * M * H)
+        mem("K2 cast_amax W1[2I,H]", lambda: ops.quantize_raw(w1, 0, scale, amax), 3 * 2 * I * H)
+        mem("K2b cast_amax_bgrad dY[M,H]", lambda: ops.quantize_bgrad_raw(x, 1, scale, amax), 3 * M * H)
+        mem("K1 rmsnorm_quant [M,H]", lambda: ops.rmsnorm_quant_raw(x, gamma, 1e-5, 0, scale, amax), 3 * M * H + 4 * M)
+        mem("K3 swiglu_quant [M,2I]", lambda: ops.swiglu_quant_raw(fc1, 0, scale, amax), 5 * M * I)
+        mem("K3b dswiglu_quant [M,2I]", lambda: ops.dswiglu_quant_raw(da, fc1, 1, scale, amax), 8 * M * I)
+        rs = ops.rmsnorm_rsigma(x, 1e-5)
+        mem("K5 rmsnorm_bwd [M,H]", lambda: ops.rmsnorm_bwd(x, x, gamma, rs), 6 * M * H)
+        mem("K2m mx_quantize row+col x[M,H]", lambda: ops.mx_quantize(x, True, True), int(4.0625 * M * H))
+        mem("K2m mx_quantize row x[M,H]", lambda: ops.mx_quantize(x, True, False), int(3.03125 * M * H))
+        mem("K2m mx_quantize row+col W1[2I,H]", lambda: ops.mx_quantize(w1, True, True), int(4.0625 * 2 * I * H))
+        mem("K1m rsigma + mx_quantize row+col [M,H]", lambda: ops.mx_quantize(x, True, True, ops.rmsnorm_rsigma(x, 1e-5), gamma), int(4.0625 * M * H))
+        mem("copy bf16 [M,2I] (torch, reference point)", lambda: fc1.clone(), 4 * M * 2 * I)
+        del x, w1, fc1, da
+
+    if not args.only or "gemm" in args.only:
+        one = torch.ones(1, device=dev)
+        layers = [("qkv", QKV, H), ("proj", H, H), ("fc1", 2 * I, H), ("fc2", H, I)]
+        for lname, N, K in layers:
+            xq = torch.randint(0, 120, (M, K), device=dev, dtype=torch.uint8)
+            wq = torch.randint(0, 120, (N, K), device=dev, dtype=torch.uint8)
+            dyq = torch.randint(0, 120, (M, N), device=dev, dtype=torch.uint8)
+            X, W, DY = ops.QTensor(xq, 0, one), ops.QTensor(wq, 0, one), ops.QTensor(dyq, 1, one)
+            flops = 2.0 * M * N * K
+
+            def rec(name, fn, extra=None):
+                med, best = timeit(fn, iters=8, warm=3, flush=False)
+                r = {"kernel": f"{name} {lname} M={M} N={N} K={K}", "ms": med, "ms_best": best, "TFLOPs": flops / med / 1e9,
+                     "frac_2x_bf16_measured": flops / med / 1e9 / (2 * bf16_tf), "frac_fp8_nominal": flops / med / 1e9 / 4500.0}
+                if extra:
+                    r.update(extra)
+                emit(r)
+
+            rec("G1 fprop fp8", lambda: ops.fp8_gemm(X, False, W, False, M, N, K))
+            rec("G2 dgrad fp8", lambda: ops.fp8_gemm(DY, False, W, True, M, K, N))
+            rec("G3 wgrad fp8", lambda: ops.fp8_gemm(DY, True, X, True, N, K, M))
+            sfx = torch.full((ops.mx_scale_bytes(M, K),), 127, device=dev, dtype=torch.uint8)
+            sfw = torch.full((ops.mx_scale_bytes(N, K),), 127, device=dev, dtype=torch.uint8)
+            rec("G1m fprop mxfp8", lambda: ops.mxfp8_gemm(xq, sfx, False, wq, sfw, False, M, N, K))
+            sfdy = torch.full((ops.mx_scale_bytes(M, N),), 127, device=dev, dtype=torch.uint8)
+            sfwc = torch.full((ops.mx_scale_bytes(K, N),), 127, device=dev, dtype=torch.uint8)
+            rec("G2m dgrad mxfp8", lambda: ops.mxfp8_gemm(dyq, sfdy, False, wq, sfwc, True, M, K, N))
+            sfdyc = torch.full((ops.mx_scale_bytes(N, M),), 127, device=dev, dtype=torch.uint8)
+            sfxc = torch.full((ops.mx_scale_bytes(K, M),), 127, device=dev, dtype=torch.uint8)
+            rec("G3m wgrad mxfp8", lambda: ops.mxfp8_gemm(dyq, sfdyc, True, xq, sfxc, True, N, K, M))
+            # comparison points (library): bf16 matmul and cuBLASLt FP8
+            xb = torch.randn(M, K, device=dev, dtype=torch.bfloat16)
+            wb = torch.randn(N, K, device=dev, dtype=torch.bfloat16)
+            rec("ref torch.matmul bf16 (cuBLAS)", lambda: xb @ wb.t())
+            try:
+                x8, w8 = xq.view(torch.float8_e4m3fn), wq.view(torch.float8_e4m3fn)
+                rec("ref torch._scaled_mm e4m3 (cuBLASLt)", lambda: torch._scaled_mm(x8, w8.t(), scale_a=one, scale_b=one, out_dtype=torch.bfloat16))
+            except Exception as e:  # noqa: BLE001
+                emit({"kernel": f"ref torch._scaled_mm {lname}", "error": str(e)[:200]})
+            del xq, wq, dyq, xb, wb
+    out.close()
+
+
+if __name__ == "__main__":
+    main()
