@@ -1,0 +1,356 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the FP8 / MXFP8 linear-layer hot path (BASELINE.json metric).
+
+A *step* = one forward + backward pass of the linear-layer path of a whole decoder stack (qkv, proj, fc1, fc2 GEMMs in
+fprop/dgrad/wgrad form, the fused RMSNorm / SwiGLU / quantise kernels around them) over one batch of synthetic tokens,
+driven through the plugin surface the reference's TELlamaDecoderLayer uses (LayerNormLinear / Linear / LayerNormMLP under
+fp8_autocast).  Default workload = BASELINE.json configs[3]: Llama-3.1-8B shapes, MXFP8BlockScaling, batch 12 x seq 512 per
+GPU, 32 layers, random-init weights.  Metric: linear TFLOP/s = 6 * tokens * P_linear / step time.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--scenario mxfp8|default|hybrid] [--model llama-3.1-8b] [--impl reference]
+
+N > 1: launched under torchrun, one rank per GPU; each rank owns `batch` sequences (weak scaling), the delayed-scaling
+amax pools are MAX-all-reduced and the weight gradients averaged over NCCL, overlapped with backward.
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "fp8_linear_path_tflops"
+UNIT = "TFLOP/s"
+FP8_NOMINAL_TFLOPS = 4500.0
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--model", default="llama-3.1-8b")
+    ap.add_argument("--scenario", default="mxfp8", choices=["mxfp8", "default", "hybrid"],
+                    help="reference decoder swap: mxfp8 = te_llama_mxfp8.py, default = te_llama.py, hybrid = te_llama_hybrid.py")
+    ap.add_argument("--batch", type=int, default=12, help="sequences per GPU (reference semantics: per-device batch)")
+    ap.add_argument("--seq", type=int, default=512)
+    ap.add_argument("--layers", type=int, default=0, help="0 = the model's own depth")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-roofline", action="store_true")
+    ap.add_argument("--cpu-sample-tokens", type=int, default=1536)
+    return ap.parse_args()
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm": d["hbm_gbs"], "bf16": d["bf16_tflops"], "bf16_sustained": d.get("bf16_tflops_sustained", d["bf16_tflops"]), "src": "measured"}
+    return {"hbm": 6650.0, "bf16": 1590.0, "bf16_sustained": 1400.0, "src": "fallback"}
+
+
+def workload_name(a, layers):
+    return f"{a.model} linear path x{layers} layers, scenario={a.scenario}, batch {a.batch} x seq {a.seq} per GPU, fwd+bwd"
+
+
+# ------------------------------------------------------------------------------------------------ clocks
+class ClockSampler:
+    Q = "clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown," \
+        "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, gpu_index: int):
+        self.p = None
+        try:
+            self.p = subprocess.Popen(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-lms", "100", "-i", str(gpu_index)],
+                                      stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except OSError:
+            self.p = None
+
+    def stop(self):
+        if self.p is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.p.terminate()
+        try:
+            out, _ = self.p.communicate(timeout=5)
+        except subprocess.TimeoutExpired:
+            self.p.kill()
+            out, _ = self.p.communicate()
+        sm, mx, pw, reasons = [], [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in out.strip().splitlines():
+            f = [x.strip() for x in line.split(",")]
+            if len(f) < 7:
+                continue
+            try:
+                sm.append(float(f[0])); mx.append(float(f[1])); pw.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[3:7]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        if not sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["no samples"]}
+        busy = [s for s, p in zip(sm, pw) if p > 0.5 * max(pw)] or sm
+        return {"sm_mhz": statistics.median(busy), "sm_max_mhz": max(mx), "power_w_max": max(pw), "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ------------------------------------------------------------------------------------------------ CPU legs
+def cpu_port_baseline(a, tokens: int):
+    """Oracle ('port') fake-quant linear path of ONE decoder layer on the host cores, bounded sample."""
+    import torch
+    from llm_fp8_b200.layer import MODEL_SHAPES, linear_params_per_layer
+    from oracle import fp8_oracle as fo
+    H, I, heads, kv, hd, _ = MODEL_SHAPES[a.model]
+    P = linear_params_per_layer(H, I, heads, kv, hd)
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    g = torch.Generator().manual_seed(7)
+    qkv = heads * hd + 2 * kv * hd
+    p = {"ln1": torch.ones(H), "ln2": torch.ones(H), "wqkv": torch.randn(qkv, H, generator=g) * 0.02, "wproj": torch.randn(H, heads * hd, generator=g) * 0.02,
+         "w1": torch.randn(2 * I, H, generator=g) * 0.02, "b1": torch.zeros(2 * I), "w2": torch.randn(H, I, generator=g) * 0.02, "b2": torch.zeros(H)}
+    for v in p.values():
+        v.requires_grad_(True)
+    x = torch.randn(tokens, H, generator=g).requires_grad_(True)
+    mx = a.scenario == "mxfp8"
+    bwd = fo.E4M3 if mx else fo.E5M2
+    best = None
+    for it in range(2):
+        t0 = time.perf_counter()
+        y = fo.fq_layer_linear_path(x, p, 1e-5, 1e-5, fo.E4M3, bwd, mx)
+        y.backward(torch.ones_like(y))
+        dt = time.perf_counter() - t0
+        best = dt if best is None or dt < best else best
+        x.grad = None
+        for v in p.values():
+            v.grad = None
+    return {"value": 6.0 * tokens * P / best / 1e12, "unit": UNIT, "cores": cores, "kind": "port",
+            "sample": f"oracle fake-quant ({'MXFP8' if mx else 'per-tensor FP8'}) linear path, 1 layer of {a.model}, {tokens} tokens, fwd+bwd, fp32 matmul, best of 2"}
+
+
+def reference_arm(a):
+    """`--impl reference`: the reference's own CPU-capable code path for these layers — the plain HF bf16 modules it builds
+    without --use_te (train_fp8.py:118-124) — on the host cores, one decoder layer's linear path per step on a bounded
+    token sample.  (Its TE path has no CPU implementation and TE is not installable here: DESIGN.md.)"""
+    import torch
+    import torch.nn as nn
+    from llm_fp8_b200.layer import MODEL_SHAPES, linear_params_per_layer
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    H, I, heads, kv, hd, L = MODEL_SHAPES[a.model]
+    P = linear_params_per_layer(H, I, heads, kv, hd)
+    tokens = a.cpu_sample_tokens
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    torch.manual_seed(0)
+    kind = "reference"
+    try:
+        from transformers import LlamaConfig
+        from transformers.models.llama.modeling_llama import LlamaMLP, LlamaRMSNorm
+        cfg = LlamaConfig(hidden_size=H, intermediate_size=I, num_attention_heads=heads, num_key_value_heads=kv, head_dim=hd, rms_norm_eps=1e-5,
+                          num_hidden_layers=1, vocab_size=32)
+        ln1, ln2, mlp = LlamaRMSNorm(H, eps=1e-5), LlamaRMSNorm(H, eps=1e-5), LlamaMLP(cfg)
+        how = "HF transformers LlamaRMSNorm / nn.Linear q,k,v,o / LlamaMLP, bf16 (the reference's non-TE path, train_fp8.py:118-124)"
+    except Exception as e:  # noqa: BLE001
+        kind = "port"
+
+        class _MLP(nn.Module):
+            def __init__(self):
+                super().__init__()
+                self.gate_proj, self.up_proj, self.down_proj = nn.Linear(H, I, bias=False), nn.Linear(H, I, bias=False), nn.Linear(I, H, bias=False)
+
+            def forward(self, x):
+                return self.down_proj(nn.functional.silu(self.gate_proj(x)) * self.up_proj(x))
+        ln1, ln2, mlp = nn.RMSNorm(H, eps=1e-5), nn.RMSNorm(H, eps=1e-5), _MLP()
+        how = f"torch bf16 modules (transformers unavailable: {str(e)[:60]})"
+    q, k, v, o = (nn.Linear(H, heads * hd, bias=False), nn.Linear(H, kv * hd, bias=False), nn.Linear(H, kv * hd, bias=False),
+                  nn.Linear(heads * hd, H, bias=False))
+    mods = nn.ModuleList([ln1, ln2, mlp, q, k, v, o]).to(torch.bfloat16)
+    x = torch.randn(1, tokens, H).bfloat16().requires_grad_(True)
+
+    def step():
+        h = x
+        y = ln1(h)
+        qq, kk, vv = q(y), k(y), v(y)
+        h = h + o(qq) + 0.0 * (kk.sum() + vv.sum())      # attention core = identity on the query slice (as in our arm); k, v still get gradients
+        h = h + mlp(ln2(h))
+        h.float().square().mean().backward()
+        x.grad = None
+        mods.zero_grad(set_to_none=True)
+
+    for _ in range(max(1, min(a.warmup, 2))):
+        step()
+    t0 = time.perf_counter()
+    for _ in range(a.steps):
+        step()
+    dt = (time.perf_counter() - t0) / a.steps
+    val = 6.0 * tokens * P / dt / 1e12
+    sample = f"{how}; 1 decoder layer's linear path of {a.model}, {tokens} tokens per step, fwd+bwd"
+    line = {"impl": "reference", "metric": METRIC, "value": val, "unit": UNIT, "n_gpus": a.gpus, "steps": a.steps, "warmup": a.warmup,
+            "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
+            "config": {"workload": workload_name(a, a.layers or L), "cpu_sample": sample},
+            "cpu_baseline": {"value": val, "unit": UNIT, "cores": cores, "kind": kind, "sample": sample},
+            "e2e": {"value": val, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------ our arm
+def main():
+    a = parse()
+    if a.impl == "reference":
+        reference_arm(a)
+        return
+    import torch
+    import torch.distributed as dist
+
+    import llm_fp8_b200 as te
+    from llm_fp8_b200 import _lib, dp
+    from llm_fp8_b200.layer import MODEL_SHAPES, LinearPathStack
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: llm_fp8_b200 has no CPU path (use --impl reference for the CPU arm)")
+    rank, world, local = dp.init_from_env()
+    dev = torch.device("cuda", local)
+    lib = _lib.load()
+    pk = peaks()
+
+    model = LinearPathStack(a.model, a.scenario, a.layers or None, device=dev)
+    L = model.n_layers
+    H = model.H
+    M = a.batch * a.seq
+    flops_step = model.linear_flops(M)                 # per rank
+    reducer = dp.GradAllReducer(model.parameters()) if world > 1 else None
+
+    g = torch.Generator(device=dev).manual_seed(1234 + rank)           # 42 + rank seeding in the reference: train_multi_gpu.py:1003
+    x_dev = torch.randn(a.batch, a.seq, H, device=dev, generator=g).bfloat16()
+    x_host = x_dev.cpu().pin_memory()
+    loss_host = torch.empty(1, dtype=torch.float32).pin_memory()
+
+    def step(x_in):
+        x = x_in.detach().requires_grad_(True)
+        y = model(x)
+        loss = y.float().square().mean()
+        loss.backward()
+        if reducer is not None:
+            reducer.finish()
+        return loss
+
+    def zero():
+        for p in model.parameters():
+            p.grad = None
+
+    def sync_all():
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize()
+
+    def timed(fn, steps):
+        sync_all()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        n0 = lib.llmfp8_launch_count()
+        e0.record()
+        for _ in range(steps):
+            fn()
+        e1.record()
+        sync_all()
+        ms = e0.elapsed_time(e1)
+        if world > 1:
+            t = torch.tensor([ms], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = t.item()
+        return ms / steps, (lib.llmfp8_launch_count() - n0) // steps
+
+    def resident_step():
+        step(x_dev)
+        zero()
+
+    x_stage = torch.empty_like(x_dev)
+
+    def e2e_step():
+        x_stage.copy_(x_host, non_blocking=True)                       # H2D from pinned memory, inside the timed region
+        loss = step(x_stage)
+        loss_host.copy_(loss.detach().reshape(1), non_blocking=False)  # D2H read of the step's result
+        zero()
+
+    # warm-up (also fills the delayed-scaling history enough for real scales)
+    for _ in range(max(a.warmup, 3)):
+        resident_step()
+    sampler = ClockSampler(local) if rank == 0 else None
+    ms_step, launches = timed(resident_step, a.steps)
+    e2e_step()
+    ms_e2e, _ = timed(e2e_step, a.steps)
+    clocks = sampler.stop() if sampler else None
+
+    value = world * flops_step / (ms_step * 1e-3) / 1e12
+    e2e_value = world * flops_step / (ms_e2e * 1e-3) / 1e12
+
+    # ---- roofline leg: every C-ABI launch of one more step bracketed by CUDA events on the launching stream
+    roof, roof_q, shares = None, None, None
+    if not a.no_roofline and rank == 0:
+        _lib.profile_start()
+        resident_step()
+        recs = _lib.profile_stop()
+        tot = sum(r[3] for r in recs) or 1e-9
+        by = {}
+        for n, u, w, ms in recs:
+            d = by.setdefault(n, {"unit": u, "work": 0.0, "ms": 0.0, "launches": 0})
+            d["work"] += w; d["ms"] += ms; d["launches"] += 1
+        shares = {n.replace("llmfp8_", ""): round(d["ms"] / tot, 4) for n, d in sorted(by.items(), key=lambda kv: -kv[1]["ms"])}
+        gname = "llmfp8_mxfp8_gemm" if a.scenario == "mxfp8" else "llmfp8_fp8_gemm"
+        traffic = None
+        tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tp):
+            traffic = json.load(open(tp))
+        if gname in by:
+            d = by[gname]
+            ach = d["work"] / (d["ms"] * 1e-3) / 1e12
+            peak = 2.0 * pk["bf16_sustained"]
+            roof = {"bound": "tensor", "kernel": gname.replace("llmfp8_", "") + " (fp8_gemm_kernel: tcgen05.mma, all fprop/dgrad/wgrad launches of the step)",
+                    "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
+                    "peak_note": f"2 x {pk['src']} sustained bf16 cuBLAS TFLOP/s (MEASURED_PEAKS.json has no FP8 figure; FP8 dense = 2 x bf16 on this part)",
+                    "frac_of_nominal_fp8_4500": ach / FP8_NOMINAL_TFLOPS, "frac_of_measured_bf16": ach / pk["bf16_sustained"],
+                    "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"], "share_of_step": d["ms"] / tot,
+                    "traffic": (traffic or {}).get(gname)}
+        qn = max((n for n in by if by[n]["unit"] == "byte"), key=lambda n: by[n]["ms"], default=None)
+        if qn:
+            d = by[qn]
+            ach = d["work"] / (d["ms"] * 1e-3) / 1e9
+            roof_q = {"bound": "hbm", "kernel": qn.replace("llmfp8_", ""), "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
+                      "peak_note": f"{pk['src']} copy bandwidth", "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
+                      "share_of_step": d["ms"] / tot, "traffic": (traffic or {}).get(qn)}
+
+    cpu = None
+    if rank == 0 and world == 1 and not a.no_cpu_baseline:
+        cpu = cpu_port_baseline(a, a.cpu_sample_tokens)
+
+    if rank == 0:
+        line = {
+            "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp8_e4m3" + ("+e8m0" if a.scenario == "mxfp8" else "/e5m2") + " (fp32 accumulate, bf16 out)",
+            "data": "synthetic",
+            "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
+                       "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,
+                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
+                       "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS},
+            "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
+            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
+            "cpu_baseline": cpu,
+        }
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -34,6 +34,8 @@ int llmfp8_abi_version(void);
 const char* llmfp8_last_error(void);
 /* number of SMs of the current device (cached) */
 int llmfp8_sm_count(void);
+/* number of kernels this library has launched in this process (monotonic; bench.py reports the per-step delta) */
+uint64_t llmfp8_launch_count(void);
 
 /* ---- per-tensor (DelayedScaling) quantise kernels ------------------------------------------------------------ */
 

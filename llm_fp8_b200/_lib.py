@@ -21,6 +21,7 @@ _PROTOTYPES = {
     "llmfp8_abi_version": [],
     "llmfp8_last_error": [],
     "llmfp8_sm_count": [],
+    "llmfp8_launch_count": [],
     "llmfp8_quant_cast_amax": [vp, vp, i64, i32, vp, vp, vp],
     "llmfp8_quant_cast_amax_bgrad": [vp, vp, i64, i64, i32, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_quant_fwd": [vp, vp, vp, vp, i64, i64, f32, i32, vp, vp, vp],
@@ -35,7 +36,7 @@ _PROTOTYPES = {
     "llmfp8_fp8_gemm": [vp, i64, i32, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp],
     "llmfp8_mxfp8_gemm": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, vp, i32, i32, vp],
 }
-_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64}
+_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64}
 EXPORTS = tuple(_PROTOTYPES)
 
 
@@ -43,7 +44,7 @@ def load():
     """Load the shared library (once).  Raises if it has not been built — there is no fallback path."""
     global _lib
     if _lib is not None:
-        return _lib
+        return _profiled if _profiled is not None else _lib
     with _lock:
         if _lib is None:
             if not os.path.exists(LIB_PATH):
@@ -59,6 +60,74 @@ def load():
                 raise RuntimeError("libllmfp8_b200.so ABI version mismatch")
             _lib = lib
     return _lib
+
+
+# ---------------------------------------------------------------------------------------------- per-call device timing
+# bench.py's roofline leg: while a profile is active every C-ABI call is bracketed by CUDA events on the current stream and
+# recorded with its algorithmic work (FLOPs for GEMMs, HBM bytes for the memory-bound kernels: SURVEY.md §8(d)).
+def _work(name: str, a):
+    if name == "llmfp8_fp8_gemm" or name == "llmfp8_mxfp8_gemm":
+        return "flop", 2.0 * a[11] * a[12] * a[13]
+    if name == "llmfp8_quant_cast_amax":
+        return "byte", 3.0 * a[2]
+    if name == "llmfp8_quant_cast_amax_bgrad":
+        return "byte", 3.0 * a[2] * a[3]
+    if name == "llmfp8_rmsnorm_quant_fwd":
+        return "byte", 3.0 * a[4] * a[5] + 4.0 * a[4]
+    if name == "llmfp8_rmsnorm_bwd":
+        return "byte", 6.0 * a[7] * a[8]
+    if name == "llmfp8_rmsnorm_rsigma":
+        return "byte", 2.0 * a[2] * a[3]
+    if name == "llmfp8_swiglu_quant_fwd":
+        return "byte", (6.0 if a[4] == 2 else 5.0) * a[2] * a[3]
+    if name == "llmfp8_dswiglu_quant_bwd":
+        return "byte", (10.0 if a[5] == 2 else 8.0) * a[3] * a[4]
+    if name == "llmfp8_mx_quantize":
+        rc = float(a[1]) * a[2]
+        return "byte", 2.0 * rc + (rc + rc / 32) * ((a[3] is not None) + (a[5] is not None))
+    return "none", 0.0
+
+
+class _Profiled:
+    """Proxy over the ctypes library that times every launch-bearing call with CUDA events."""
+
+    def __init__(self, lib, records):
+        self._lib, self._records = lib, records
+
+    def __getattr__(self, name):
+        fn = getattr(self._lib, name)
+        if name in ("llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
+                    "llmfp8_rmsnorm_bwd_ws_rows"):
+            return fn
+        import torch
+
+        def timed(*a):
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            rc = fn(*a)
+            e1.record()
+            unit, work = _work(name, a)
+            self._records.append((name, unit, work, e0, e1))
+            return rc
+        return timed
+
+
+_profiled = None
+
+
+def profile_start():
+    global _profiled
+    _profiled = _Profiled(load(), [])
+
+
+def profile_stop():
+    """-> list of (c_function, unit, algorithmic work, milliseconds); synchronises the device."""
+    global _profiled
+    import torch
+    torch.cuda.synchronize()
+    recs = [(n, u, w, e0.elapsed_time(e1)) for n, u, w, e0, e1 in _profiled._records]
+    _profiled = None
+    return recs
 
 
 def check(rc: int, what: str):

@@ -1,6 +1,7 @@
 // extern "C" surface of libllmfp8_b200.so (declared in include/llmfp8_b200.h) + process-wide plumbing:
 // thread-local error string, SM-count cache, TMA descriptor encoder resolved through the runtime.
 #include <cstdarg>
+#include <atomic>
 #include <cstdio>
 #include <mutex>
 
@@ -18,6 +19,9 @@ void set_error(const char* fmt, ...) {
     vsnprintf(g_err, sizeof g_err, fmt, ap);
     va_end(ap);
 }
+
+static std::atomic<unsigned long long> g_launches{0};
+void count_launch() { g_launches.fetch_add(1, std::memory_order_relaxed); }
 
 int sm_count() {
     static int cached[64] = {0};
@@ -92,6 +96,7 @@ extern "C" {
 int llmfp8_abi_version(void) { return LLMFP8_ABI_VERSION; }
 const char* llmfp8_last_error(void) { return g_err; }
 int llmfp8_sm_count(void) { return sm_count(); }
+uint64_t llmfp8_launch_count(void) { return g_launches.load(std::memory_order_relaxed); }
 
 int llmfp8_quant_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* scale, float* amax, void* stream) {
     return launch_cast_amax(x, q, n, fmt, scale, amax, S(stream));

@@ -1,0 +1,111 @@
+"""Data-parallel plumbing of the FP8 linear path: one process per GPU, tokens (M) sharded over ranks,
+weights replicated.  Only two exchanges exist on this path, both NCCL over NVLink:
+
+  * amax MAX all-reduce of the delayed-scaling pools — fp8.ScalePool.flush(), once per direction per step;
+  * weight-gradient all-reduce (each rank's dW = dY_local^T X_local is a partial sum over its tokens), launched per
+    parameter the moment autograd has produced it so it overlaps the rest of the backward pass.
+
+Mirrors what the reference gets from `DDP(model, gradient_as_bucket_view=True)` (train_multi_gpu.py:355-378) and its
+env-var rendezvous (train_multi_gpu.py:969-1006), without the DDP wrapper: no bucket copies — the wgrad GEMM's output
+tensor is the all-reduce buffer.
+"""
+from __future__ import annotations
+
+import os
+from typing import Iterable, List, Optional
+
+import torch
+import torch.distributed as dist
+
+
+def init_from_env(backend: Optional[str] = None):
+    """RANK / WORLD_SIZE / LOCAL_RANK / MASTER_ADDR / MASTER_PORT rendezvous (same contract as train_multi_gpu.py:972-976).
+    Returns (rank, world_size, local_rank); a no-op single-process setup when WORLD_SIZE is absent or 1."""
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world > 1 and not dist.is_initialized():
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        os.environ.setdefault("MASTER_PORT", "29500")
+        if backend is None:
+            backend = "nccl" if torch.cuda.is_available() else "gloo"
+        if backend == "nccl":
+            torch.cuda.set_device(local)
+            dist.init_process_group(backend, rank=rank, world_size=world, device_id=torch.device("cuda", local))
+        else:
+            dist.init_process_group(backend, rank=rank, world_size=world)
+    elif torch.cuda.is_available():
+        torch.cuda.set_device(local)
+    return rank, world, local
+
+
+def shard_tokens(global_batch: int, rank: int, world: int) -> range:
+    """Sequences [lo, hi) of the global batch that `rank` owns (contiguous, remainder spread over the first ranks)."""
+    base, rem = divmod(global_batch, world)
+    lo = rank * base + min(rank, rem)
+    return range(lo, lo + base + (1 if rank < rem else 0))
+
+
+class GradAllReducer:
+    """Averages parameter gradients over the data-parallel group, overlapped with backward.
+
+    Large gradients (>= `direct_numel` elements) are all-reduced in place, individually, as soon as their
+    post-accumulate hook fires (asynchronously, on NCCL's stream); small ones (norm weights, biases) are packed into one
+    flat buffer and reduced together in `finish()`.  Call `finish()` after `backward()`; it makes the current stream wait
+    for every outstanding reduction."""
+
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True):
+        self.group = group
+        self.world = dist.get_world_size(group) if dist.is_initialized() else 1
+        self.average = average
+        self.direct_numel = direct_numel
+        self._work: List = []
+        self._small: List[torch.nn.Parameter] = []
+        self._handles = []
+        self.bytes_reduced = 0
+        if self.world > 1:
+            for p in params:
+                if p.requires_grad:
+                    self._handles.append(p.register_post_accumulate_grad_hook(self._hook))
+
+    def _op(self):
+        # gloo has no AVG: sum, then scale in finish()
+        return dist.ReduceOp.AVG if (self.average and dist.get_backend(self.group) == "nccl") else dist.ReduceOp.SUM
+
+    def _hook(self, p: torch.nn.Parameter):
+        g = p.grad
+        if g is None:
+            return
+        if g.numel() >= self.direct_numel and g.is_contiguous():
+            self._work.append((dist.all_reduce(g, op=self._op(), group=self.group, async_op=True), g))
+            self.bytes_reduced += g.numel() * g.element_size()
+        else:
+            self._small.append(p)
+
+    def finish(self):
+        if self.world == 1:
+            return
+        post_scale = self.average and self._op() == dist.ReduceOp.SUM
+        if self._small:
+            grads = [p.grad for p in self._small]
+            flat = torch.cat([g.reshape(-1).float() for g in grads])
+            dist.all_reduce(flat, op=self._op(), group=self.group)
+            if post_scale:
+                flat /= self.world
+            off = 0
+            for g in grads:
+                n = g.numel()
+                g.copy_(flat[off:off + n].view_as(g))
+                off += n
+            self.bytes_reduced += flat.numel() * 4
+            self._small = []
+        for w, g in self._work:
+            w.wait()
+            if post_scale:
+                g /= self.world
+        self._work = []
+
+    def remove(self):
+        for h in self._handles:
+            h.remove()
+        self._handles = []
