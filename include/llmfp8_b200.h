@@ -92,6 +92,13 @@ int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
                     int out_fp32, int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, int accumulate,
                     int max_ctas, void* stream);
 
+/* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  Process-wide, not thread-safe. */
+void llmfp8_gemm_force_bn(int bn);
+/* likewise the CTA group: 1 = single-CTA kernel, 2 = CTA pairs (cta_group::2), 0 = automatic */
+void llmfp8_gemm_force_cg(int cg);
+/* experiments only (results become wrong): bit 0 skips the MX scale smem->TMEM copies, bit 1 the scale loads */
+void llmfp8_gemm_debug(int flags);
+
 /* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */
 int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
                       int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream);

@@ -72,6 +72,27 @@ int make_tensor_map_2d(CUtensorMap* map, const void* base, CUtensorMapDataType d
     return 0;
 }
 
+int make_tensor_map_3d(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int64_t d0, int64_t d1, int64_t d2, int64_t stride1_bytes,
+                       int64_t stride2_bytes, int b0, int b1, int b2) {
+    EncodeTiledFn fn = encode_fn();
+    if (!fn) {
+        set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
+        return -2;
+    }
+    cuuint64_t dims[3] = {static_cast<cuuint64_t>(d0), static_cast<cuuint64_t>(d1), static_cast<cuuint64_t>(d2)};
+    cuuint64_t strides[2] = {static_cast<cuuint64_t>(stride1_bytes), static_cast<cuuint64_t>(stride2_bytes)};
+    cuuint32_t box[3] = {static_cast<cuuint32_t>(b0), static_cast<cuuint32_t>(b1), static_cast<cuuint32_t>(b2)};
+    cuuint32_t estr[3] = {1, 1, 1};
+    CUresult r = fn(map, dtype, 3, const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE,
+                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) {
+        set_error("cuTensorMapEncodeTiled(3d) failed (%d): base=%p dims=(%lld,%lld,%lld) strides=(%lld,%lld) box=(%d,%d,%d)", (int)r, base, (long long)d0,
+                  (long long)d1, (long long)d2, (long long)stride1_bytes, (long long)stride2_bytes, b0, b1, b2);
+        return -3;
+    }
+    return 0;
+}
+
 // kernels (defined in the other translation units)
 int launch_cast_amax(const void*, void*, int64_t, int, const float*, float*, cudaStream_t);
 int launch_cast_amax_bgrad(const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
@@ -85,6 +106,9 @@ int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, 
 int launch_mx_quantize(const void*, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
 int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
                     const void*, const void*, const void*, int, int, cudaStream_t);
+void gemm_force_bn(int);
+void gemm_force_cg(int);
+void gemm_debug(int);
 
 }  // namespace llmfp8
 
@@ -142,6 +166,9 @@ int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     return launch_fp8_gemm(a, lda, a_fmt, a_mn, b, ldb, b_fmt, b_mn, d, ldd, out_fp32, M, N, K, a_scale_inv, b_scale_inv, nullptr, nullptr, bias,
                            accumulate, max_ctas, S(stream));
 }
+void llmfp8_gemm_force_bn(int bn) { gemm_force_bn(bn); }
+void llmfp8_gemm_force_cg(int cg) { gemm_force_cg(cg); }
+void llmfp8_gemm_debug(int flags) { gemm_debug(flags); }
 int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
                       int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream) {
     if (!sfa || !sfb) {

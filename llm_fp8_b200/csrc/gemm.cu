@@ -12,18 +12,33 @@
 // This is what TE does through cuBLASLt (tex.generic_gemm) for every Linear reached from te_llama.py:45-63.
 //
 // CTA = 6 warps: warp 0 TMA producer, warp 1 MMA issuer (+TMEM owner), warps 2..5 epilogue (one TMEM lane quadrant each).
-// Persistent over 128 x BN output tiles, grouped rasterisation so a wave's A/B panels stay L2-resident.
+// Persistent over (128*CG) x BN output tiles, grouped rasterisation so a wave's A/B panels stay L2-resident.
+// CG = 2 (the default for large problems) runs CTA PAIRS (2-CTA clusters, tcgen05 cta_group::2): each CTA of the pair stages its own
+// 128 rows of A and HALF of the B tile, the leader CTA issues one M=256 MMA that reads both halves, and each CTA keeps its
+// 128 x BN accumulator in its own TMEM.  Shared-memory traffic per MMA cycle drops from 96 B/clk (1-CTA 128x256) to 64 B/clk —
+// the 1-CTA kernel measured shared-memory bound (profiles/r01_*: BN sweep).
+// BN (the UMMA N) is a RUNTIME parameter in {128, 192, 256}: the host picks it per problem to minimise wave quantisation
+// (tiles / 148 CTAs), and MXFP8 uses BN <= 192 so that TWO accumulators (2 x 192 columns) plus the scale-factor columns fit the
+// 512 TMEM columns — the epilogue of tile t then overlaps the mainloop of tile t+1 for both kinds.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
 
 namespace llmfp8 {
 
-constexpr int BM = 128;          // tile rows  (UMMA M, cta_group::1)
+constexpr int BM = 128;          // tile rows per CTA (UMMA M = 128 * CG)
 constexpr int BK = 128;          // k elements per pipeline stage (= one 128 B swizzle row when K-major)
 constexpr int UMMA_K = 32;       // k per tcgen05.mma for 8-bit operands
-constexpr int GEMM_THREADS = 192;
-constexpr int GROUP_M = 16;
+constexpr int GEMM_THREADS = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quadrant)
+constexpr int EPI_WARPS = 8;
+constexpr int GROUP_M = 16;      // rasterisation group, in 128-row blocks
+constexpr int MAX_STAGES = 8;
+constexpr int SF_COL0 = 448;     // TMEM columns 448..511: four rotating scale-factor buffers of 16 columns (SFA 4 + SFB up to 12), so the
+constexpr int SF_BUFS = 4;       // smem->TMEM copy for k-block i+1 never waits for the MMAs of k-block i to finish reading theirs
+constexpr int SF_STAGE_BYTES = 3 * 512;   // per stage and CTA: 1 SFA tile + 2 SFB tiles
+constexpr int SMEM_BUDGET = 227 * 1024;
+constexpr int EPI_BUF_BYTES = 4096;          // one TMA-store box: 32 rows x 128 B
+constexpr int EPI_BYTES = EPI_WARPS * EPI_BUF_BYTES;
 
 struct GemmParams {
     void* d;                 // output, row-major [M, N], leading dimension ldd (elements)
@@ -34,139 +49,154 @@ struct GemmParams {
     const void* bias;           // bf16 [N] or null
     int accumulate;             // D += result
     int out_fp32;               // 0: bf16 output, 1: fp32 output
-    const uint8_t* sfa;         // MX only: swizzled E8M0 tiles, [ceil(M/128)][ceil(K/128)][512]
-    const uint8_t* sfb;         //          [ceil(N/128)][ceil(K/128)][512]
     uint32_t idesc;
+    int bn;                     // tile columns = UMMA N (128 | 192 | 256)
+    int b_rows_cta;             // B rows staged per CTA: bn / CG (K-major) or that rounded up to 128 (MN-major chunks)
+    int stages;                 // smem ring depth
+    int acc_stages;             // TMEM accumulator buffers (2, or 1 for MX with bn > 192)
+    int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads
 };
 
-template <int BN, int STAGES, bool MX>
-struct GemmSmem {
-    static constexpr int A_BYTES = BM * BK;
-    static constexpr int B_BYTES = BN * BK;
-    static constexpr int SF_BYTES = MX ? (512 + (BN / 128) * 512) : 0;
-    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int BAR_OFF = STAGES * (STAGE_BYTES + SF_BYTES);
-    static constexpr int TOTAL = BAR_OFF + 256 + 1024;   // + barriers + alignment slack
-};
+template <int CG>
+__device__ __forceinline__ void tma2d(const CUtensorMap* m, uint64_t* bar, uint32_t bar_leader, void* dst, int c0, int c1) {
+    if constexpr (CG == 1) ptx::tma_load_2d(m, bar, dst, c0, c1);
+    else ptx::tma_load_2d_cg2(m, bar_leader, dst, c0, c1);
+}
+template <int CG>
+__device__ __forceinline__ void tma3d(const CUtensorMap* m, uint64_t* bar, uint32_t bar_leader, void* dst, int c0, int c1, int c2) {
+    if constexpr (CG == 1) ptx::tma_load_3d(m, bar, dst, c0, c1, c2);
+    else ptx::tma_load_3d_cg2(m, bar_leader, dst, c0, c1, c2);
+}
 
-template <int BN, int STAGES, int ACC_STAGES, bool A_MN, bool B_MN, bool MX>
+template <int CG, bool A_MN, bool B_MN, bool MX>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const GemmParams p) {
-    using L = GemmSmem<BN, STAGES, MX>;
-    static_assert(BN % 128 == 0 && BN <= 256, "BN is 128 or 256");
-    constexpr int ACC_COLS = BN;
-    constexpr int SFA_COL = ACC_STAGES * ACC_COLS;
-    constexpr int SFB_COL = SFA_COL + 4;
+fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_sfa,
+                const __grid_constant__ CUtensorMap map_sfb, const __grid_constant__ CUtensorMap map_d, const GemmParams p) {
+    constexpr int A_BYTES = BM * BK;
+    constexpr int TM = BM * CG;                      // output rows per tile (per CTA pair when CG == 2)
     constexpr int TMEM_COLS = 512;
-    static_assert(!MX || SFB_COL + BN / 32 <= TMEM_COLS, "TMEM overflow");
+    const int BN = p.bn;
+    const int STAGES = p.stages, ACC_STAGES = p.acc_stages;
+    const int stage_bytes = A_BYTES + p.b_rows_cta * BK;
 
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-    uint8_t* sf_base = smem + STAGES * L::STAGE_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(smem + L::BAR_OFF);
-    uint64_t* empty_bar = full_bar + STAGES;
-    uint64_t* tmem_full = empty_bar + STAGES;
-    uint64_t* tmem_empty = tmem_full + ACC_STAGES;
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + ACC_STAGES);
+    uint8_t* epi_base = smem + STAGES * stage_bytes;          // 8 epilogue warps x 4 KB, 1024 B aligned (128B-swizzled TMA-store boxes)
+    uint8_t* sf_base = epi_base + EPI_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(sf_base + (MX ? STAGES * SF_STAGE_BYTES : 0));
+    uint64_t* empty_bar = full_bar + MAX_STAGES;
+    uint64_t* tmem_full = empty_bar + MAX_STAGES;
+    uint64_t* tmem_empty = tmem_full + 2;
+    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int num_m = (p.M + BM - 1) / BM, num_n = (p.N + BN - 1) / BN;
+    const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;    // 0 = leader (issues the MMAs)
+    const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
+    const int num_m = (p.M + TM - 1) / TM, num_n = (p.N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int num_kb = (p.K + BK - 1) / BK;
-    const int kb_tiles = num_kb;   // scale tiles along k (one 512 B tile per 128 k)
-    const int n_sf_tiles = (p.N + 127) / 128;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&map_a);
         ptx::prefetch_tensormap(&map_b);
+        if (MX) {
+            ptx::prefetch_tensormap(&map_sfa);
+            ptx::prefetch_tensormap(&map_sfb);
+        }
         for (int s = 0; s < STAGES; s++) {
             ptx::mbar_init(&full_bar[s], 1);
             ptx::mbar_init(&empty_bar[s], 1);
         }
         for (int s = 0; s < ACC_STAGES; s++) {
             ptx::mbar_init(&tmem_full[s], 1);
-            ptx::mbar_init(&tmem_empty[s], 4);
+            ptx::mbar_init(&tmem_empty[s], EPI_WARPS * CG);
         }
         ptx::fence_barrier_init();
     }
-    if (warp == 1) {
-        ptx::tmem_alloc(tmem_ptr_smem, TMEM_COLS);
-        ptx::tmem_relinquish();
-    }
+    if (warp == 1) ptx::tmem_alloc_cg<CG>(tmem_ptr_smem, TMEM_COLS);
     ptx::tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 2) ptx::cluster_sync();      // peer barriers must be initialised before anything signals them
+    else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
 
+    constexpr int GROUP = GROUP_M / CG;
     auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {
-        const int per_group = GROUP_M * num_n;
+        const int per_group = GROUP * num_n;
         const int group = tile / per_group;
-        const int first_m = group * GROUP_M;
-        const int gsize = (num_m - first_m) < GROUP_M ? (num_m - first_m) : GROUP_M;
+        const int first_m = group * GROUP;
+        const int gsize = (num_m - first_m) < GROUP ? (num_m - first_m) : GROUP;
         const int in_group = tile - group * per_group;
         m_blk = first_m + in_group % gsize;
         n_blk = in_group / gsize;
     };
 
     if (warp == 0) {
-        // ================================ TMA producer
-        if (lane == 0) {
+        // ================================ TMA producer (one per CTA: own A rows, own part of B, own scale tiles)
+        {
             int stage = 0, phase = 0;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            const int b_chunks = p.b_rows_cta >> 7;     // MN-major B: 128-column chunks (the last one may over-fetch)
+            const int bn_cta = BN / CG;
+            const bool sf_load = MX && !(p.debug & 2);
+            const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? SF_STAGE_BYTES : 0));
+            for (int tile = unit; tile < num_tiles; tile += num_units) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
-                const int m0 = m_blk * BM, n0 = n_blk * BN;
+                const int m0 = m_blk * TM + rank * BM, n0 = n_blk * BN, nb0 = n0 + rank * bn_cta;
                 for (int kb = 0; kb < num_kb; kb++) {
-                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);
-                    uint8_t* sa = smem + stage * L::STAGE_BYTES;
-                    uint8_t* sb = sa + L::A_BYTES;
-                    // scale tiles past the last 128-row tile of B do not exist in memory: skip them (their columns are never stored)
-                    int sfb_tiles = BN / 128;
-                    if (MX && (n_blk * (BN / 128) + sfb_tiles) > n_sf_tiles) sfb_tiles = n_sf_tiles - n_blk * (BN / 128);
-                    ptx::mbar_arrive_expect_tx(&full_bar[stage], L::STAGE_BYTES + (MX ? 512 + 512 * sfb_tiles : 0));
+                    ptx::mbar_wait(&empty_bar[stage], phase ^ 1);     // all lanes poll (keeps the warp converged and its values uniform)
+                    if (ptx::elect_one_sync()) {
+                    uint8_t* sa = smem + stage * stage_bytes;
+                    uint8_t* sb = sa + A_BYTES;
+                    uint64_t* fb = &full_bar[stage];
+                    const uint32_t fb_leader = CG == 2 ? ptx::mapa(ptx::smem_u32(fb), 0) : 0u;
+                    if (rank == 0) ptx::mbar_arrive_expect_tx(fb, tx_bytes);
                     const int k0 = kb * BK;
-                    if (!A_MN) ptx::tma_load_2d(&map_a, &full_bar[stage], sa, k0, m0);
-                    else ptx::tma_load_2d(&map_a, &full_bar[stage], sa, m0, k0);
+                    if (!A_MN) tma2d<CG>(&map_a, fb, fb_leader, sa, k0, m0);
+                    else tma2d<CG>(&map_a, fb, fb_leader, sa, m0, k0);
                     if (!B_MN) {
-                        ptx::tma_load_2d(&map_b, &full_bar[stage], sb, k0, n0);
+                        tma2d<CG>(&map_b, fb, fb_leader, sb, k0, nb0);
                     } else {
-#pragma unroll
-                        for (int j = 0; j < BN / 128; j++) ptx::tma_load_2d(&map_b, &full_bar[stage], sb + j * (128 * BK), n0 + j * 128, k0);
+                        for (int j = 0; j < b_chunks; j++) tma2d<CG>(&map_b, fb, fb_leader, sb + j * (128 * BK), nb0 + j * 128, k0);
                     }
-                    if (MX) {
-                        uint8_t* ssf = sf_base + stage * L::SF_BYTES;
-                        ptx::bulk_load_1d(ssf, p.sfa + (static_cast<int64_t>(m_blk) * kb_tiles + kb) * 512, 512, &full_bar[stage]);
-#pragma unroll
-                        for (int j = 0; j < BN / 128; j++)
-                            if (j < sfb_tiles)
-                                ptx::bulk_load_1d(ssf + 512 + j * 512,
-                                                  p.sfb + (static_cast<int64_t>(n_blk * (BN / 128) + j) * kb_tiles + kb) * 512, 512, &full_bar[stage]);
+                    if (sf_load) {
+                        uint8_t* ssf = sf_base + stage * SF_STAGE_BYTES;
+                        tma3d<CG>(&map_sfa, fb, fb_leader, ssf, 0, kb, m_blk * CG + static_cast<int>(rank));
+                        tma3d<CG>(&map_sfb, fb, fb_leader, ssf + 512, 0, kb, n0 >> 7);     // two 128-row scale tiles (zero-filled past the end)
                     }
+                    }
+                    __syncwarp();
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
             }
         }
     } else if (warp == 1) {
-        // ================================ MMA issuer (one thread)
-        if (lane == 0) {
-            int stage = 0, phase = 0, acc = 0, acc_phase = 0;
+        // ================================ MMA issuer (one thread of the leader CTA)
+        if (rank == 0) {
+            int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
             constexpr uint32_t A_LBO = A_MN ? (BK * 128) : 16, B_LBO = B_MN ? (BK * 128) : 16;
             constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K * 128) : UMMA_K;
-            for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+            for (int tile = unit; tile < num_tiles; tile += num_units) {
+                int m_blk, n_blk;
+                tile_coords(tile, m_blk, n_blk);
+                // MX: the scale of column n lives in TMEM column (sf buffer) + 4 + (n - 128 * (n0 / 128)) / 32: a tile that starts 64 rows
+                // into a 128-row scale tile (BN = 192) skips the leading 32-row groups by advancing the column address
+                const uint32_t sfb_off = 4 + (((n_blk * BN) & 127) >> 5);
                 ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 ptx::tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * ACC_COLS;
+                const uint32_t tmem_d = tmem_base + acc * BN;
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
-                    const uint32_t sa = ptx::smem_u32(smem + stage * L::STAGE_BYTES);
-                    const uint32_t sb = sa + L::A_BYTES;
-                    if (MX) {
-                        const uint32_t ssf = ptx::smem_u32(sf_base + stage * L::SF_BYTES);
-                        ptx::tc_cp_32x128b_warpx4(tmem_base + SFA_COL, ptx::make_smem_desc(ssf, 0, 128, 0));
-#pragma unroll
-                        for (int j = 0; j < BN / 128; j++)
-                            ptx::tc_cp_32x128b_warpx4(tmem_base + SFB_COL + 4 * j, ptx::make_smem_desc(ssf + 512 + j * 512, 0, 128, 0));
+                    const uint32_t sa = ptx::smem_u32(smem + stage * stage_bytes);
+                    const uint32_t sb = sa + A_BYTES;
+                    const uint32_t tmem_sf = tmem_base + SF_COL0 + 16 * sfi;
+                    if (ptx::elect_one_sync()) {
+                    if (MX && !((p.debug & 1) && (kb | tile) != 0)) {
+                        const uint32_t ssf = ptx::smem_u32(sf_base + stage * SF_STAGE_BYTES);
+                        ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf, ptx::make_smem_desc(ssf, 0, 128, 0));
+                        ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf + 4, ptx::make_smem_desc(ssf + 512, 0, 128, 0));
+                        ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf + 8, ptx::make_smem_desc(ssf + 1024, 0, 128, 0));
                     }
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; k++) {
@@ -175,34 +205,116 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         const uint32_t accum = (kb | k) != 0;
                         if (MX) {
                             const uint32_t idesc = p.idesc | (static_cast<uint32_t>(k) << 4) | (static_cast<uint32_t>(k) << 29);
-                            ptx::mma_mxf8f6f4(tmem_d, da, db, idesc, accum, tmem_base + SFA_COL, tmem_base + SFB_COL);
+                            ptx::mma_mxf8f6f4_cg<CG>(tmem_d, da, db, idesc, accum, tmem_sf, tmem_sf + sfb_off);
                         } else {
-                            ptx::mma_f8f6f4(tmem_d, da, db, p.idesc, accum);
+                            ptx::mma_f8f6f4_cg<CG>(tmem_d, da, db, p.idesc, accum);
                         }
                     }
-                    ptx::tc_commit(&empty_bar[stage]);          // smem slot reusable once these MMAs have read it
+                    ptx::tc_commit_cg<CG>(&empty_bar[stage]);   // smem slot (in both CTAs) reusable once these MMAs have read it
+                    }
+                    __syncwarp();
+                    if (MX && !(p.debug & 4)) sfi = (sfi + 1) & (SF_BUFS - 1);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                ptx::tc_commit(&tmem_full[acc]);                // accumulator complete -> epilogue
+                if (ptx::elect_one_sync()) ptx::tc_commit_cg<CG>(&tmem_full[acc]);         // accumulator complete -> epilogue warps of both CTAs
+                __syncwarp();
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
             }
         }
     } else {
         // ================================ epilogue: TMEM -> registers -> (alpha, bias, accumulate) -> global
-        const int quad = warp & 3;
+        const int quad = warp & 3;            // TMEM lane quadrant this warp may read
+        const int half = (warp - 2) >> 2;     // two warps per quadrant split the column chunks (even / odd)
         int acc = 0, acc_phase = 0;
         float alpha = 1.0f;
         if (!MX) alpha = __fmul_rn(__ldg(p.a_scale_inv), __ldg(p.b_scale_inv));
-        for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const uint32_t tmem_empty_leader = CG == 2 ? ptx::mapa(ptx::smem_u32(&tmem_empty[0]), 0) : 0u;
+        auto release_acc = [&](int a) {
+            ptx::tc_fence_before();
+            __syncwarp();
+            if (lane == 0) {
+                if constexpr (CG == 2) ptx::mbar_arrive_cluster(tmem_empty_leader + a * 8);
+                else ptx::mbar_arrive(&tmem_empty[a]);
+            }
+        };
+        if (!p.accumulate) {
+            // ---- staged path: 32 x 128 B boxes (64 bf16 or 32 fp32 columns) -> swizzled smem -> TMA store (coalesced, clips partial tiles)
+            uint8_t* stg = epi_base + (warp - 2) * EPI_BUF_BYTES;
+            const int ccols = p.out_fp32 ? 32 : 64;
+            const int nchunks = BN / ccols;
+            if (lane == 0) ptx::prefetch_tensormap(&map_d);
+            for (int tile = unit; tile < num_tiles; tile += num_units) {
+                int m_blk, n_blk;
+                tile_coords(tile, m_blk, n_blk);
+                const int row0 = m_blk * TM + static_cast<int>(rank) * BM + quad * 32;
+                const int n0 = n_blk * BN;
+                ptx::mbar_wait(&tmem_full[acc], acc_phase);
+                ptx::tc_fence_after();
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+#pragma unroll 1
+                for (int c = half; c < nchunks; c += 2) {
+                    const int col = n0 + c * ccols;
+                    uint32_t r0[32], r1[32];
+                    ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
+                    if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
+                    if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
+                    ptx::tmem_ld_wait();
+                    if (c + 2 >= nchunks) release_acc(acc);           // this warp's share of the accumulator is in registers
+                    else __syncwarp();
+                    uint8_t* sbuf = stg + lane * 128;
+                    const uint32_t sw = lane & 7;
+                    if (col < p.N) {
+                        if (p.out_fp32) {
+#pragma unroll
+                            for (int g = 0; g < 8; g++) {
+                                float4 o = make_float4(__uint_as_float(r0[g * 4]) * alpha, __uint_as_float(r0[g * 4 + 1]) * alpha,
+                                                       __uint_as_float(r0[g * 4 + 2]) * alpha, __uint_as_float(r0[g * 4 + 3]) * alpha);
+                                if (p.bias && col + g * 4 < p.N) {
+                                    const uint2 bv = __ldg(reinterpret_cast<const uint2*>(static_cast<const uint16_t*>(p.bias) + col + g * 4));
+                                    o.x += bf16lo(bv.x); o.y += bf16hi(bv.x); o.z += bf16lo(bv.y); o.w += bf16hi(bv.y);
+                                }
+                                *reinterpret_cast<float4*>(sbuf + ((g ^ sw) << 4)) = o;
+                            }
+                        } else {
+#pragma unroll
+                            for (int g = 0; g < 8; g++) {
+                                float v[8];
+#pragma unroll
+                                for (int j = 0; j < 8; j++) v[j] = __uint_as_float(g < 4 ? r0[g * 8 + j] : r1[(g - 4) * 8 + j]) * alpha;
+                                if (p.bias && col + g * 8 < p.N) {
+                                    float bf[8];
+                                    unpack8(__ldg(reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.bias) + col + g * 8)), bf);
+#pragma unroll
+                                    for (int j = 0; j < 8; j++) v[j] += bf[j];
+                                }
+                                uint4 o;
+                                o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
+                                o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
+                                *reinterpret_cast<uint4*>(sbuf + ((g ^ sw) << 4)) = o;
+                            }
+                        }
+                        ptx::fence_proxy_async();
+                        __syncwarp();
+                        if (lane == 0) {
+                            ptx::tma_store_2d(&map_d, stg, col, row0);
+                            ptx::tma_store_commit();
+                        }
+                    }
+                }
+                if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+            }
+            if (lane == 0) ptx::tma_store_wait<0>();
+        } else
+        for (int tile = unit; tile < num_tiles; tile += num_units) {
             int m_blk, n_blk;
             tile_coords(tile, m_blk, n_blk);
-            const int row = m_blk * BM + quad * 32 + lane;
+            const int row = m_blk * TM + static_cast<int>(rank) * BM + quad * 32 + lane;
             const int n0 = n_blk * BN;
             ptx::mbar_wait(&tmem_full[acc], acc_phase);
             ptx::tc_fence_after();
-            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * ACC_COLS;
+            const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; c++) {
+            for (int c = half; c < (BN >> 5); c += 2) {
                 uint32_t r[32];
                 ptx::tmem_ld_32x32b_x32(taddr + c * 32, r);
                 ptx::tmem_ld_wait();
@@ -260,34 +372,99 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             }
             ptx::tc_fence_before();
             __syncwarp();
-            if (lane == 0) ptx::mbar_arrive(&tmem_empty[acc]);
+            if (lane == 0) {
+                if constexpr (CG == 2) ptx::mbar_arrive_cluster(tmem_empty_leader + acc * 8);
+                else ptx::mbar_arrive(&tmem_empty[acc]);
+            }
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
         }
     }
 
     ptx::tc_fence_before();
-    __syncthreads();
+    if constexpr (CG == 2) ptx::cluster_sync();      // neither CTA may retire while its peer can still signal its barriers / read its smem
+    else __syncthreads();
     if (warp == 1) {
         ptx::tc_fence_after();
-        ptx::tmem_dealloc(tmem_base, TMEM_COLS);
+        ptx::tmem_dealloc_cg<CG>(tmem_base, TMEM_COLS);
     }
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-template <int BN, int STAGES, int ACC_STAGES, bool A_MN, bool B_MN, bool MX>
-static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const GemmParams& p, int grid, cudaStream_t stream) {
-    using L = GemmSmem<BN, STAGES, MX>;
-    auto kern = fp8_gemm_kernel<BN, STAGES, ACC_STAGES, A_MN, B_MN, MX>;
+static int g_bn_override = 0;     // tuning / tests only (llmfp8_gemm_force_bn / llmfp8_gemm_force_cg)
+static int g_cg_override = 0;
+static int g_debug = 0;
+void gemm_debug(int d) { g_debug = d; }
+void gemm_force_bn(int bn) { g_bn_override = bn; }
+void gemm_force_cg(int cg) { g_cg_override = cg; }
+
+template <int CG, bool A_MN, bool B_MN, bool MX>
+static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
+                          const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX>;
     static bool configured = false;   // benign race: the attribute call is idempotent
     if (!configured) {
-        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, L::TOTAL);
-        if (e != cudaSuccess) { set_error("fp8_gemm: smem attribute (%d B): %s", L::TOTAL, cudaGetErrorString(e)); return (int)e; }
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
+        if (e != cudaSuccess) { set_error("fp8_gemm: smem attribute (%d B): %s", SMEM_BUDGET, cudaGetErrorString(e)); return (int)e; }
         configured = true;
     }
-    kern<<<grid, GEMM_THREADS, L::TOTAL, stream>>>(ma, mb, p);
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3(grid);
+    cfg.blockDim = dim3(GEMM_THREADS);
+    cfg.dynamicSmemBytes = smem_bytes;
+    cfg.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = CG;
+    attr[0].val.clusterDim.y = 1;
+    attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, msa, msb, md, p);
+    if (e != cudaSuccess) { set_error("fp8_gemm: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     LLMFP8_LAUNCH_CHECK("fp8_gemm");
     return 0;
 }
+
+template <int CG>
+static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb,
+                    const CUtensorMap& md, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+    if (!mx) {
+        if (!a_mn && !b_mn) return launch_variant<CG, false, false, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        if (!a_mn && b_mn) return launch_variant<CG, false, true, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        if (a_mn && b_mn) return launch_variant<CG, true, true, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        return launch_variant<CG, true, false, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    }
+    if (!a_mn && !b_mn) return launch_variant<CG, false, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    if (!a_mn && b_mn) return launch_variant<CG, false, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    return launch_variant<CG, true, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+}
+
+// Tile width: minimise (waves x per-tile cost).  Narrow tiles cost more per column: their shared-memory traffic per MMA cycle is
+// higher (measured, profiles/r01_gemm_bn_sweep: 192 runs 10-25 % and 128 30-35 % below 256 in the 1-CTA kernel).
+static int pick_bn(int M, int N, bool mx, bool b_mn, int cg, int units) {
+    if (g_bn_override) return g_bn_override;
+    const int cand[3] = {256, 192, 128};
+    const double eff1[3] = {1.0, b_mn ? 0.76 : 0.88, 0.70};
+    const double eff2[3] = {1.0, 0.90, 0.80};
+    int best = 0;
+    double best_cost = 1e300;
+    const int num_m = (M + BM * cg - 1) / (BM * cg);
+    for (int i = 0; i < 3; i++) {
+        const int bn = cand[i];
+        if (cg == 2 && bn == 192 && b_mn) continue;           // 96 MN-major columns per CTA is not a whole swizzle chunk
+        if (bn > 128 && N <= bn - 64) continue;               // do not pad tiny N
+        double e = cg == 2 ? eff2[i] : eff1[i];
+        if (mx) e *= bn > 192 ? 0.95 : 0.85;                   // MX at 256 has one accumulator (epilogue exposed); narrower tiles pay more scale copies per FLOP
+        const long tiles = static_cast<long>(num_m) * ((N + bn - 1) / bn);
+        const long waves = (tiles + units - 1) / units;
+        const double cost = static_cast<double>(waves) * bn / e;
+        if (cost < best_cost) { best_cost = cost; best = bn; }
+    }
+    return best ? best : 128;
+}
+
+int make_tensor_map_3d(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int64_t d0, int64_t d1, int64_t d2, int64_t stride1_bytes,
+                       int64_t stride2_bytes, int b0, int b1, int b2);
 
 // a: fp8 bytes. !a_mn: stored [M, K] (lda = row pitch in bytes >= K);  a_mn: stored [K, M] (lda >= M).  Same for b with N.
 int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd,
@@ -304,38 +481,62 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     LLMFP8_REQUIRE(!mx || (reinterpret_cast<uintptr_t>(sfa) | reinterpret_cast<uintptr_t>(sfb)) % 16 == 0, "fp8_gemm: scale tensors must be 16 B aligned");
     LLMFP8_REQUIRE(!(mx && (a_mn != b_mn) && a_mn), "fp8_gemm: operand layout combination (A MN-major, B K-major) is not built");
 
-    CUtensorMap ma, mb;
-    int rc;
-    // K-major operand [rows, K]: inner dim = K, box = {128 k, tile rows}.   MN-major operand [K, rows]: inner = rows, box = {128 rows, 128 k}.
-    constexpr int BN = 256;
-    if (!a_mn) rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, K, M, lda, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
-    else rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, K, lda, 128, BK, CU_TENSOR_MAP_SWIZZLE_128B);
-    if (rc) return rc;
-    if (!b_mn) rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, K, N, ldb, BK, BN, CU_TENSOR_MAP_SWIZZLE_128B);
-    else rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, K, ldb, 128, BK, CU_TENSOR_MAP_SWIZZLE_128B);
-    if (rc) return rc;
+    int grid = sm_count();
+    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+    // CTA pairs for anything with at least one full wave of 256-row tiles; the single-CTA kernel for small problems
+    int cg = g_cg_override ? g_cg_override : ((M > BM && grid >= 2 && static_cast<long>((M + 255) / 256) * ((N + 255) / 256) >= grid / 4) ? 2 : 1);
+    if (grid < 2) cg = 1;
+    if (cg == 2) grid &= ~1;
+    const int units = grid / cg;
+    const int BN = pick_bn(M, N, mx, b_mn != 0, cg, units);
+    LLMFP8_REQUIRE(BN == 128 || BN == 192 || BN == 256, "fp8_gemm: tile width %d is not built", BN);
+    LLMFP8_REQUIRE(cg == 1 || cg == 2, "fp8_gemm: cta group %d is not built", cg);
 
     GemmParams p;
     p.d = d; p.ldd = ldd; p.M = M; p.N = N; p.K = K;
     p.a_scale_inv = a_scale_inv; p.b_scale_inv = b_scale_inv; p.bias = bias; p.accumulate = accumulate; p.out_fp32 = out_fp32;
-    p.sfa = static_cast<const uint8_t*>(sfa); p.sfb = static_cast<const uint8_t*>(sfb);
-    p.idesc = mx ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM, BN, 0, 0) : ptx::make_idesc_f8(a_fmt, b_fmt, a_mn, b_mn, BM, BN);
+    p.idesc = mx ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN, 0, 0) : ptx::make_idesc_f8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN);
+    p.bn = BN;
+    p.debug = g_debug;
+    const int bn_cta = BN / cg;
+    p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
+    p.acc_stages = (mx && BN > 192) ? 1 : 2;
+    const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
+    const int fixed = 1024 /*alignment slack*/ + 256 /*barriers*/ + EPI_BYTES /*epilogue staging*/;
+    int stages = (SMEM_BUDGET - fixed) / stage_bytes;
+    if (stages > MAX_STAGES) stages = MAX_STAGES;
+    p.stages = stages;
+    const int smem_bytes = fixed + stages * stage_bytes;
 
-    const int num_tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-    int grid = sm_count();
-    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
-    if (num_tiles < grid) grid = num_tiles;
-
-    constexpr int ST = 4;
-    if (!mx) {
-        if (!a_mn && !b_mn) return launch_variant<BN, ST, 2, false, false, false>(ma, mb, p, grid, stream);
-        if (!a_mn && b_mn) return launch_variant<BN, ST, 2, false, true, false>(ma, mb, p, grid, stream);
-        if (a_mn && b_mn) return launch_variant<BN, ST, 2, true, true, false>(ma, mb, p, grid, stream);
-        return launch_variant<BN, ST, 2, true, false, false>(ma, mb, p, grid, stream);
+    CUtensorMap ma, mb, msa, msb, md;
+    int rc;
+    // output boxes of 32 rows x 128 B for the staged epilogue
+    if (out_fp32) rc = make_tensor_map_2d(&md, d, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, N, M, ldd * 4, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
+    else rc = make_tensor_map_2d(&md, d, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, N, M, ldd * 2, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    // K-major operand [rows, K]: inner dim = K, box = {128 k, tile rows}.   MN-major operand [K, rows]: inner = rows, box = {128 rows, 128 k}.
+    if (!a_mn) rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, K, M, lda, BK, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+    else rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, M, K, lda, 128, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    if (!b_mn) rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, K, N, ldb, BK, bn_cta, CU_TENSOR_MAP_SWIZZLE_128B);
+    else rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, N, K, ldb, 128, BK, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    if (mx) {
+        // swizzled E8M0 tensors viewed as [row tiles][k tiles][128 x u32]: one 512 B tile per (128 rows, 128 k)
+        const int64_t kt = (K + 127) / 128;
+        rc = make_tensor_map_3d(&msa, sfa, CU_TENSOR_MAP_DATA_TYPE_UINT32, 128, kt, (M + 127) / 128, 512, 512 * kt, 128, 1, 1);
+        if (rc) return rc;
+        rc = make_tensor_map_3d(&msb, sfb, CU_TENSOR_MAP_DATA_TYPE_UINT32, 128, kt, (N + 127) / 128, 512, 512 * kt, 128, 1, 2);
+        if (rc) return rc;
+    } else {
+        msa = ma;
+        msb = mb;
     }
-    if (!a_mn && !b_mn) return launch_variant<BN, ST, 1, false, false, true>(ma, mb, p, grid, stream);
-    if (!a_mn && b_mn) return launch_variant<BN, ST, 1, false, true, true>(ma, mb, p, grid, stream);
-    return launch_variant<BN, ST, 1, true, true, true>(ma, mb, p, grid, stream);
+
+    const int num_tiles = ((M + BM * cg - 1) / (BM * cg)) * ((N + BN - 1) / BN);
+    if (num_tiles * cg < grid) grid = num_tiles * cg;
+    if (cg == 2) return dispatch<2>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    return dispatch<1>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
 }
 
 }  // namespace llmfp8

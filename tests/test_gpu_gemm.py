@@ -165,3 +165,82 @@ def test_mxfp8_quantize_then_gemm_roundtrip():
     check(dx, ref_matmul(deq_row(dyq, T, N), deq_col(wq, N, K).t()))
     dw = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, xq.col, xq.sf_col, True, N, K, T)
     check(dw, ref_matmul(deq_col(dyq, T, N).t(), deq_col(xq, T, K).t()))
+
+
+# ------------------------------------------------------------------------------------------------ tile-width / CTA-group variants
+@pytest.fixture()
+def force():
+    from llm_fp8_b200 import _lib
+    lib = _lib.load()
+
+    def f(bn, cg):
+        lib.llmfp8_gemm_force_bn(bn)
+        lib.llmfp8_gemm_force_cg(cg)
+    yield f
+    lib.llmfp8_gemm_force_bn(0)
+    lib.llmfp8_gemm_force_cg(0)
+
+
+VARIANTS = [(1, 128), (1, 192), (1, 256), (2, 128), (2, 256)]
+
+
+@pytest.mark.parametrize("cg,bn", VARIANTS + [(2, 192)])
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True)])
+def test_fp8_gemm_forced_variant(cg, bn, a_mn, b_mn, force):
+    """Every (CTA group, tile width) the host heuristic may pick, on a shape with partial tiles in M and N and > 148 tiles."""
+    ops = _ops()
+    if cg == 2 and bn == 192 and b_mn:
+        pytest.skip("not built: 96 MN-major columns per CTA")
+    force(bn, cg)
+    M, N, K = 2000, 3280, 640
+    a, b = rand_fp8((M, K), E4M3, 31), rand_fp8((N, K), E5M2, 32, 0.5)
+    want = ref_matmul(a.float(), b.float())
+    A = qt(ops, a.t().contiguous() if a_mn else a, E4M3, 1.0)
+    B = qt(ops, b.t().contiguous() if b_mn else b, E5M2, 1.0)
+    check(ops.fp8_gemm(A, a_mn, B, b_mn, M, N, K), want)
+    g = torch.Generator().manual_seed(5)
+    bias = torch.randn(N, generator=g).bfloat16()
+    got = ops.fp8_gemm(A, a_mn, B, b_mn, M, N, K, bias=bias.cuda(), out_dtype=torch.float32)
+    check(got, want + bias.float(), tol=1e-5)
+
+
+@pytest.mark.parametrize("cg,bn", VARIANTS + [(2, 192)])
+def test_mxfp8_gemm_forced_variant(cg, bn, force):
+    """MX with every variant: 192 starts every other tile 64 rows into a 128-row scale tile (TMEM column offset 2)."""
+    ops = _ops()
+    force(bn, cg)
+    M, N, K = 640, 1600, 1024
+    x, w = mx_operands(M, K, 41), mx_operands(N, K, 42)
+    xq, xe = fo.mx_quantize_rowwise(x)
+    wq, we = fo.mx_quantize_rowwise(w)
+    want = ref_matmul(fo.mx_dequantize_rowwise(xq, xe), fo.mx_dequantize_rowwise(wq, we))
+    got = ops.mxfp8_gemm(xq.view(torch.uint8).cuda(), fo.swizzle_sf(xe).cuda(), False, wq.view(torch.uint8).cuda(), fo.swizzle_sf(we).cuda(), False, M, N, K)
+    check(got, want)
+    if cg == 2 and bn == 192:
+        return
+    # dgrad / wgrad layouts at the same width
+    bt = w.t().contiguous()
+    bq, be = fo.mx_quantize_colwise(bt)
+    want = ref_matmul(fo.mx_dequantize_rowwise(xq, xe), fo.mx_dequantize_colwise(bq, be).t())
+    got = ops.mxfp8_gemm(xq.view(torch.uint8).cuda(), fo.swizzle_sf(xe).cuda(), False, bq.view(torch.uint8).cuda(), fo.swizzle_sf(be).cuda(), True, M, N, K)
+    check(got, want)
+    at = x.t().contiguous()
+    aq2, ae2 = fo.mx_quantize_colwise(at)
+    want = ref_matmul(fo.mx_dequantize_colwise(aq2, ae2).t(), fo.mx_dequantize_colwise(bq, be).t())
+    got = ops.mxfp8_gemm(aq2.view(torch.uint8).cuda(), fo.swizzle_sf(ae2).cuda(), True, bq.view(torch.uint8).cuda(), fo.swizzle_sf(be).cuda(), True, M, N, K)
+    check(got, want)
+
+
+@pytest.mark.parametrize("cg", [1, 2])
+def test_gemm_full_shape_checksum(cg, force):
+    """Full Llama-3.1-8B fc2 fprop shape through both kernels: identical results (same fp32 accumulation order per output) and a
+    column-sum identity against an fp64 reference: sum_m Y[m, :] == (sum_m A[m, :]) B^T."""
+    ops = _ops()
+    force(0, cg)
+    M, N, K = 6144, 4096, 14336
+    a, b = rand_fp8((M, K), E4M3, 51), rand_fp8((N, K), E4M3, 52)
+    y = ops.fp8_gemm(qt(ops, a, E4M3, 1.0), False, qt(ops, b, E4M3, 1.0), False, M, N, K, out_dtype=torch.float32)
+    colsum = y.double().sum(0).cpu()
+    want = (a.double().cuda().sum(0, keepdim=True) @ b.double().cuda().t()).cpu()[0]
+    err = (colsum - want).abs().max().item() / want.abs().max().item()
+    assert err < 1e-5, err

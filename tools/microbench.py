@@ -67,14 +67,28 @@ def main():
     ap.add_argument("--model", default="llama8b")
     ap.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "micro.jsonl"))
     ap.add_argument("--only", default="")
+    ap.add_argument("--bn", type=int, default=0, help="force the GEMM tile width (0 = heuristic)")
+    ap.add_argument("--cg", type=int, default=0, help="force the CTA group (1 | 2; 0 = heuristic)")
+    ap.add_argument("--debug", type=int, default=0)
+    ap.add_argument("--tag", default="")
     args = ap.parse_args()
     H, I, QKV, M = SHAPES[args.model]
     hbm, bf16_tf, src = peaks()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     out = open(args.out, "a")
 
+    from llm_fp8_b200 import _lib
+    _lib.load().llmfp8_gemm_force_bn(args.bn)
+    _lib.load().llmfp8_gemm_force_cg(args.cg)
+    _lib.load().llmfp8_gemm_debug(args.debug)
+
     def emit(rec):
         rec["model"] = args.model
+        rec["bn"] = args.bn
+        rec["cg"] = args.cg
+        rec["debug"] = args.debug
+        if args.tag:
+            rec["tag"] = args.tag
         print(json.dumps(rec), flush=True)
         out.write(json.dumps(rec) + "\n")
         out.flush()
@@ -148,6 +162,11 @@ def main():
                 rec("ref torch._scaled_mm e4m3 (cuBLASLt)", lambda: torch._scaled_mm(x8, w8.t(), scale_a=one, scale_b=one, out_dtype=torch.bfloat16))
             except Exception as e:  # noqa: BLE001
                 emit({"kernel": f"ref torch._scaled_mm {lname}", "error": str(e)[:200]})
+            try:   # cuBLASLt block-scaled MXFP8 (comparison point)
+                e8 = torch.float8_e8m0fnu
+                rec("ref torch._scaled_mm mxfp8 (cuBLASLt)", lambda: torch._scaled_mm(x8, w8.t(), scale_a=sfx.view(e8), scale_b=sfw.view(e8), out_dtype=torch.bfloat16))
+            except Exception as e:  # noqa: BLE001
+                emit({"kernel": f"ref torch._scaled_mm mxfp8 {lname}", "error": str(e)[:300]})
             del xq, wq, dyq, xb, wb
     out.close()
 
