@@ -1,0 +1,86 @@
+"""Data-parallel host logic (llm_fp8_b200/dp.py) on CPU: two gloo ranks, tokens sharded over ranks, the gradient all-reducer
+must reproduce the single-process gradient of the concatenated batch, and the amax exchange must leave both ranks with the
+same maximum (what fp8.ScalePool.flush does with NCCL on the GPU box).  Mirrors the reference's DDP contract
+(train_multi_gpu.py:355-378: averaged gradients; :969-1006: env-var rendezvous)."""
+import os
+import socket
+
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from llm_fp8_b200 import dp
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _model(seed=0):
+    torch.manual_seed(seed)
+    # one weight above the reducer's direct threshold (in-place all-reduce) and small ones (packed bucket)
+    return torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.SiLU(), torch.nn.Linear(128, 64, bias=True))
+
+
+def _batch():
+    g = torch.Generator().manual_seed(5)
+    return torch.randn(6, 10, 64, generator=g)          # 6 sequences of 10 tokens
+
+
+def _worker(rank, world, port, out):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    r, w, _ = dp.init_from_env(backend="gloo")
+    assert (r, w) == (rank, world) and dist.get_backend() == "gloo"
+    model = _model()
+    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128)
+    x = _batch()
+    mine = dp.shard_tokens(x.shape[0], rank, world)
+    xs = x[mine.start:mine.stop]
+    # mean loss over the LOCAL shard; DDP semantics average over ranks, which equals the global mean for equal shards
+    model(xs).square().mean().backward()
+    reducer.finish()
+    grads = [p.grad.clone() for p in model.parameters()]
+    # amax exchange: element-wise MAX of a flat fp32 buffer
+    amax = torch.tensor([1.0 + rank, 5.0 - rank, 0.0])
+    dist.all_reduce(amax, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        torch.save({"grads": grads, "amax": amax, "bytes": reducer.bytes_reduced}, out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_grad_allreduce_matches_single_process(tmp_path):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    model = _model()
+    model(_batch()).square().mean().backward()
+    for g, p in zip(got["grads"], model.parameters()):
+        assert torch.allclose(g, p.grad, rtol=1e-5, atol=1e-7)
+    assert torch.equal(got["amax"], torch.tensor([2.0, 5.0, 0.0]))
+    assert got["bytes"] > 0
+
+
+def test_shard_tokens_partitions_exactly():
+    for gb in (1, 7, 12, 16):
+        for world in (1, 2, 3, 4, 8):
+            seen = []
+            for r in range(world):
+                seen += list(dp.shard_tokens(gb, r, world))
+            assert seen == list(range(gb))
+            sizes = [len(dp.shard_tokens(gb, r, world)) for r in range(world)]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def test_single_process_is_a_noop(monkeypatch):
+    for k in ("RANK", "WORLD_SIZE", "LOCAL_RANK"):
+        monkeypatch.delenv(k, raising=False)
+    assert dp.init_from_env()[:2] == (0, 1)
+    m = _model()
+    red = dp.GradAllReducer(m.parameters())
+    m(_batch()).sum().backward()
+    red.finish()
+    assert red.bytes_reduced == 0
