@@ -9,39 +9,34 @@
 namespace llmfp8 {
 
 // ------------------------------------------------------------------------------------------- K2
-// Each thread owns groups of 16 elements: two 16 B loads in, one 16 B store out; UNROLL groups in flight.
+// Each thread owns UNROLL units of 8 elements (one 16 B load, one 8 B store), a warp's units contiguous in memory so every request
+// covers whole 32 B sectors exactly once; all UNROLL loads are issued before the first use.
 template <int FMT, int UNROLL>
-__global__ void __launch_bounds__(256) cast_amax_kernel(const uint4* __restrict__ x, uint4* __restrict__ q, int64_t ngroups,
+__global__ void __launch_bounds__(256) cast_amax_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t nunits,
                                                         const float* __restrict__ scale_ptr, float* __restrict__ amax) {
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
+    const f32x2 scale2 = pk2(scale, scale);
     float m = 0.f;
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
-    for (int64_t g0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; g0 < ngroups; g0 += stride * UNROLL) {
-        uint4 v[UNROLL][2];
+    const int64_t base = static_cast<int64_t>(blockIdx.x) * (256 * UNROLL) + threadIdx.x;
+    uint4 v[UNROLL];
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const int64_t g = g0 + u * stride;
-            if (g < ngroups) {
-                v[u][0] = ldg_stream(x + 2 * g);
-                v[u][1] = ldg_stream(x + 2 * g + 1);
-            }
-        }
+    for (int u = 0; u < UNROLL; u++)
+        if (base + u * 256 < nunits) v[u] = ldg_stream(x + base + u * 256);
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const int64_t g = g0 + u * stride;
-            if (g < ngroups) {
-                float f[8];
-                uint4 o;
-                unpack8(v[u][0], f);
-                m = amax8(f, m);
-                uint2 a = quant8<FMT>(f, scale);
-                unpack8(v[u][1], f);
-                m = amax8(f, m);
-                uint2 b = quant8<FMT>(f, scale);
-                o.x = a.x; o.y = a.y; o.z = b.x; o.w = b.y;
-                q[g] = o;
+    for (int u = 0; u < UNROLL; u++) {
+        if (base + u * 256 < nunits) {
+            float f[8];
+            unpack8(v[u], f);
+            uint32_t h[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                m = fmaxf(m, fmaxf(fabsf(f[2 * k]), fabsf(f[2 * k + 1])));
+                float lo, hi;
+                upk2(mul2(pk2(f[2 * k], f[2 * k + 1]), scale2), lo, hi);
+                h[k] = cvt_fp8x2<FMT>(lo, hi);
             }
+            q[base + u * 256] = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
         }
     }
     if (amax) block_amax_to_global(m, red, amax);
@@ -52,15 +47,15 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
     LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) % 16 == 0, "cast_amax: pointers must be 16 B aligned");
     LLMFP8_REQUIRE(fmt == FMT_E4M3 || fmt == FMT_E5M2, "cast_amax: bad fp8 format %d", fmt);
     if (n == 0) return 0;
-    const int64_t ngroups = n / 16;
-    constexpr int UNROLL = 4;
-    int64_t want = (ngroups + 256 * UNROLL - 1) / (256 * UNROLL);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    const int grid = static_cast<int>(want < cap ? want : cap);
+    const int64_t nunits = n / 8;
+    constexpr int UNROLL = 8;
+    const int64_t want = (nunits + 256 * UNROLL - 1) / (256 * UNROLL);
+    LLMFP8_REQUIRE(want < (int64_t(1) << 31), "cast_amax: tensor too large (%lld elements)", (long long)n);
+    const int grid = static_cast<int>(want);
     if (fmt == FMT_E4M3)
-        cast_amax_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint4*>(q), ngroups, scale, amax);
+        cast_amax_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
     else
-        cast_amax_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint4*>(q), ngroups, scale, amax);
+        cast_amax_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
     LLMFP8_LAUNCH_CHECK("cast_amax");
     return 0;
 }

@@ -11,6 +11,16 @@ namespace llmfp8 {
 
 constexpr int RMS_T = 128;
 
+// Persistent row kernels run exactly one wave: grid = resident CTAs per SM (occupancy query) x SMs.  A grid of 1.1-1.4 waves
+// costs a whole extra wave (measured: rmsnorm_bwd 592 CTAs on 444 slots ran at 36-40 % of HBM bandwidth).
+template <typename K>
+static int resident_grid(K kern, int threads, int64_t M) {
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, threads, 0) != cudaSuccess || per_sm < 1) per_sm = 1;
+    const int64_t cap = static_cast<int64_t>(sm_count()) * per_sm;
+    return static_cast<int>(M < cap ? M : cap);
+}
+
 template <int NIT>
 __device__ __forceinline__ float rms_row_rsigma(const uint4 (&v)[NIT], int t, int nchunk, int H, float eps, float* red /*[4]*/) {
     float acc = 0.f;
@@ -81,6 +91,7 @@ static int dispatch_rms_fwd(int nit, int grid, cudaStream_t s, const uint4* x, c
                             const float* scale, float* amax) {
 #define RMS_CASE(N)                                                                                              \
     case N:                                                                                                      \
+        grid = resident_grid(rmsnorm_fwd_kernel<FMT, N, OUT_MODE>, RMS_T, M);                                    \
         rmsnorm_fwd_kernel<FMT, N, OUT_MODE><<<grid, RMS_T, 0, s>>>(x, g, q, rs, M, H, eps, scale, amax);        \
         break;
     switch (nit) {
@@ -124,72 +135,107 @@ int launch_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, fl
 
 // ------------------------------------------------------------------------------------------- K5
 // dx = rs * (dy*g - xhat * mean(dy*g*xhat)),  dgamma = sum_rows dy * xhat   (xhat = x * rs), fp32 math.
+// 256 threads per row (two 16 B chunks per thread at H = 4096); the NEXT row's x / dy are loaded before the current row is
+// reduced, so a CTA always has one row of loads in flight while it computes (the one-row-at-a-time version measured 40 % of HBM).
+constexpr int RB_T = 256;
 template <int NIT>
-__global__ void __launch_bounds__(RMS_T) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
-                                                            const float* __restrict__ rsigma, uint4* __restrict__ dx, float* __restrict__ dgamma_part,
-                                                            int64_t M, int H) {
-    __shared__ float red[2][4];
+__global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
+                                                           const float* __restrict__ rsigma, uint4* __restrict__ dx, float* __restrict__ dgamma_part,
+                                                           int64_t M, int H) {
+    __shared__ float red[2][RB_T / 32];
     const int t = threadIdx.x;
     const int nchunk = H / 8;
-    float dg[NIT][8];
-    uint4 g[NIT];
+    // per thread: NIT chunks of 8 columns; gamma and the dgamma partial sums stay in registers as packed fp32 pairs
+    f32x2 dg[NIT][4], g2[NIT][4];
 #pragma unroll
     for (int it = 0; it < NIT; it++) {
+        float gf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (it * RB_T + t < nchunk) unpack8(__ldg(gamma + it * RB_T + t), gf);
 #pragma unroll
-        for (int j = 0; j < 8; j++) dg[it][j] = 0.f;
-        if (it * RMS_T + t < nchunk) g[it] = __ldg(gamma + it * RMS_T + t);
+        for (int k = 0; k < 4; k++) {
+            dg[it][k] = pk2(0.f, 0.f);
+            g2[it][k] = pk2(gf[2 * k], gf[2 * k + 1]);
+        }
     }
-    int par = 0;
-    for (int64_t row = blockIdx.x; row < M; row += gridDim.x, par ^= 1) {
-        uint4 vx[NIT], vdy[NIT];
+    uint4 nx[NIT], ndy[NIT];
+    float nrs = 0.f;
+    int64_t row = blockIdx.x;
+    if (row < M) {
 #pragma unroll
         for (int it = 0; it < NIT; it++)
-            if (it * RMS_T + t < nchunk) {
-                vx[it] = ldg_stream(x + row * nchunk + it * RMS_T + t);
-                vdy[it] = ldg_stream(dy + row * nchunk + it * RMS_T + t);
+            if (it * RB_T + t < nchunk) {
+                nx[it] = ldg_stream(x + row * nchunk + it * RB_T + t);
+                ndy[it] = ldg_stream(dy + row * nchunk + it * RB_T + t);
             }
-        const float rs = rsigma[row];
-        float dot = 0.f;
+        nrs = rsigma[row];
+    }
+    const float inv_h = 1.0f / static_cast<float>(H);
+    int par = 0;
+    for (; row < M; row += gridDim.x, par ^= 1) {
+        const float rs = nrs;
+        const f32x2 rs2 = pk2(rs, rs);
+        f32x2 xh[NIT][4], tg[NIT][4];       // xhat = x * rs ; tg = dy * gamma
+        f32x2 dot2 = pk2(0.f, 0.f);
 #pragma unroll
         for (int it = 0; it < NIT; it++)
-            if (it * RMS_T + t < nchunk) {
-                float fx[8], fdy[8], fg[8];
-                unpack8(vx[it], fx);
-                unpack8(vdy[it], fdy);
-                unpack8(g[it], fg);
+            if (it * RB_T + t < nchunk) {
+                float fx[8], fdy[8];
+                unpack8(nx[it], fx);
+                unpack8(ndy[it], fdy);
 #pragma unroll
-                for (int j = 0; j < 8; j++) {
-                    const float xh = fx[j] * rs;
-                    dot = fmaf(fdy[j] * fg[j], xh, dot);
-                    dg[it][j] = fmaf(fdy[j], xh, dg[it][j]);
+                for (int k = 0; k < 4; k++) {
+                    const f32x2 dy2 = pk2(fdy[2 * k], fdy[2 * k + 1]);
+                    xh[it][k] = mul2(pk2(fx[2 * k], fx[2 * k + 1]), rs2);
+                    tg[it][k] = mul2(dy2, g2[it][k]);
+                    dot2 = fma2(tg[it][k], xh[it][k], dot2);
+                    dg[it][k] = fma2(dy2, xh[it][k], dg[it][k]);
                 }
             }
-        dot = warp_sum(dot);
+        // the next row's loads go out before this row's reduction and stores
+        const int64_t nrow = row + gridDim.x;
+        if (nrow < M) {
+#pragma unroll
+            for (int it = 0; it < NIT; it++)
+                if (it * RB_T + t < nchunk) {
+                    nx[it] = ldg_stream(x + nrow * nchunk + it * RB_T + t);
+                    ndy[it] = ldg_stream(dy + nrow * nchunk + it * RB_T + t);
+                }
+            nrs = rsigma[nrow];
+        }
+        float d0, d1;
+        upk2(dot2, d0, d1);
+        const float dot = warp_sum(d0 + d1);
         if ((t & 31) == 0) red[par][t >> 5] = dot;
         __syncthreads();
-        const float c = (red[par][0] + red[par][1] + red[par][2] + red[par][3]) / static_cast<float>(H);
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < RB_T / 32; w++) tot += red[par][w];
+        // dx = rs * tg - (rs * c) * xhat
+        const float nc = -(rs * (tot * inv_h));
+        const f32x2 nc2 = pk2(nc, nc);
 #pragma unroll
         for (int it = 0; it < NIT; it++)
-            if (it * RMS_T + t < nchunk) {
-                float fx[8], fdy[8], fg[8], o[8];
-                unpack8(vx[it], fx);
-                unpack8(vdy[it], fdy);
-                unpack8(g[it], fg);
+            if (it * RB_T + t < nchunk) {
+                uint32_t o[4];
 #pragma unroll
-                for (int j = 0; j < 8; j++) o[j] = rs * (fdy[j] * fg[j] - (fx[j] * rs) * c);
-                uint4 ov;
-                ov.x = pack_bf16x2(o[0], o[1]); ov.y = pack_bf16x2(o[2], o[3]);
-                ov.z = pack_bf16x2(o[4], o[5]); ov.w = pack_bf16x2(o[6], o[7]);
-                dx[row * nchunk + it * RMS_T + t] = ov;
+                for (int k = 0; k < 4; k++) {
+                    float lo, hi;
+                    upk2(fma2(xh[it][k], nc2, mul2(tg[it][k], rs2)), lo, hi);
+                    o[k] = pack_bf16x2(lo, hi);
+                }
+                dx[row * nchunk + it * RB_T + t] = make_uint4(o[0], o[1], o[2], o[3]);
             }
     }
     float* out = dgamma_part + static_cast<int64_t>(blockIdx.x) * H;
 #pragma unroll
     for (int it = 0; it < NIT; it++)
-        if (it * RMS_T + t < nchunk) {
-            float4* o4 = reinterpret_cast<float4*>(out + (it * RMS_T + t) * 8);
-            o4[0] = make_float4(dg[it][0], dg[it][1], dg[it][2], dg[it][3]);
-            o4[1] = make_float4(dg[it][4], dg[it][5], dg[it][6], dg[it][7]);
+        if (it * RB_T + t < nchunk) {
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 4; k++) upk2(dg[it][k], v[2 * k], v[2 * k + 1]);
+            float4* o4 = reinterpret_cast<float4*>(out + (it * RB_T + t) * 8);
+            o4[0] = make_float4(v[0], v[1], v[2], v[3]);
+            o4[1] = make_float4(v[4], v[5], v[6], v[7]);
         }
 }
 
@@ -202,25 +248,27 @@ __global__ void colreduce_bf16_kernel(const float* __restrict__ part, int nparts
 }
 
 int rmsnorm_bwd_grid(int64_t M) {
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 3;
+    const int64_t cap = static_cast<int64_t>(sm_count()) * 4;
     return static_cast<int>(M < cap ? M : cap);
 }
 
-// ws: fp32 [rmsnorm_bwd_grid(M) * H]
+// ws: fp32 [rmsnorm_bwd_grid(M) * H] (an upper bound of the grid actually launched)
 int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma_bf16, float* ws,
                        int64_t M, int64_t H, cudaStream_t stream) {
     LLMFP8_REQUIRE(H % 8 == 0 && H > 0 && H <= 8192, "rmsnorm_bwd: hidden size %lld must be a multiple of 8 and <= 8192", (long long)H);
     LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gamma) | reinterpret_cast<uintptr_t>(dx) |
                     reinterpret_cast<uintptr_t>(ws)) % 16 == 0, "rmsnorm_bwd: misaligned pointers");
     if (M == 0) return 0;
-    const int nit = static_cast<int>((H / 8 + RMS_T - 1) / RMS_T);
-    const int grid = rmsnorm_bwd_grid(M);
+    const int nit = static_cast<int>((H / 8 + RB_T - 1) / RB_T);
+    int grid = 0;
 #define RMSB_CASE(N)                                                                                                                           \
     case N:                                                                                                                                    \
-        rmsnorm_bwd_kernel<N><<<grid, RMS_T, 0, stream>>>((const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (uint4*)dx, ws, M, (int)H); \
+        grid = resident_grid(rmsnorm_bwd_kernel<N>, RB_T, M);                                                                                  \
+        if (grid > rmsnorm_bwd_grid(M)) grid = rmsnorm_bwd_grid(M);                                                                            \
+        rmsnorm_bwd_kernel<N><<<grid, RB_T, 0, stream>>>((const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (uint4*)dx, ws, M, (int)H); \
         break;
     switch (nit) {
-        RMSB_CASE(1) RMSB_CASE(2) RMSB_CASE(3) RMSB_CASE(4) RMSB_CASE(5) RMSB_CASE(6) RMSB_CASE(7) RMSB_CASE(8)
+        RMSB_CASE(1) RMSB_CASE(2) RMSB_CASE(3) RMSB_CASE(4)
         default: set_error("rmsnorm_bwd: hidden size too large"); return -1;
     }
 #undef RMSB_CASE

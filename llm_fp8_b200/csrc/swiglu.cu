@@ -3,50 +3,87 @@
 //   K3b dswiglu_quant_bwd  : da bf16 [M,I], fc1_out bf16 [M,2I] -> fp8 [M,2I] (dgate | dup), amax, dbias[2I]  (8*M*I bytes)
 // Replaces TE's swiglu / dswiglu (+cast, +dbias) inside LayerNormMLP(activation="swiglu") (te_llama.py:58-63);
 // gate rows come first (te_llama.py:225-233).  exp/sigmoid are the pinned oracle versions (oracle_c.c: orc_expf).
+#include <cstdlib>
 #include "common.cuh"
 
 namespace llmfp8 {
 
 constexpr int FMT_BF16 = 2;   // unquantised bf16 output (feeds the MXFP8 block quantiser)
 
-// One thread: 8 gate + 8 up values -> 8 fp8 bytes.
+// 8 packed results -> 8 fp8 bytes (scale multiply separately rounded, as the oracle does) / amax / bf16
+template <int FMT>
+__device__ __forceinline__ uint2 quant8_p(const f32x2 (&a)[4], f32x2 scale2) {
+    uint32_t h[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        float lo, hi;
+        upk2(mul2(a[j], scale2), lo, hi);
+        h[j] = cvt_fp8x2<FMT>(lo, hi);
+    }
+    return make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
+}
+__device__ __forceinline__ float amax8_p(const f32x2 (&a)[4], float m) {
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        float lo, hi;
+        upk2(a[j], lo, hi);
+        m = fmaxf(m, fmaxf(fabsf(lo), fabsf(hi)));
+    }
+    return m;
+}
+__device__ __forceinline__ uint4 bf16x8_p(const f32x2 (&a)[4]) {
+    uint32_t o[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+        float lo, hi;
+        upk2(a[j], lo, hi);
+        o[j] = pack_bf16x2(lo, hi);
+    }
+    return make_uint4(o[0], o[1], o[2], o[3]);
+}
+
+// One thread: UNROLL units of (8 gate + 8 up values -> 8 outputs), all loads of the batch issued before the first use.
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) swiglu_quant_kernel(const uint4* __restrict__ fc1, uint2* __restrict__ q, int64_t M, int64_t ivec /* I/8 */,
                                                            const float* __restrict__ scale_ptr, float* __restrict__ amax) {
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
-    const int64_t total = M * ivec;
-    const int64_t stride = static_cast<int64_t>(gridDim.x) * blockDim.x;
+    const f32x2 scale2 = pk2(scale, scale);
+    const uint32_t total = static_cast<uint32_t>(M * ivec), iv = static_cast<uint32_t>(ivec);    // host guarantees < 2^31
+    const uint32_t base = blockIdx.x * (256u * UNROLL) + threadIdx.x;
     float m = 0.f;
-    for (int64_t i0 = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x; i0 < total; i0 += stride * UNROLL) {
-        uint4 vg[UNROLL], vu[UNROLL];
+    uint4 vg[UNROLL], vu[UNROLL];
+    {
+        uint32_t row = base / iv, c = base - row * iv;       // one division per thread; later units advance (row, c) by 256 columns
 #pragma unroll
         for (int u = 0; u < UNROLL; u++) {
-            const int64_t i = i0 + u * stride;
-            if (i < total) {
-                const int64_t row = i / ivec, c = i - row * ivec;
-                vg[u] = ldg_stream(fc1 + row * 2 * ivec + c);
-                vu[u] = ldg_stream(fc1 + row * 2 * ivec + ivec + c);
+            if (base + u * 256u < total) {
+                const uint4* p = fc1 + static_cast<int64_t>(row) * 2 * iv + c;
+                vg[u] = ldg_stream(p);
+                vu[u] = ldg_stream(p + iv);
             }
+            c += 256u;
+            while (c >= iv) { c -= iv; row++; }
         }
+    }
 #pragma unroll
-        for (int u = 0; u < UNROLL; u++) {
-            const int64_t i = i0 + u * stride;
-            if (i < total) {
-                float g[8], up[8], a[8];
-                unpack8(vg[u], g);
-                unpack8(vu[u], up);
+    for (int u = 0; u < UNROLL; u++) {
+        const uint32_t i = base + u * 256u;
+        if (i < total) {
+            float g[8], up[8];
+            unpack8(vg[u], g);
+            unpack8(vu[u], up);
+            f32x2 a[4];
 #pragma unroll
-                for (int j = 0; j < 8; j++) a[j] = __fmul_rn(__fmul_rn(g[j], sigmoid_pinned(g[j])), up[j]);
-                if constexpr (FMT == FMT_BF16) {
-                    uint4 o;
-                    o.x = pack_bf16x2(a[0], a[1]); o.y = pack_bf16x2(a[2], a[3]);
-                    o.z = pack_bf16x2(a[4], a[5]); o.w = pack_bf16x2(a[6], a[7]);
-                    reinterpret_cast<uint4*>(q)[i] = o;
-                } else {
-                    m = amax8(a, m);
-                    q[i] = quant8<FMT>(a, scale);
-                }
+            for (int j = 0; j < 4; j++) {
+                const f32x2 sig = sigmoid2_pinned(g[2 * j], g[2 * j + 1]);
+                a[j] = mul2(mul2(pk2(g[2 * j], g[2 * j + 1]), sig), pk2(up[2 * j], up[2 * j + 1]));
+            }
+            if constexpr (FMT == FMT_BF16) {
+                reinterpret_cast<uint4*>(q)[i] = bf16x8_p(a);
+            } else {
+                m = amax8_p(a, m);
+                q[i] = quant8_p<FMT>(a, scale2);
             }
         }
     }
@@ -59,11 +96,11 @@ int launch_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, 
     LLMFP8_REQUIRE(fmt == FMT_E4M3 || fmt == FMT_E5M2 || fmt == FMT_BF16, "swiglu_quant_fwd: bad output format %d", fmt);
     LLMFP8_REQUIRE(fmt != FMT_BF16 || reinterpret_cast<uintptr_t>(q) % 16 == 0, "swiglu_quant_fwd: misaligned bf16 output");
     if (M == 0 || I == 0) return 0;
-    constexpr int UNROLL = 2;
+    constexpr int UNROLL = 4;
     const int64_t total = M * (I / 8);
-    int64_t want = (total + 256 * UNROLL - 1) / (256 * UNROLL);
-    const int64_t cap = static_cast<int64_t>(sm_count()) * 8;
-    const int grid = static_cast<int>(want < cap ? want : cap);
+    const int64_t want = (total + 256 * UNROLL - 1) / (256 * UNROLL);
+    LLMFP8_REQUIRE(total < (int64_t(1) << 31), "swiglu_quant_fwd: problem too large (%lld x %lld)", (long long)M, (long long)I);
+    const int grid = static_cast<int>(want);
     if (fmt == FMT_E4M3)
         swiglu_quant_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>((const uint4*)fc1_out, (uint2*)q, M, I / 8, scale, amax);
     else if (fmt == FMT_E5M2)
@@ -76,8 +113,8 @@ int launch_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, 
 
 // Backward.  CTA = 32 column-vectors x 8 row lanes over a 256-column strip of I (so 256 dgate + 256 dup columns).
 constexpr int DS_CV = 32, DS_RL = 8, DS_COLS = DS_CV * 8;
-template <int FMT>
-__global__ void __launch_bounds__(256) dswiglu_quant_kernel(const uint4* __restrict__ da, const uint4* __restrict__ fc1, uint2* __restrict__ q,
+template <int FMT, int UN, int MINB>
+__global__ void __launch_bounds__(256, MINB) dswiglu_quant_kernel(const uint4* __restrict__ da, const uint4* __restrict__ fc1, uint2* __restrict__ q,
                                                             int64_t M, int64_t I, int64_t rows_per_cta, const float* __restrict__ scale_ptr,
                                                             float* __restrict__ amax, float* __restrict__ dbias_ws /* [2I] or null */) {
     __shared__ float red[8];
@@ -89,53 +126,54 @@ __global__ void __launch_bounds__(256) dswiglu_quant_kernel(const uint4* __restr
     const int64_t r_begin = static_cast<int64_t>(blockIdx.y) * rows_per_cta;
     const int64_t r_end = r_begin + rows_per_cta < M ? r_begin + rows_per_cta : M;
     float m = 0.f;
-    float sg[8], su[8];
+    const f32x2 one2 = pk2(1.0f, 1.0f), scale2 = pk2(scale, scale);
+    f32x2 sg[4], su[4];
 #pragma unroll
-    for (int j = 0; j < 8; j++) sg[j] = su[j] = 0.f;
+    for (int j = 0; j < 4; j++) sg[j] = su[j] = pk2(0.f, 0.f);
     if (col0 < I) {
-        constexpr int UN = 2;
-        for (int64_t r0 = r_begin + rl; r0 < r_end; r0 += DS_RL * UN) {
+        const uint4* pda = da + r_begin * ivec + col0 / 8;
+        const uint4* pfc = fc1 + r_begin * 2 * ivec + col0 / 8;
+        uint2* pq = q + r_begin * 2 * ivec + col0 / 8;
+        const int nrows = static_cast<int>(r_end - r_begin);
+        for (int r0 = rl; r0 < nrows; r0 += DS_RL * UN) {
             uint4 vda[UN], vg[UN], vu[UN];
 #pragma unroll
             for (int u = 0; u < UN; u++) {
-                const int64_t r = r0 + u * DS_RL;
-                if (r < r_end) {
-                    vda[u] = ldg_stream(da + r * ivec + col0 / 8);
-                    vg[u] = ldg_stream(fc1 + r * 2 * ivec + col0 / 8);
-                    vu[u] = ldg_stream(fc1 + r * 2 * ivec + ivec + col0 / 8);
+                const int r = r0 + u * DS_RL;
+                if (r < nrows) {
+                    vda[u] = ldg_stream(pda + r * ivec);
+                    vg[u] = ldg_stream(pfc + r * 2 * ivec);
+                    vu[u] = ldg_stream(pfc + r * 2 * ivec + ivec);
                 }
             }
 #pragma unroll
             for (int u = 0; u < UN; u++) {
-                const int64_t r = r0 + u * DS_RL;
-                if (r < r_end) {
-                    float dy[8], g[8], up[8], dg[8], du[8];
+                const int r = r0 + u * DS_RL;
+                if (r < nrows) {
+                    float dy[8], g[8], up[8];
                     unpack8(vda[u], dy);
                     unpack8(vg[u], g);
                     unpack8(vu[u], up);
+                    f32x2 dg[4], du[4];
 #pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        const float sig = sigmoid_pinned(g[j]);
-                        const float tt = __fmaf_rn(g[j], __fsub_rn(1.0f, sig), 1.0f);
-                        const float dsilu = __fmul_rn(sig, tt);
-                        dg[j] = __fmul_rn(__fmul_rn(dy[j], up[j]), dsilu);
-                        du[j] = __fmul_rn(dy[j], __fmul_rn(g[j], sig));
-                        sg[j] += dg[j];
-                        su[j] += du[j];
+                    for (int j = 0; j < 4; j++) {
+                        const f32x2 g2 = pk2(g[2 * j], g[2 * j + 1]), u2 = pk2(up[2 * j], up[2 * j + 1]), dy2 = pk2(dy[2 * j], dy[2 * j + 1]);
+                        const f32x2 sig = sigmoid2_pinned(g[2 * j], g[2 * j + 1]);
+                        const f32x2 tt = fma2(g2, sub2(one2, sig), one2);
+                        const f32x2 dsilu = mul2(sig, tt);
+                        dg[j] = mul2(mul2(dy2, u2), dsilu);
+                        du[j] = mul2(dy2, mul2(g2, sig));
+                        sg[j] = add2(dg[j], sg[j]);
+                        su[j] = add2(du[j], su[j]);
                     }
                     if constexpr (FMT == FMT_BF16) {
-                        uint4 o;
-                        o.x = pack_bf16x2(dg[0], dg[1]); o.y = pack_bf16x2(dg[2], dg[3]);
-                        o.z = pack_bf16x2(dg[4], dg[5]); o.w = pack_bf16x2(dg[6], dg[7]);
-                        reinterpret_cast<uint4*>(q)[r * 2 * ivec + col0 / 8] = o;
-                        o.x = pack_bf16x2(du[0], du[1]); o.y = pack_bf16x2(du[2], du[3]);
-                        o.z = pack_bf16x2(du[4], du[5]); o.w = pack_bf16x2(du[6], du[7]);
-                        reinterpret_cast<uint4*>(q)[r * 2 * ivec + ivec + col0 / 8] = o;
+                        reinterpret_cast<uint4*>(q)[(r_begin + r) * 2 * ivec + col0 / 8] = bf16x8_p(dg);
+                        reinterpret_cast<uint4*>(q)[(r_begin + r) * 2 * ivec + ivec + col0 / 8] = bf16x8_p(du);
                     } else {
-                        m = amax8(dg, m);
-                        m = amax8(du, m);
-                        q[r * 2 * ivec + col0 / 8] = quant8<FMT>(dg, scale);
-                        q[r * 2 * ivec + ivec + col0 / 8] = quant8<FMT>(du, scale);
+                        m = amax8_p(dg, m);
+                        m = amax8_p(du, m);
+                        pq[r * 2 * ivec] = quant8_p<FMT>(dg, scale2);
+                        pq[r * 2 * ivec + ivec] = quant8_p<FMT>(du, scale2);
                     }
                 }
             }
@@ -143,9 +181,14 @@ __global__ void __launch_bounds__(256) dswiglu_quant_kernel(const uint4* __restr
     }
     if (dbias_ws) {
 #pragma unroll
-        for (int j = 0; j < 8; j++) {
-            part[rl][cv * 8 + j] = sg[j];
-            part[rl][DS_COLS + cv * 8 + j] = su[j];
+        for (int j = 0; j < 4; j++) {
+            float lo, hi;
+            upk2(sg[j], lo, hi);
+            part[rl][cv * 8 + 2 * j] = lo;
+            part[rl][cv * 8 + 2 * j + 1] = hi;
+            upk2(su[j], lo, hi);
+            part[rl][DS_COLS + cv * 8 + 2 * j] = lo;
+            part[rl][DS_COLS + cv * 8 + 2 * j + 1] = hi;
         }
     }
     if (FMT != FMT_BF16 && amax) block_amax_to_global(m, red, amax);
@@ -180,17 +223,27 @@ int launch_dswiglu_quant_bwd(const void* da, const void* fc1_out, void* q, int64
         if (e != cudaSuccess) { set_error("dswiglu_quant_bwd: memset: %s", cudaGetErrorString(e)); return (int)e; }
     }
     const int strips = static_cast<int>((I + DS_COLS - 1) / DS_COLS);
-    int64_t ychunks = (static_cast<int64_t>(sm_count()) * 4 + strips - 1) / strips;
-    int64_t rows_per_cta = (M + ychunks - 1) / ychunks;
-    rows_per_cta = (rows_per_cta + 15) / 16 * 16;
-    ychunks = (M + rows_per_cta - 1) / rows_per_cta;
+    // many short CTAs (64 rows x 256 columns) rather than ~1.4 waves of long ones: the tail of the last wave stays a few percent
+    // (the long-CTA version measured 67 % of HBM bandwidth with 616 CTAs on 444 resident slots)
+    int64_t rows_per_cta = 64;
+    while ((M + rows_per_cta - 1) / rows_per_cta > 65535) rows_per_cta *= 2;
+    const int64_t ychunks = (M + rows_per_cta - 1) / rows_per_cta;
     dim3 grid(strips, static_cast<unsigned>(ychunks));
-    if (fmt == FMT_E4M3)
-        dswiglu_quant_kernel<FMT_E4M3><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws);
-    else if (fmt == FMT_E5M2)
-        dswiglu_quant_kernel<FMT_E5M2><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws);
-    else
-        dswiglu_quant_kernel<FMT_BF16><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, nullptr, nullptr, dbias_ws);
+    static const int variant = [] { const char* e = getenv("LLMFP8_TUNE_DSWIGLU"); return e ? atoi(e) : 0; }();
+#define DSW_LAUNCH(UN, MINB)                                                                                                                  \
+    do {                                                                                                                                      \
+        if (fmt == FMT_E4M3)                                                                                                                  \
+            dswiglu_quant_kernel<FMT_E4M3, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
+        else if (fmt == FMT_E5M2)                                                                                                             \
+            dswiglu_quant_kernel<FMT_E5M2, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
+        else                                                                                                                                  \
+            dswiglu_quant_kernel<FMT_BF16, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, nullptr, nullptr, dbias_ws); \
+    } while (0)
+    if (variant == 1) DSW_LAUNCH(2, 4);
+    else if (variant == 2) DSW_LAUNCH(1, 4);
+    else if (variant == 3) DSW_LAUNCH(4, 2);
+    else DSW_LAUNCH(2, 3);
+#undef DSW_LAUNCH
     LLMFP8_LAUNCH_CHECK("dswiglu_quant_bwd");
     if (dbias_ws) return launch_f32_to_bf16(dbias_ws, dbias_bf16, 2 * I, stream);
     return 0;

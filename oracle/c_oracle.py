@@ -35,8 +35,10 @@ def lib():
         _lib.orc_fp8_to_f32.argtypes = [C.c_uint8, C.c_int]
         _lib.orc_e8m0_roundup.restype = C.c_uint8
         _lib.orc_e8m0_roundup.argtypes = [C.c_float]
-        _lib.orc_expf.restype = C.c_float
-        _lib.orc_expf.argtypes = [C.c_float]
+        _lib.orc_exp_neg.restype = C.c_float
+        _lib.orc_exp_neg.argtypes = [C.c_float]
+        _lib.orc_sigmoid.restype = C.c_float
+        _lib.orc_sigmoid.argtypes = [C.c_float]
         _lib.orc_rms_rsigma.restype = C.c_float
         _lib.orc_sf_offset.restype = C.c_int64
         _lib.orc_sf_offset.argtypes = [C.c_int64] * 3

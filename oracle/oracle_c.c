@@ -226,24 +226,29 @@ void orc_rmsnorm_quant(const uint16_t* x, const uint16_t* gamma, int64_t M, int6
 }
 
 /* ---- K3: SwiGLU with a pinned exp ----------------------------------------------------------- */
-float orc_expf(float x) {
-    x = fminf(fmaxf(x, -87.0f), 87.0f);
-    float t = x * 1.44269504f;
-    float n = rintf(t);
-    float r = fmaf(n, -0.693359375f, x);
-    r = fmaf(n, 2.12194440e-4f, r);
-    float p = 1.9875691500e-4f;
-    p = fmaf(p, r, 1.3981999507e-3f);
-    p = fmaf(p, r, 8.3334519073e-3f);
-    p = fmaf(p, r, 4.1665795894e-2f);
-    p = fmaf(p, r, 1.6666665459e-1f);
-    p = fmaf(p, r, 5.0000001201e-1f);
-    float r2 = r * r;
-    float y = fmaf(p, r2, r);
-    y = y + 1.0f;
-    return y * u2f((uint32_t)((int)n + 127) << 23);
+/* sigmoid(g) = 1 / (1 + E),  E = exp(-g) evaluated as 2^(x * log2e), x = clamp(-g, -80, 80):
+ *   m = fma(x, log2e, 1.5 * 2^23)        -> the low mantissa bits of m hold n = rint(x * log2e) (ties to even)
+ *   f = fma(x, log2e, 1.5 * 2^23 - m)    -> x * log2e - n, |f| <= 0.5, one rounding
+ *   p = 2^f by a degree-5 Horner chain of fmas (max rel. error 1.7e-7)
+ *   E = bits(p) + (bits(m) << 23)        -> 2^n * p by integer exponent arithmetic
+ * Every step is one IEEE fp32 operation; csrc/common.cuh: sigmoid2_pinned performs the same steps (two lanes at a time). */
+#define SIG_CLAMP 80.0f
+#define SIG_LOG2E 1.44269502162933349609375f
+#define SIG_MAGIC 12582912.0f
+float orc_exp_neg(float g) {
+    float x = fminf(fmaxf(-g, -SIG_CLAMP), SIG_CLAMP);
+    float m = fmaf(x, SIG_LOG2E, SIG_MAGIC);
+    float nneg = SIG_MAGIC - m;
+    float f = fmaf(x, SIG_LOG2E, nneg);
+    float p = 0.001326472731307149f;
+    p = fmaf(p, f, 0.009671512991189957f);
+    p = fmaf(p, f, 0.05550733581185341f);
+    p = fmaf(p, f, 0.24022242426872253f);
+    p = fmaf(p, f, 0.6931470036506653f);
+    p = fmaf(p, f, 1.0f);
+    return u2f(f2u(p) + (f2u(m) << 23));
 }
-static inline float orc_sigmoid(float g) { return 1.0f / (1.0f + orc_expf(-g)); }
+float orc_sigmoid(float g) { return 1.0f / (1.0f + orc_exp_neg(g)); }
 
 /* fc1_out [M, 2I] bf16, gate = [:, :I], up = [:, I:]  (te_llama.py:225-233: gate rows first) */
 void orc_swiglu_f32(const uint16_t* fc1, int64_t M, int64_t I, float* a) {

@@ -155,6 +155,30 @@ def test_swiglu_quant(shape):
     assert torch.equal(ab.cpu(), a.bfloat16())
 
 
+def test_swiglu_every_bf16_gate_value():
+    """The pinned sigmoid depends on the gate alone, and the gate is bf16: all 65536 gate bit patterns (x 4 up values) are checked
+    bit for bit — exhaustive proof that MUFU.RCP + one Newton step equals the oracle's correctly rounded 1 / (1 + E)."""
+    ops = _ops()
+    allg = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16)
+    ups = torch.tensor([1.0, -0.7421875, 3.140625, 1e-3]).bfloat16()
+    gate = allg.repeat(4).reshape(4 * 64, 1024)                     # M = 256 rows of I = 1024
+    up = ups.repeat_interleave(65536).reshape(4 * 64, 1024)
+    fc1 = torch.cat([gate, up], dim=1).contiguous()
+    a = co.swiglu_f32(fc1)
+    ab = ops.swiglu_bf16(dev(fc1)).cpu()
+    want = a.bfloat16()
+    nan = torch.isnan(want.float())
+    assert torch.equal(torch.isnan(ab.float()), nan)
+    assert torch.equal(ab.view(torch.int16)[~nan], want.view(torch.int16)[~nan])
+    da = torch.full((256, 1024), 0.5).bfloat16()
+    d = co.dswiglu_f32(da, fc1)
+    db, _ = ops.dswiglu_bf16(dev(da), dev(fc1))
+    wantd = d.bfloat16()
+    nand = torch.isnan(wantd.float())
+    assert torch.equal(torch.isnan(db.cpu().float()), nand)
+    assert torch.equal(db.cpu().view(torch.int16)[~nand], wantd.view(torch.int16)[~nand])
+
+
 @pytest.mark.parametrize("shape", [(4096, 1024), (77, 264), (5, 8)])
 def test_dswiglu_quant(shape):
     ops = _ops()

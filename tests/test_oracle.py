@@ -200,10 +200,17 @@ def test_swiglu_c_close_to_torch():
     a = co.swiglu_f32(fc1)
     ar = fo.swiglu_ref(fc1)
     assert torch.allclose(a, ar, rtol=1e-5, atol=1e-30)
-    xs = torch.linspace(-87, 87, 20001)
-    ex = torch.tensor([co.lib().orc_expf(v) for v in xs.tolist()], dtype=torch.float64)
-    rel = ((ex - torch.exp(xs.double())) / torch.exp(xs.double())).abs().max().item()
-    assert rel < 4e-7
+    # the pinned exp(-g) (orc_exp_neg) against the double-precision exponential: full clamp range and the range that matters
+    for lim, tol in ((80.0, 1.5e-6), (16.0, 5e-7)):
+        xs = torch.linspace(-lim, lim, 20001)
+        ex = torch.tensor([co.lib().orc_exp_neg(v) for v in xs.tolist()], dtype=torch.float64)
+        rel = ((ex - torch.exp(-xs.double())) / torch.exp(-xs.double())).abs().max().item()
+        assert rel < tol, (lim, rel)
+    # pinned sigmoid over EVERY bf16 gate value in the clamp range against torch
+    allg = torch.arange(0, 65536, dtype=torch.int32).to(torch.int16).view(torch.bfloat16).float()
+    allg = allg[torch.isfinite(allg) & (allg.abs() <= 80)]
+    sg = torch.tensor([co.lib().orc_sigmoid(v) for v in allg.tolist()], dtype=torch.float64)
+    assert torch.allclose(sg, torch.sigmoid(allg.double()), rtol=2e-6, atol=0)
     q, am = co.swiglu_quant(fc1, 3.0, E4M3)
     assert same_bytes(q, fo.sat_cast(a * 3.0, E4M3)) and am == a.abs().max().item()
     # backward against autograd of the torch reference

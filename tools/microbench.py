@@ -71,6 +71,7 @@ def main():
     ap.add_argument("--cg", type=int, default=0, help="force the CTA group (1 | 2; 0 = heuristic)")
     ap.add_argument("--debug", type=int, default=0)
     ap.add_argument("--tag", default="")
+    ap.add_argument("--kfilter", default="", help="only run memory-bound kernels whose name contains this substring")
     args = ap.parse_args()
     H, I, QKV, M = SHAPES[args.model]
     hbm, bf16_tf, src = peaks()
@@ -99,6 +100,8 @@ def main():
     amax = torch.zeros(1, device=dev)
 
     def mem(name, fn, nbytes):
+        if args.kfilter and args.kfilter not in name:
+            return
         med, best = timeit(fn)
         emit({"kernel": name, "ms": med, "ms_best": best, "GBps": nbytes / med / 1e6, "frac_hbm": nbytes / med / 1e6 / hbm, "peak": src, "bytes": nbytes})
 
@@ -121,6 +124,7 @@ def main():
         mem("K2m mx_quantize row+col W1[2I,H]", lambda: ops.mx_quantize(w1, True, True), int(4.0625 * 2 * I * H))
         mem("K1m rsigma + mx_quantize row+col [M,H]", lambda: ops.mx_quantize(x, True, True, ops.rmsnorm_rsigma(x, 1e-5), gamma), int(4.0625 * M * H))
         mem("copy bf16 [M,2I] (torch, reference point)", lambda: fc1.clone(), 4 * M * 2 * I)
+        mem("copy bf16 [M,H] (torch, reference point for the short kernels)", lambda: x.clone(), 4 * M * H)
         del x, w1, fc1, da
 
     if not args.only or "gemm" in args.only:
