@@ -218,6 +218,8 @@ def main():
 
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: llm_fp8_b200 has no CPU path (use --impl reference for the CPU arm)")
+    if os.environ.get("NCCL_DEBUG", "").upper() in ("", "VERSION"):
+        os.environ["NCCL_DEBUG"] = "WARN"          # NCCL prints its version banner on stdout; stdout carries the JSON line only
     rank, world, local = dp.init_from_env()
     dev = torch.device("cuda", local)
     lib = _lib.load()
@@ -296,6 +298,8 @@ def main():
 
     # ---- roofline leg: every C-ABI launch of one more step bracketed by CUDA events on the launching stream
     roof, roof_q, shares = None, None, None
+    if not a.no_roofline and rank != 0:
+        resident_step()                      # every rank runs the step (its gradient / amax all-reduces must match rank 0's)
     if not a.no_roofline and rank == 0:
         _lib.profile_start()
         resident_step()
