@@ -29,8 +29,13 @@ namespace llmfp8 {
 constexpr int BM = 128;          // tile rows per CTA (UMMA M = 128 * CG)
 constexpr int BK = 128;          // k elements per pipeline stage (= one 128 B swizzle row when K-major)
 constexpr int UMMA_K = 32;       // k per tcgen05.mma for 8-bit operands
-constexpr int GEMM_THREADS = 320;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quadrant)
+constexpr int GEMM_THREADS = 352;   // warp 0 TMA, warp 1 MMA, warps 2..9 epilogue (two per TMEM lane quadrant), warp 10 tile scheduler
 constexpr int EPI_WARPS = 8;
+constexpr int NUM_WARPS = GEMM_THREADS / 32;
+constexpr int CLC_ST = 2;           // cluster-launch-control queries in flight
+constexpr int RING = 4;             // tile ids queued per CTA (the producer runs up to ~3 tiles ahead of the epilogue)
+constexpr int RING_READERS = 10;    // warps 0..9 of the CTA
+constexpr int CTRL_BYTES = 512;     // barriers + CLC responses + TMEM pointer
 constexpr int GROUP_M = 16;      // rasterisation group, in 128-row blocks
 constexpr int MAX_STAGES = 8;
 constexpr int SF_COL0 = 448;     // TMEM columns 448..511: four rotating scale-factor buffers of 16 columns (SFA 4 + SFB up to 12), so the
@@ -55,6 +60,46 @@ struct GemmParams {
     int stages;                 // smem ring depth
     int acc_stages;             // TMEM accumulator buffers (2, or 1 for MX with bn > 192)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads
+    int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
+};
+
+// Shared-memory control block of one CTA.
+struct GemmCtrl {
+    uint64_t full[MAX_STAGES], empty[MAX_STAGES];
+    uint64_t tmem_full[2], tmem_empty[2];
+    uint64_t clc_full[CLC_ST], clc_empty[CLC_ST];     // CLC responses: scheduler warps only
+    uint64_t ring_full[RING], ring_empty[RING];       // tile ids re-broadcast by this CTA's scheduler warp to its other warps
+    alignas(16) uint8_t clc_resp[CLC_ST][16];
+    int ring_tile[RING];
+    uint32_t tmem_ptr;
+};
+static_assert(sizeof(GemmCtrl) <= CTRL_BYTES, "control block");
+
+// Tile sequence of one warp role.  Static mode: tile += units.  Dynamic mode: the cluster's first tile is its own blockIdx; every
+// further tile is a not-yet-launched cluster that the scheduler warp cancelled through cluster launch control — so CTAs that start
+// late (SMs held by a concurrent NCCL kernel) or run slow simply take fewer tiles, instead of stretching the kernel by a whole wave.
+// The scheduler warp of each CTA reads the (multicast) CLC response and hands the tile id to the other warps through a small ring
+// in shared memory, so the TMA / MMA warps never touch the async proxy fence the response read needs.
+struct TileSched {
+    GemmCtrl* c;
+    int r, ph, dynamic, num_tiles, num_units;
+    __device__ __forceinline__ void init(GemmCtrl* ctrl, int dyn, int ntiles, int nunits) {
+        c = ctrl; r = 0; ph = 0; dynamic = dyn; num_tiles = ntiles; num_units = nunits;
+    }
+    // whole warp calls, AFTER it has issued the work of tile `cur`; -> true and `next` when another tile follows
+    __device__ __forceinline__ bool advance(int cur, int& next) {
+        if (!dynamic) {
+            next = cur + num_units;
+            return next < num_tiles;
+        }
+        ptx::mbar_wait(&c->ring_full[r], ph);
+        const int t = *reinterpret_cast<volatile int*>(&c->ring_tile[r]);
+        __syncwarp();
+        if ((threadIdx.x & 31) == 0) ptx::mbar_arrive(&c->ring_empty[r]);
+        if (++r == RING) { r = 0; ph ^= 1; }
+        next = t;
+        return t >= 0;
+    }
 };
 
 template <int CG>
@@ -80,18 +125,19 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const int stage_bytes = A_BYTES + p.b_rows_cta * BK;
 
     extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+    uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (STS, not generic ST)
     uint8_t* epi_base = smem + STAGES * stage_bytes;          // 8 epilogue warps x 4 KB, 1024 B aligned (128B-swizzled TMA-store boxes)
     uint8_t* sf_base = epi_base + EPI_BYTES;
-    uint64_t* full_bar = reinterpret_cast<uint64_t*>(sf_base + (MX ? STAGES * SF_STAGE_BYTES : 0));
-    uint64_t* empty_bar = full_bar + MAX_STAGES;
-    uint64_t* tmem_full = empty_bar + MAX_STAGES;
-    uint64_t* tmem_empty = tmem_full + 2;
-    uint32_t* tmem_ptr_smem = reinterpret_cast<uint32_t*>(tmem_empty + 2);
+    GemmCtrl* ctrl = reinterpret_cast<GemmCtrl*>(sf_base + (MX ? STAGES * SF_STAGE_BYTES : 0));
+    uint64_t* full_bar = ctrl->full;
+    uint64_t* empty_bar = ctrl->empty;
+    uint64_t* tmem_full = ctrl->tmem_full;
+    uint64_t* tmem_empty = ctrl->tmem_empty;
+    uint32_t* tmem_ptr_smem = &ctrl->tmem_ptr;
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;    // 0 = leader (issues the MMAs)
-    const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;
+    const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;     // dynamic mode: unit = this cluster's own (first) tile
     const int num_m = (p.M + TM - 1) / TM, num_n = (p.N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int num_kb = (p.K + BK - 1) / BK;
@@ -110,6 +156,14 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         for (int s = 0; s < ACC_STAGES; s++) {
             ptx::mbar_init(&tmem_full[s], 1);
             ptx::mbar_init(&tmem_empty[s], EPI_WARPS * CG);
+        }
+        for (int s = 0; s < CLC_ST; s++) {
+            ptx::mbar_init(&ctrl->clc_full[s], 1);
+            ptx::mbar_init(&ctrl->clc_empty[s], CG);                 // the scheduler warp of every CTA of the pair reads each response
+        }
+        for (int s = 0; s < RING; s++) {
+            ptx::mbar_init(&ctrl->ring_full[s], 1);
+            ptx::mbar_init(&ctrl->ring_empty[s], RING_READERS);
         }
         ptx::fence_barrier_init();
     }
@@ -131,6 +185,9 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         n_blk = in_group / gsize;
     };
 
+    TileSched sched;
+    sched.init(ctrl, p.dynamic, num_tiles, num_units);
+
     if (warp == 0) {
         // ================================ TMA producer (one per CTA: own A rows, own part of B, own scale tiles)
         {
@@ -139,7 +196,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int bn_cta = BN / CG;
             const bool sf_load = MX && !(p.debug & 2);
             const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? SF_STAGE_BYTES : 0));
-            for (int tile = unit; tile < num_tiles; tile += num_units) {
+            int tile = unit, next_tile;
+            for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
                 const int m0 = m_blk * TM + rank * BM, n0 = n_blk * BN, nb0 = n0 + rank * bn_cta;
@@ -168,6 +226,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     __syncwarp();
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
+                more = sched.advance(tile, next_tile);
             }
         }
     } else if (warp == 1) {
@@ -176,7 +235,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
             constexpr uint32_t A_LBO = A_MN ? (BK * 128) : 16, B_LBO = B_MN ? (BK * 128) : 16;
             constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K * 128) : UMMA_K;
-            for (int tile = unit; tile < num_tiles; tile += num_units) {
+            int tile = unit, next_tile;
+            for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
                 // MX: the scale of column n lives in TMEM column (sf buffer) + 4 + (n - 128 * (n0 / 128)) / 32: a tile that starts 64 rows
@@ -219,6 +279,44 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if (ptx::elect_one_sync()) ptx::tc_commit_cg<CG>(&tmem_full[acc]);         // accumulator complete -> epilogue warps of both CTAs
                 __syncwarp();
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+                more = sched.advance(tile, next_tile);
+            }
+        } else {
+            // the peer's MMA warp issues nothing, but it is one of the readers every CLC response waits for
+            int tile = unit, next_tile;
+            while (sched.advance(tile, next_tile)) tile = next_tile;
+        }
+    } else if (warp == NUM_WARPS - 1) {
+        // ================================ tile scheduler.  Per round: (leader) wait until both CTAs' scheduler warps have read the
+        // response slot, arm this CTA's barrier for the 16 response bytes, (leader) issue the query — the response is multicast to both
+        // CTAs; read it (async-proxy fenced), free the slot, push the tile id into this CTA's ring.  Stops after the first failed query.
+        if (p.dynamic) {
+            const uint32_t clc_empty_leader = CG == 2 ? ptx::mapa(ptx::smem_u32(&ctrl->clc_empty[0]), 0) : 0u;
+            int cs = 0, cph = 0, rr = 0, rph = 0;
+            for (bool more = true; more;) {
+                if (rank == 0) ptx::mbar_wait(&ctrl->clc_empty[cs], cph ^ 1);
+                if (ptx::elect_one_sync()) {
+                    ptx::mbar_arrive_expect_tx(&ctrl->clc_full[cs], 16);
+                    if (rank == 0) ptx::clc_try_cancel<CG>(ctrl->clc_resp[cs], &ctrl->clc_full[cs]);
+                }
+                __syncwarp();
+                ptx::mbar_wait(&ctrl->clc_full[cs], cph);
+                uint32_t x;
+                more = ptx::clc_query(ctrl->clc_resp[cs], x);
+                ptx::fence_proxy_async();        // the response read is ordered before the async-proxy write of the next query into this slot
+                __syncwarp();
+                if (lane == 0) {
+                    if constexpr (CG == 2) ptx::mbar_arrive_cluster(clc_empty_leader + 8 * cs);
+                    else ptx::mbar_arrive(&ctrl->clc_empty[cs]);
+                }
+                if (++cs == CLC_ST) { cs = 0; cph ^= 1; }
+                ptx::mbar_wait(&ctrl->ring_empty[rr], rph ^ 1);
+                if (lane == 0) {
+                    ctrl->ring_tile[rr] = more ? static_cast<int>(x) / CG : -1;
+                    ptx::mbar_arrive(&ctrl->ring_full[rr]);          // release: the tile id is visible to whoever acquires this phase
+                }
+                __syncwarp();
+                if (++rr == RING) { rr = 0; rph ^= 1; }
             }
         }
     } else {
@@ -243,7 +341,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int ccols = p.out_fp32 ? 32 : 64;
             const int nchunks = BN / ccols;
             if (lane == 0) ptx::prefetch_tensormap(&map_d);
-            for (int tile = unit; tile < num_tiles; tile += num_units) {
+            int tile = unit, next_tile;
+            for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
                 const int row0 = m_blk * TM + static_cast<int>(rank) * BM + quad * 32;
@@ -302,10 +401,12 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     }
                 }
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+                more = sched.advance(tile, next_tile);
             }
             if (lane == 0) ptx::tma_store_wait<0>();
-        } else
-        for (int tile = unit; tile < num_tiles; tile += num_units) {
+        } else {
+        int tile = unit, next_tile;
+        for (bool more = true; more; tile = next_tile) {
             int m_blk, n_blk;
             tile_coords(tile, m_blk, n_blk);
             const int row = m_blk * TM + static_cast<int>(rank) * BM + quad * 32 + lane;
@@ -377,6 +478,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 else ptx::mbar_arrive(&tmem_empty[acc]);
             }
             if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
+            more = sched.advance(tile, next_tile);
+        }
         }
     }
 
@@ -502,7 +605,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
     p.acc_stages = (mx && BN > 192) ? 1 : 2;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
-    const int fixed = 1024 /*alignment slack*/ + 256 /*barriers*/ + EPI_BYTES /*epilogue staging*/;
+    const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;
     int stages = (SMEM_BUDGET - fixed) / stage_bytes;
     if (stages > MAX_STAGES) stages = MAX_STAGES;
     p.stages = stages;
@@ -534,7 +637,11 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     }
 
     const int num_tiles = ((M + BM * cg - 1) / (BM * cg)) * ((N + BN - 1) / BN);
-    if (num_tiles * cg < grid) grid = num_tiles * cg;
+    // dynamic (default): one cluster per tile, handed out by cluster launch control; static (debug bit 3, or a caller-imposed CTA
+    // budget): persistent grid, round-robin tiles
+    p.dynamic = ((g_debug & 8) || max_ctas > 0) ? 0 : 1;
+    if (p.dynamic) grid = num_tiles * cg;
+    else if (num_tiles * cg < grid) grid = num_tiles * cg;
     if (cg == 2) return dispatch<2>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
     return dispatch<1>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
 }

@@ -169,6 +169,35 @@ __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
     asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 // TMA loads whose completion is signalled on a barrier that may live in the PEER CTA of the pair (the leader's)
+// ---- cluster launch control (CLC): a running cluster cancels a not-yet-launched cluster of the same grid and takes over its
+// tile.  The 16 B response lands in shared memory (multicast: at the same offset in every CTA of the cluster) and completes 16 tx
+// bytes on the mbarrier at `bar` (same offset in every CTA).
+template <int CG>
+__device__ __forceinline__ void clc_try_cancel(void* resp, uint64_t* bar) {
+    if constexpr (CG == 1)
+        asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.b128 [%0], [%1];"
+                     :: "r"(smem_u32(resp)), "r"(smem_u32(bar)) : "memory");
+    else
+        asm volatile("clusterlaunchcontrol.try_cancel.async.shared::cta.mbarrier::complete_tx::bytes.multicast::cluster::all.b128 [%0], [%1];"
+                     :: "r"(smem_u32(resp)), "r"(smem_u32(bar)) : "memory");
+}
+// -> true and the cancelled cluster's first blockIdx.x when a cluster was taken over; false when none is left to launch
+__device__ __forceinline__ bool clc_query(const void* resp, uint32_t& ctaid_x) {
+    uint32_t valid, x = 0;
+    asm volatile(
+        "{\n"
+        ".reg .pred p1;\n"
+        ".reg .b128 r;\n"
+        "ld.shared.b128 r, [%2];\n"
+        "clusterlaunchcontrol.query_cancel.is_canceled.pred.b128 p1, r;\n"
+        "selp.u32 %1, 1, 0, p1;\n"
+        "@p1 clusterlaunchcontrol.query_cancel.get_first_ctaid::x.b32.b128 %0, r;\n"
+        "}\n"
+        : "+r"(x), "=r"(valid) : "r"(smem_u32(resp)) : "memory");
+    ctaid_x = x;
+    return valid != 0;
+}
+
 __device__ __forceinline__ void tma_load_2d_cg2(const CUtensorMap* m, uint32_t bar_cluster_addr, void* smem_dst, int32_t c0, int32_t c1) {
     asm volatile(
         "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.tile.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];"
