@@ -44,6 +44,9 @@ def parse():
     ap.add_argument("--batch", type=int, default=12, help="sequences per GPU (reference semantics: per-device batch)")
     ap.add_argument("--seq", type=int, default=512)
     ap.add_argument("--layers", type=int, default=0, help="0 = the model's own depth")
+    ap.add_argument("--graph", type=int, default=int(os.environ.get("LLMFP8_BENCH_GRAPH", "0")),
+                    help="1: capture the whole forward+backward step in one CUDA graph and replay it (N=1 only; same kernels, no host launch cost)")
+    ap.add_argument("--no-fuse-residual", action="store_true", help="run the plain h = h + f(h) layer form (separate elementwise passes)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--cpu-sample-tokens", type=int, default=1536)
@@ -225,7 +228,7 @@ def main():
     lib = _lib.load()
     pk = peaks()
 
-    model = LinearPathStack(a.model, a.scenario, a.layers or None, device=dev)
+    model = LinearPathStack(a.model, a.scenario, a.layers or None, device=dev, fuse_residual=False if a.no_fuse_residual else None)
     L = model.n_layers
     H = model.H
     M = a.batch * a.seq
@@ -287,8 +290,42 @@ def main():
     # warm-up (also fills the delayed-scaling history enough for real scales)
     for _ in range(max(a.warmup, 3)):
         resident_step()
+
+    graphed = False
+    eager_resident_step, eager_e2e_step = resident_step, e2e_step
+    if a.graph and world == 1:
+        # the same step, captured once into a CUDA graph (every kernel of forward + backward, the weight-gradient writes included)
+        # and replayed: the host issues one launch per step instead of ~1500
+        try:
+            n0 = lib.llmfp8_launch_count()
+            x_static = x_dev.clone()
+            zero()
+            cg = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(cg):
+                loss_static = step(x_static)
+            captured_launches = int(lib.llmfp8_launch_count() - n0)
+            torch.cuda.synchronize()
+
+            def resident_step():            # noqa: F811
+                cg.replay()
+
+            def e2e_step():                 # noqa: F811
+                x_static.copy_(x_host, non_blocking=True)
+                cg.replay()
+                loss_host.copy_(loss_static.detach().reshape(1), non_blocking=False)
+            graphed = True
+            for _ in range(2):
+                resident_step()
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001
+            print(f"[bench] CUDA-graph capture failed, staying eager: {type(e).__name__}: {str(e)[:300]}", file=sys.stderr, flush=True)
+            torch.cuda.synchronize()
+            graphed = False
+            resident_step, e2e_step = eager_resident_step, eager_e2e_step
     sampler = ClockSampler(local) if rank == 0 else None
     ms_step, launches = timed(resident_step, a.steps)
+    if graphed:
+        launches = captured_launches
     e2e_step()
     ms_e2e, _ = timed(e2e_step, a.steps)
     clocks = sampler.stop() if sampler else None
@@ -302,11 +339,14 @@ def main():
         resident_step()                      # every rank runs the step (its gradient / amax all-reduces must match rank 0's)
     if not a.no_roofline and rank == 0:
         _lib.profile_start()
-        resident_step()
+        eager_resident_step()
         recs = _lib.profile_stop()
         tot = sum(r[3] for r in recs) or 1e-9
         by = {}
+        canon = {"llmfp8_fp8_gemm_res": "llmfp8_fp8_gemm", "llmfp8_mxfp8_gemm_res": "llmfp8_mxfp8_gemm", "llmfp8_mx_quantize_ld": "llmfp8_mx_quantize",
+                 "llmfp8_quant_cast_amax_2d": "llmfp8_quant_cast_amax", "llmfp8_rmsnorm_bwd_add": "llmfp8_rmsnorm_bwd"}   # same kernels, extended entry points
         for n, u, w, ms in recs:
+            n = canon.get(n, n)
             d = by.setdefault(n, {"unit": u, "work": 0.0, "ms": 0.0, "launches": 0})
             d["work"] += w; d["ms"] += ms; d["launches"] += 1
         shares = {n.replace("llmfp8_", ""): round(d["ms"] / tot, 4) for n, d in sorted(by.items(), key=lambda kv: -kv[1]["ms"])}
@@ -344,7 +384,8 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
                        "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,
-                       "parallelism": f"dp{world}", "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
+                       "parallelism": f"dp{world}", "launch": "cuda-graph replay" if graphed else "eager stream launches",
+                       "residual_adds": "fused (GEMM epilogue / RMSNorm backward)" if model.layers[0].fuse_residual else "separate elementwise passes", "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,

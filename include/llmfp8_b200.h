@@ -43,6 +43,10 @@ uint64_t llmfp8_launch_count(void);
  * x bf16 [n] (n % 16 == 0), q u8 [n]; scale, amax fp32 device scalars (amax may be NULL). */
 int llmfp8_quant_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* scale, float* amax, void* stream);
 
+/* K2 on a column slice: x is [rows, cols] with row pitch ldx elements (ldx >= cols, ldx % 8 == 0, cols % 16 == 0), q dense [rows, cols].
+ * Lets Linear consume a view such as qkv[:, :q_out] (te_llama.py:45-56: the attention output / query slice) without a copy. */
+int llmfp8_quant_cast_amax_2d(const void* x, int64_t ldx, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax, void* stream);
+
 /* K2b: as K2 on a [rows, cols] matrix, plus bgrad[c] = sum_r x[r, c] (bf16 out).   [tex.fp8_cast_transpose_bgrad_fused]
  * colsum_ws: fp32 [cols] scratch. */
 int llmfp8_quant_cast_amax_bgrad(const void* x, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax,
@@ -57,6 +61,10 @@ int llmfp8_rmsnorm_quant_fwd(const void* x, const void* gamma, void* q, float* r
 int llmfp8_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma, float* ws, int64_t M,
                        int64_t H, void* stream);
 int llmfp8_rmsnorm_bwd_ws_rows(int64_t M);
+/* K5 with the residual-branch gradient folded in: dx = rmsnorm_bwd(...) + dres (dres bf16 [M, H]) — the `h + f(norm(h))` pattern of
+ * TELlamaDecoderLayer.forward (te_llama.py:78, 81) then needs no separate gradient-accumulation pass. */
+int llmfp8_rmsnorm_bwd_add(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma, float* ws,
+                           int64_t M, int64_t H, void* stream);
 
 /* K3: a = silu(gate) * up over fc1_out bf16 [M, 2I] (gate = [:, :I], up = [:, I:]); q u8 [M, I].   [tex.swiglu + cast] */
 int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream);
@@ -79,6 +87,9 @@ int llmfp8_amax_scale_update(float* amax_history, float* scale, float* scale_inv
  * [tex.quantize with an MXFP8 quantizer; rmsnorm_fwd with MXFP8 output] */
 int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
                        const void* gamma, void* stream);
+/* same with an explicit row pitch of x (elements; >= cols, % 8 == 0): quantises a column slice of a wider matrix in place */
+int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                          const float* rsigma, const void* gamma, void* stream);
 int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream);
 /* bytes of the swizzled scale tensor of a matrix with `rows` rows and `k` elements along the blocked dimension */
 int64_t llmfp8_mx_scale_bytes(int64_t rows, int64_t k);
@@ -92,6 +103,12 @@ int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
                     int out_fp32, int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, int accumulate,
                     int max_ctas, void* stream);
 
+/* D bf16 [M, N] = (a_scale_inv * b_scale_inv) * A B^T (+ bias[n]) + R[m, n]: the residual add of `h + proj(...)` / `h + fc2(...)`
+ * (te_llama.py:78, 81) fused into the epilogue — R bf16 with leading dimension ldr, added in fp32 before the single bf16 rounding. */
+int llmfp8_fp8_gemm_res(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd, int M,
+                        int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, const void* residual, int64_t ldr,
+                        int max_ctas, void* stream);
+
 /* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  Process-wide, not thread-safe. */
 void llmfp8_gemm_force_bn(int bn);
 /* likewise the CTA group: 1 = single-CTA kernel, 2 = CTA pairs (cta_group::2), 0 = automatic */
@@ -102,6 +119,10 @@ void llmfp8_gemm_debug(int flags);
 /* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */
 int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
                       int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream);
+
+/* block-scaled GEMM with the fused residual (see llmfp8_fp8_gemm_res) */
+int llmfp8_mxfp8_gemm_res(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
+                          int64_t ldd, int M, int N, int K, const void* bias, const void* residual, int64_t ldr, int max_ctas, void* stream);
 
 #ifdef __cplusplus
 }

@@ -23,14 +23,17 @@ _PROTOTYPES = {
     "llmfp8_sm_count": [],
     "llmfp8_launch_count": [],
     "llmfp8_quant_cast_amax": [vp, vp, i64, i32, vp, vp, vp],
+    "llmfp8_quant_cast_amax_2d": [vp, i64, vp, i64, i64, i32, vp, vp, vp],
     "llmfp8_quant_cast_amax_bgrad": [vp, vp, i64, i64, i32, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_quant_fwd": [vp, vp, vp, vp, i64, i64, f32, i32, vp, vp, vp],
     "llmfp8_rmsnorm_bwd": [vp, vp, vp, vp, vp, vp, vp, i64, i64, vp],
     "llmfp8_rmsnorm_bwd_ws_rows": [i64],
+    "llmfp8_rmsnorm_bwd_add": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, vp],
     "llmfp8_swiglu_quant_fwd": [vp, vp, i64, i64, i32, vp, vp, vp],
     "llmfp8_dswiglu_quant_bwd": [vp, vp, vp, i64, i64, i32, vp, vp, vp, vp, vp],
     "llmfp8_amax_scale_update": [vp, vp, vp, vp, i32, i32, i32, vp],
     "llmfp8_mx_quantize": [vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
+    "llmfp8_mx_quantize_ld": [vp, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_rsigma": [vp, vp, i64, i64, f32, vp],
     "llmfp8_mx_scale_bytes": [i64, i64],
     "llmfp8_gemm_force_bn": [i32],
@@ -38,6 +41,8 @@ _PROTOTYPES = {
     "llmfp8_gemm_debug": [i32],
     "llmfp8_fp8_gemm": [vp, i64, i32, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp],
     "llmfp8_mxfp8_gemm": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, vp, i32, i32, vp],
+    "llmfp8_fp8_gemm_res": [vp, i64, i32, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, vp, vp, vp, vp, i64, i32, vp],
+    "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }
 _RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
 EXPORTS = tuple(_PROTOTYPES)
@@ -71,14 +76,20 @@ def load():
 def _work(name: str, a):
     if name == "llmfp8_fp8_gemm" or name == "llmfp8_mxfp8_gemm":
         return "flop", 2.0 * a[11] * a[12] * a[13]
+    if name == "llmfp8_fp8_gemm_res" or name == "llmfp8_mxfp8_gemm_res":
+        return "flop", 2.0 * a[10] * a[11] * a[12]
     if name == "llmfp8_quant_cast_amax":
         return "byte", 3.0 * a[2]
+    if name == "llmfp8_quant_cast_amax_2d":
+        return "byte", 3.0 * a[3] * a[4]
     if name == "llmfp8_quant_cast_amax_bgrad":
         return "byte", 3.0 * a[2] * a[3]
     if name == "llmfp8_rmsnorm_quant_fwd":
         return "byte", 3.0 * a[4] * a[5] + 4.0 * a[4]
     if name == "llmfp8_rmsnorm_bwd":
         return "byte", 6.0 * a[7] * a[8]
+    if name == "llmfp8_rmsnorm_bwd_add":
+        return "byte", 8.0 * a[8] * a[9]
     if name == "llmfp8_rmsnorm_rsigma":
         return "byte", 2.0 * a[2] * a[3]
     if name == "llmfp8_swiglu_quant_fwd":
@@ -88,6 +99,9 @@ def _work(name: str, a):
     if name == "llmfp8_mx_quantize":
         rc = float(a[1]) * a[2]
         return "byte", 2.0 * rc + (rc + rc / 32) * ((a[3] is not None) + (a[5] is not None))
+    if name == "llmfp8_mx_quantize_ld":
+        rc = float(a[2]) * a[3]
+        return "byte", 2.0 * rc + (rc + rc / 32) * ((a[4] is not None) + (a[6] is not None))
     return "none", 0.0
 
 

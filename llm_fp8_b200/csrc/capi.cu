@@ -95,17 +95,18 @@ int make_tensor_map_3d(CUtensorMap* map, const void* base, CUtensorMapDataType d
 
 // kernels (defined in the other translation units)
 int launch_cast_amax(const void*, void*, int64_t, int, const float*, float*, cudaStream_t);
+int launch_cast_amax_2d(const void*, int64_t, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
 int launch_cast_amax_bgrad(const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
 int launch_amax_scale_update(float*, float*, float*, const float*, int, int, int, cudaStream_t);
 int launch_rmsnorm_quant_fwd(const void*, const void*, void*, float*, int64_t, int64_t, float, int, const float*, float*, cudaStream_t);
 int launch_rmsnorm_rsigma(const void*, float*, int64_t, int64_t, float, cudaStream_t);
-int launch_rmsnorm_bwd(const void*, const void*, const void*, const float*, void*, void*, float*, int64_t, int64_t, cudaStream_t);
+int launch_rmsnorm_bwd(const void*, const void*, const void*, const float*, const void*, void*, void*, float*, int64_t, int64_t, cudaStream_t);
 int rmsnorm_bwd_grid(int64_t);
 int launch_swiglu_quant_fwd(const void*, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
 int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
-int launch_mx_quantize(const void*, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
+int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
 int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
-                    const void*, const void*, const void*, int, int, cudaStream_t);
+                    const void*, const void*, const void*, const void*, int64_t, int, int, cudaStream_t);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
@@ -125,6 +126,9 @@ uint64_t llmfp8_launch_count(void) { return g_launches.load(std::memory_order_re
 int llmfp8_quant_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* scale, float* amax, void* stream) {
     return launch_cast_amax(x, q, n, fmt, scale, amax, S(stream));
 }
+int llmfp8_quant_cast_amax_2d(const void* x, int64_t ldx, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax, void* stream) {
+    return launch_cast_amax_2d(x, ldx, q, rows, cols, fmt, scale, amax, S(stream));
+}
 int llmfp8_quant_cast_amax_bgrad(const void* x, void* q, int64_t rows, int64_t cols, int fmt, const float* scale, float* amax, float* colsum_ws,
                                  void* bgrad, void* stream) {
     return launch_cast_amax_bgrad(x, q, rows, cols, fmt, scale, amax, colsum_ws, bgrad, S(stream));
@@ -135,7 +139,11 @@ int llmfp8_rmsnorm_quant_fwd(const void* x, const void* gamma, void* q, float* r
 }
 int llmfp8_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const float* rsigma, void* dx, void* dgamma, float* ws, int64_t M, int64_t H,
                        void* stream) {
-    return launch_rmsnorm_bwd(dy, x, gamma, rsigma, dx, dgamma, ws, M, H, S(stream));
+    return launch_rmsnorm_bwd(dy, x, gamma, rsigma, nullptr, dx, dgamma, ws, M, H, S(stream));
+}
+int llmfp8_rmsnorm_bwd_add(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma, float* ws,
+                           int64_t M, int64_t H, void* stream) {
+    return launch_rmsnorm_bwd(dy, x, gamma, rsigma, dres, dx, dgamma, ws, M, H, S(stream));
 }
 int llmfp8_rmsnorm_bwd_ws_rows(int64_t M) { return rmsnorm_bwd_grid(M); }
 int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream) {
@@ -151,7 +159,11 @@ int llmfp8_amax_scale_update(float* amax_history, float* scale, float* scale_inv
 }
 int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
                        const void* gamma, void* stream) {
-    return launch_mx_quantize(x, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+    return launch_mx_quantize(x, cols, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+}
+int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                          const float* rsigma, const void* gamma, void* stream) {
+    return launch_mx_quantize(x, ldx, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
 }
 int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream) {
     return launch_rmsnorm_rsigma(x, rsigma, M, H, eps, S(stream));
@@ -164,7 +176,17 @@ int llmfp8_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
                     int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, int accumulate, int max_ctas,
                     void* stream) {
     return launch_fp8_gemm(a, lda, a_fmt, a_mn, b, ldb, b_fmt, b_mn, d, ldd, out_fp32, M, N, K, a_scale_inv, b_scale_inv, nullptr, nullptr, bias,
-                           accumulate, max_ctas, S(stream));
+                           nullptr, 0, accumulate, max_ctas, S(stream));
+}
+int llmfp8_fp8_gemm_res(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd, int M,
+                        int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, const void* residual, int64_t ldr,
+                        int max_ctas, void* stream) {
+    if (!residual) {
+        set_error("fp8_gemm_res: residual is required (use llmfp8_fp8_gemm otherwise)");
+        return -1;
+    }
+    return launch_fp8_gemm(a, lda, a_fmt, a_mn, b, ldb, b_fmt, b_mn, d, ldd, 0, M, N, K, a_scale_inv, b_scale_inv, nullptr, nullptr, bias, residual, ldr,
+                           0, max_ctas, S(stream));
 }
 void llmfp8_gemm_force_bn(int bn) { gemm_force_bn(bn); }
 void llmfp8_gemm_force_cg(int cg) { gemm_force_cg(cg); }
@@ -176,7 +198,16 @@ int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, con
         return -1;
     }
     return launch_fp8_gemm(a, lda, LLMFP8_E4M3, a_mn, b, ldb, LLMFP8_E4M3, b_mn, d, ldd, out_fp32, M, N, K, nullptr, nullptr, sfa, sfb, bias,
-                           accumulate, max_ctas, S(stream));
+                           nullptr, 0, accumulate, max_ctas, S(stream));
+}
+int llmfp8_mxfp8_gemm_res(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
+                          int64_t ldd, int M, int N, int K, const void* bias, const void* residual, int64_t ldr, int max_ctas, void* stream) {
+    if (!sfa || !sfb || !residual) {
+        set_error("mxfp8_gemm_res: scale tensors and residual are required");
+        return -1;
+    }
+    return launch_fp8_gemm(a, lda, LLMFP8_E4M3, a_mn, b, ldb, LLMFP8_E4M3, b_mn, d, ldd, 0, M, N, K, nullptr, nullptr, sfa, sfb, bias, residual, ldr, 0,
+                           max_ctas, S(stream));
 }
 
 }  // extern "C"

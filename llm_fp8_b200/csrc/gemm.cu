@@ -52,6 +52,8 @@ struct GemmParams {
     const float* a_scale_inv;   // per-tensor only
     const float* b_scale_inv;
     const void* bias;           // bf16 [N] or null
+    const void* residual;       // bf16 [M, N] (leading dimension ldr) added in fp32 before the bf16 rounding, or null (bf16 output, staged path)
+    int64_t ldr;
     int accumulate;             // D += result
     int out_fp32;               // 0: bf16 output, 1: fp32 output
     uint32_t idesc;
@@ -113,7 +115,9 @@ __device__ __forceinline__ void tma3d(const CUtensorMap* m, uint64_t* bar, uint3
     else ptx::tma_load_3d_cg2(m, bar_leader, dst, c0, c1, c2);
 }
 
-template <int CG, bool A_MN, bool B_MN, bool MX>
+// RES: fused residual add in the staged bf16 epilogue (fprop layouts only) — a separate instantiation so the 32 prefetch registers
+// it needs never weigh on the plain kernels.
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_sfa,
                 const __grid_constant__ CUtensorMap map_sfb, const __grid_constant__ CUtensorMap map_d, const GemmParams p) {
@@ -356,6 +360,15 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     uint32_t r0[32], r1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
                     if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
+                    // fused residual: this lane's 128 B row segment of R, requested while the TMEM load is in flight
+                    uint4 rv[RES ? 8 : 1];
+                    if constexpr (RES) {
+                        const int row = row0 + lane;
+                        const uint16_t* rp = static_cast<const uint16_t*>(p.residual) + static_cast<int64_t>(row) * p.ldr + col;
+#pragma unroll
+                        for (int g = 0; g < 8; g++)
+                            rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
+                    }
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
                     ptx::tmem_ld_wait();
                     if (c + 2 >= nchunks) release_acc(acc);           // this warp's share of the accumulator is in registers
@@ -385,6 +398,12 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                     unpack8(__ldg(reinterpret_cast<const uint4*>(static_cast<const uint16_t*>(p.bias) + col + g * 8)), bf);
 #pragma unroll
                                     for (int j = 0; j < 8; j++) v[j] += bf[j];
+                                }
+                                if constexpr (RES) {
+                                    float rf[8];
+                                    unpack8(rv[g], rf);
+#pragma unroll
+                                    for (int j = 0; j < 8; j++) v[j] += rf[j];
                                 }
                                 uint4 o;
                                 o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
@@ -500,10 +519,10 @@ void gemm_debug(int d) { g_debug = d; }
 void gemm_force_bn(int bn) { g_bn_override = bn; }
 void gemm_force_cg(int cg) { g_cg_override = cg; }
 
-template <int CG, bool A_MN, bool B_MN, bool MX>
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false>
 static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
                           const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX>;
+    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES>;
     static bool configured = false;   // benign race: the attribute call is idempotent
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
@@ -531,6 +550,11 @@ static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CU
 template <int CG>
 static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb,
                     const CUtensorMap& md, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
+    if (p.residual) {
+        if (a_mn || b_mn) { set_error("fp8_gemm: the fused residual is built for the fprop layout only (A, B K-major)"); return -1; }
+        if (mx) return launch_variant<CG, false, false, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        return launch_variant<CG, false, false, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    }
     if (!mx) {
         if (!a_mn && !b_mn) return launch_variant<CG, false, false, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
         if (!a_mn && b_mn) return launch_variant<CG, false, true, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
@@ -572,8 +596,11 @@ int make_tensor_map_3d(CUtensorMap* map, const void* base, CUtensorMapDataType d
 // a: fp8 bytes. !a_mn: stored [M, K] (lda = row pitch in bytes >= K);  a_mn: stored [K, M] (lda >= M).  Same for b with N.
 int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void* b, int64_t ldb, int b_fmt, int b_mn, void* d, int64_t ldd,
                     int out_fp32, int M, int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* sfa, const void* sfb,
-                    const void* bias, int accumulate, int max_ctas, cudaStream_t stream) {
+                    const void* bias, const void* residual, int64_t ldr, int accumulate, int max_ctas, cudaStream_t stream) {
     const bool mx = sfa != nullptr || sfb != nullptr;
+    LLMFP8_REQUIRE(!residual || (!accumulate && !out_fp32), "fp8_gemm: a fused residual needs a bf16 output without accumulate");
+    LLMFP8_REQUIRE(!residual || (ldr % 8 == 0 && ldr >= N && reinterpret_cast<uintptr_t>(residual) % 16 == 0 && residual != d),
+                   "fp8_gemm: residual must be 16 B aligned, distinct from D, with ldr %% 8 == 0 and ldr >= N (ldr=%lld)", (long long)ldr);
     LLMFP8_REQUIRE(M > 0 && N > 0 && K > 0, "fp8_gemm: empty problem M=%d N=%d K=%d", M, N, K);
     LLMFP8_REQUIRE((a_fmt == FMT_E4M3 || a_fmt == FMT_E5M2) && (b_fmt == FMT_E4M3 || b_fmt == FMT_E5M2), "fp8_gemm: bad operand formats");
     LLMFP8_REQUIRE(mx ? (sfa && sfb) : (a_scale_inv && b_scale_inv), "fp8_gemm: %s", mx ? "MX needs both scale tensors" : "per-tensor needs both scale_inv pointers");
@@ -597,7 +624,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
 
     GemmParams p;
     p.d = d; p.ldd = ldd; p.M = M; p.N = N; p.K = K;
-    p.a_scale_inv = a_scale_inv; p.b_scale_inv = b_scale_inv; p.bias = bias; p.accumulate = accumulate; p.out_fp32 = out_fp32;
+    p.a_scale_inv = a_scale_inv; p.b_scale_inv = b_scale_inv; p.bias = bias; p.residual = residual; p.ldr = ldr; p.accumulate = accumulate; p.out_fp32 = out_fp32;
     p.idesc = mx ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN, 0, 0) : ptx::make_idesc_f8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN);
     p.bn = BN;
     p.debug = g_debug;

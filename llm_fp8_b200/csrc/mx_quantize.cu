@@ -211,18 +211,20 @@ __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant_
 }
 
 // sf_row: u8 [ceil(R/128)*128 * ceil(C/128)*4]; sf_col: u8 [ceil(C/128)*128 * ceil(R/128)*4]
-int launch_mx_quantize(const void* x, int64_t R, int64_t C, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
+// ldx: row pitch of x in elements (>= C, multiple of 8): a column slice of a wider matrix is quantised in place, without a copy
+int launch_mx_quantize(const void* x, int64_t ldx, int64_t R, int64_t C, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
                        const void* gamma, cudaStream_t stream) {
     const int do_row = q_row != nullptr, do_col = q_col != nullptr;
     LLMFP8_REQUIRE(do_row || do_col, "mx_quantize: nothing to produce");
     LLMFP8_REQUIRE(!do_row || (C % 32 == 0 && sf_row), "mx_quantize: rowwise needs cols %% 32 == 0 (got %lld) and a scale buffer", (long long)C);
     LLMFP8_REQUIRE(!do_col || (R % 32 == 0 && sf_col), "mx_quantize: colwise needs rows %% 32 == 0 (got %lld) and a scale buffer", (long long)R);
     LLMFP8_REQUIRE(C % 16 == 0, "mx_quantize: cols %lld must be a multiple of 16", (long long)C);
+    LLMFP8_REQUIRE(ldx >= C && ldx % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0, "mx_quantize: row pitch %lld must be >= cols, a multiple of 8, x 16 B aligned", (long long)ldx);
     LLMFP8_REQUIRE((rsigma == nullptr) == (gamma == nullptr), "mx_quantize: rsigma and gamma go together");
     LLMFP8_REQUIRE(R < (1ll << 31) && C < (1ll << 31), "mx_quantize: dims too large");
     if (R == 0 || C == 0) return 0;
     CUtensorMap m_in, m_row, m_col;
-    int rc = make_tensor_map_2d(&m_in, x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, C, R, C * 2, MXT, MXT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    int rc = make_tensor_map_2d(&m_in, x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, C, R, ldx * 2, MXT, MXT, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
     rc = make_tensor_map_2d(&m_row, do_row ? q_row : q_col, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, C, R, C, MXT, MXT, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;

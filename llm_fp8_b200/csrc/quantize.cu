@@ -60,6 +60,63 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
     return 0;
 }
 
+// K2 on a column slice: x is [R, C] with row pitch ldx elements (a view into a wider matrix), q is dense [R, C].
+// Same unit mapping as the flat kernel over the DENSE index space; only the load address carries the pitch.
+template <int FMT, int UNROLL>
+__global__ void __launch_bounds__(256) cast_amax_2d_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, uint32_t nunits, uint32_t cvec,
+                                                           int64_t ldvec, const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    __shared__ float red[8];
+    const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
+    const f32x2 scale2 = pk2(scale, scale);
+    float m = 0.f;
+    const uint32_t base = blockIdx.x * (256u * UNROLL) + threadIdx.x;
+    uint4 v[UNROLL];
+    {
+        uint32_t row = base / cvec, c = base - row * cvec;
+#pragma unroll
+        for (int u = 0; u < UNROLL; u++) {
+            if (base + u * 256u < nunits) v[u] = ldg_stream(x + static_cast<int64_t>(row) * ldvec + c);
+            c += 256u;
+            while (c >= cvec) { c -= cvec; row++; }
+        }
+    }
+#pragma unroll
+    for (int u = 0; u < UNROLL; u++) {
+        if (base + u * 256u < nunits) {
+            float f[8];
+            unpack8(v[u], f);
+            uint32_t h[4];
+#pragma unroll
+            for (int k = 0; k < 4; k++) {
+                m = fmaxf(m, fmaxf(fabsf(f[2 * k]), fabsf(f[2 * k + 1])));
+                float lo, hi;
+                upk2(mul2(pk2(f[2 * k], f[2 * k + 1]), scale2), lo, hi);
+                h[k] = cvt_fp8x2<FMT>(lo, hi);
+            }
+            q[base + u * 256u] = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
+        }
+    }
+    if (amax) block_amax_to_global(m, red, amax);
+}
+
+int launch_cast_amax_2d(const void* x, int64_t ldx, void* q, int64_t R, int64_t C, int fmt, const float* scale, float* amax, cudaStream_t stream) {
+    if (ldx == C) return launch_cast_amax(x, q, R * C, fmt, scale, amax, stream);
+    LLMFP8_REQUIRE(C % 16 == 0 && ldx % 8 == 0 && ldx > C, "cast_amax_2d: cols %lld must be a multiple of 16, pitch %lld a multiple of 8 and >= cols", (long long)C, (long long)ldx);
+    LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) % 16 == 0, "cast_amax_2d: pointers must be 16 B aligned");
+    LLMFP8_REQUIRE(fmt == FMT_E4M3 || fmt == FMT_E5M2, "cast_amax_2d: bad fp8 format %d", fmt);
+    if (R == 0 || C == 0) return 0;
+    const int64_t nunits = R * (C / 8);
+    LLMFP8_REQUIRE(nunits < (int64_t(1) << 31), "cast_amax_2d: tensor too large (%lld x %lld)", (long long)R, (long long)C);
+    constexpr int UNROLL = 8;
+    const int grid = static_cast<int>((nunits + 256 * UNROLL - 1) / (256 * UNROLL));
+    if (fmt == FMT_E4M3)
+        cast_amax_2d_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
+    else
+        cast_amax_2d_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
+    LLMFP8_LAUNCH_CHECK("cast_amax_2d");
+    return 0;
+}
+
 // ------------------------------------------------------------------------------------------- K2b
 // CTA = 256 threads = 32 column-vectors (8 bf16 each: 256 columns, 512 B contiguous per row) x 8 row lanes.
 // A CTA walks `rows_per_cta` rows of its 256-column strip, keeping 8 fp32 column sums per thread, then folds the

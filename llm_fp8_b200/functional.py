@@ -58,6 +58,13 @@ def _2d(x: torch.Tensor) -> torch.Tensor:
     return x.reshape(-1, x.shape[-1])
 
 
+def _rows(x: torch.Tensor) -> torch.Tensor:
+    """[..., C] -> [R, C] readable by the strided quantisers: a column slice of a wider matrix (the query slice of a fused qkv
+    output, an attention core's strided output) stays a view — no copy; anything else is made contiguous."""
+    x2 = _2d(x)
+    return x2 if (x2.is_contiguous() or ops.rows_ok(x2)) else x2.contiguous()
+
+
 def _wgrad(dyq, xq, N, K, T, weight):
     """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
     return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
@@ -66,14 +73,17 @@ def _wgrad(dyq, xq, N, K, T, weight):
 # ====================================================================================== per-tensor (DelayedScaling)
 class LinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, meta: Fp8Meta, recipe: DelayedScaling, ln_weight, eps, is_grad_enabled):
-        """ln_weight None: plain Linear; else LayerNormLinear (RMSNorm fused into the input cast)."""
+    def forward(ctx, x, weight, bias, meta: Fp8Meta, recipe: DelayedScaling, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False):
+        """ln_weight None: plain Linear; else LayerNormLinear (RMSNorm fused into the input cast).
+        residual [.., N]: y = residual + x W^T (+b), added in the GEMM epilogue; its gradient is dy itself.
+        passthrough: also return an alias of x, so that the gradient of a residual branch taken from it arrives here and is folded
+        into the RMSNorm backward instead of costing an accumulation pass."""
         dev = x.device
         s = meta.get(recipe, dev)
         Fp8Meta.begin_fwd(s, is_grad_enabled)
         pf, f0 = s["pf"], s["f0"]
         ff = fwd_fmt(recipe.fp8_format)
-        x2 = _2d(x).contiguous()
+        x2 = _2d(x).contiguous() if ln_weight is not None else _rows(x)
         M, K = x2.shape
         N = weight.shape[0]
         rsigma = None
@@ -82,7 +92,7 @@ class LinearFn(torch.autograd.Function):
         else:
             xq = ops.quantize(x2, ff, pf, f0 + 0)
         wq = ops.quantize(weight, ff, pf, f0 + 1)
-        y = ops.fp8_gemm(xq, False, wq, False, M, N, K, bias=bias)
+        y = ops.fp8_gemm(xq, False, wq, False, M, N, K, bias=bias, residual=_rows(residual) if residual is not None else None)
         if is_grad_enabled:
             ctx.save_for_backward(xq.data, wq.data, x2 if ln_weight is not None else None, ln_weight, rsigma)
             ctx.meta, ctx.recipe, ctx.slots = meta, recipe, s
@@ -91,10 +101,15 @@ class LinearFn(torch.autograd.Function):
             ctx.dims = (M, N, K)
             ctx.wdtype = weight.dtype
             ctx.needs = (x.requires_grad, weight.requires_grad)
-        return y.reshape(*x.shape[:-1], N)
+            ctx.has_residual = residual is not None
+        ctx.set_materialize_grads(False)
+        y = y.reshape(*x.shape[:-1], N)
+        return (y, x.view_as(x)) if passthrough else y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dres=None):
+        if dy is None:                       # only the pass-through alias was used downstream
+            return (dres,) + (None,) * 9
         xq_d, wq_d, x2, ln_weight, rsigma = ctx.saved_tensors
         s, recipe = ctx.slots, ctx.recipe
         M, N, K = ctx.dims
@@ -113,14 +128,17 @@ class LinearFn(torch.autograd.Function):
         dw = ops.fp8_gemm(dyq, True, xq, True, N, K, M, out_dtype=ctx.wdtype)   # wgrad: contraction over tokens
         dgamma = None
         if ln_weight is not None:
-            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma)
+            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
+        elif dres is not None:
+            dx = dx + _2d(dres)
         Fp8Meta.end_bwd(s)
-        return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None
+        return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None, (dy if ctx.has_residual else None), None
 
 
 class LayerNormMLPFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, ln_weight, w1, b1, w2, b2, meta: Fp8Meta, recipe: DelayedScaling, eps, is_grad_enabled):
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, meta: Fp8Meta, recipe: DelayedScaling, eps, is_grad_enabled, residual=False):
+        """residual=True: returns x + MLP(x) — the add rides in the fc2 GEMM epilogue, its gradient in the RMSNorm backward."""
         dev = x.device
         s = meta.get(recipe, dev)
         Fp8Meta.begin_fwd(s, is_grad_enabled)
@@ -135,10 +153,11 @@ class LayerNormMLPFn(torch.autograd.Function):
         fc1 = ops.fp8_gemm(lnq, False, w1q, False, M, I2, H, bias=b1)
         aq = ops.swiglu_quant(fc1, ff, pf, f0 + 3)
         w2q = ops.quantize(w2, ff, pf, f0 + 4)
-        y = ops.fp8_gemm(aq, False, w2q, False, M, H, I, bias=b2)
+        y = ops.fp8_gemm(aq, False, w2q, False, M, H, I, bias=b2, residual=x2 if residual else None)
         if is_grad_enabled:
             ctx.save_for_backward(x2, ln_weight, rsigma, lnq.data, w1q.data, fc1, aq.data, w2q.data)
             ctx.recipe, ctx.slots = recipe, s
+            ctx.residual = residual
             ctx.has_bias = b1 is not None
             ctx.shape = x.shape
             ctx.dims = (M, H, I)
@@ -168,9 +187,9 @@ class LayerNormMLPFn(torch.autograd.Function):
         dw2 = ops.fp8_gemm(dyq, True, aq, True, H, I, M, out_dtype=ctx.wdtype)   # fc2 wgrad
         dln = ops.fp8_gemm(dfc1q, False, w1q, True, M, H, 2 * I)                 # fc1 dgrad
         dw1 = ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype)   # fc1 wgrad
-        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma)
+        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
         Fp8Meta.end_bwd(s)
-        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None
 
 
 # ====================================================================================== MXFP8
@@ -182,8 +201,9 @@ def _mx_bgrad(dy2: torch.Tensor) -> torch.Tensor:
 
 class MXLinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, ln_weight, eps, is_grad_enabled):
-        x2 = _2d(x).contiguous()
+    def forward(ctx, x, weight, bias, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False):
+        """residual / passthrough: as LinearFn.forward."""
+        x2 = _2d(x).contiguous() if ln_weight is not None else _rows(x)
         M, K = x2.shape
         N = weight.shape[0]
         rsigma = None
@@ -193,15 +213,21 @@ class MXLinearFn(torch.autograd.Function):
         else:
             xq = ops.mx_quantize(x2, True, is_grad_enabled)
         wq = ops.mx_quantize(weight, True, is_grad_enabled)
-        y = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, bias=bias)
+        y = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, bias=bias,
+                           residual=_rows(residual) if residual is not None else None)
         if is_grad_enabled:
             ctx.save_for_backward(xq.col, xq.sf_col, wq.col, wq.sf_col, x2 if ln_weight is not None else None, ln_weight, rsigma)
             ctx.has_bias = bias is not None
             ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, N, K), weight.dtype
-        return y.reshape(*x.shape[:-1], N)
+            ctx.has_residual = residual is not None
+        ctx.set_materialize_grads(False)
+        y = y.reshape(*x.shape[:-1], N)
+        return (y, x.view_as(x)) if passthrough else y
 
     @staticmethod
-    def backward(ctx, dy):
+    def backward(ctx, dy, dres=None):
+        if dy is None:                       # only the pass-through alias was used downstream
+            return (dres,) + (None,) * 7
         x_col, x_sfc, w_col, w_sfc, x2, ln_weight, rsigma = ctx.saved_tensors
         M, N, K = ctx.dims
         dy2 = _2d(dy).contiguous()
@@ -213,8 +239,10 @@ class MXLinearFn(torch.autograd.Function):
         dw = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out_dtype=ctx.wdtype)
         dgamma = None
         if ln_weight is not None:
-            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma)
-        return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None
+            dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
+        elif dres is not None:
+            dx = dx + _2d(dres)
+        return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None, (dy if ctx.has_residual else None), None
 
 
 class MXLayerNormMLPFn(torch.autograd.Function):
@@ -222,7 +250,7 @@ class MXLayerNormMLPFn(torch.autograd.Function):
     reads (one extra bf16 round trip compared with a fully fused activation+MX quantiser: DESIGN.md 'next')."""
 
     @staticmethod
-    def forward(ctx, x, ln_weight, w1, b1, w2, b2, eps, is_grad_enabled):
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, eps, is_grad_enabled, residual=False):
         x2 = _2d(x).contiguous()
         M, H = x2.shape
         I2 = w1.shape[0]
@@ -235,10 +263,11 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         a = ops.swiglu_bf16(fc1)
         aq = ops.mx_quantize(a, True, g)
         w2q = ops.mx_quantize(w2, True, g)
-        y = ops.mxfp8_gemm(aq.row, aq.sf_row, False, w2q.row, w2q.sf_row, False, M, H, I, bias=b2)
+        y = ops.mxfp8_gemm(aq.row, aq.sf_row, False, w2q.row, w2q.sf_row, False, M, H, I, bias=b2, residual=x2 if residual else None)
         if g:
             ctx.save_for_backward(x2, ln_weight, rsigma, lnq.col, lnq.sf_col, w1q.col, w1q.sf_col, fc1, aq.col, aq.sf_col, w2q.col, w2q.sf_col)
             ctx.has_bias = b1 is not None
+            ctx.residual = residual
             ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, H, I), w1.dtype
         return y.reshape(x.shape)
 
@@ -255,5 +284,5 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         dw2 = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype)      # fc2 wgrad
         dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad
         dw1 = ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype)  # fc1 wgrad
-        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma)
-        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None
+        dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None

@@ -10,6 +10,7 @@ data-parallel tests run stacks of it; the full block with a real attention core 
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -48,12 +49,34 @@ def linear_params_per_layer(H: int, I: int, heads: int, kv: int, hd: int) -> int
     return (heads * hd + 2 * kv * hd) * H + H * heads * hd + 2 * I * H + H * I
 
 
+class _QuerySlice(torch.autograd.Function):
+    """The attention-core stand-in: context = the query columns of the fused qkv output, handed on as a VIEW (the proj quantiser
+    reads it through its row pitch, no copy).  Backward writes dq next to a zero dk|dv block with one vectorised concat instead
+    of autograd's zero-fill + strided copy — a real attention backward would emit the whole [M, q+2kv] gradient itself."""
+
+    @staticmethod
+    def forward(ctx, qkv, q_out):
+        ctx.rest = qkv.shape[-1] - q_out
+        return qkv[..., :q_out]
+
+    @staticmethod
+    def backward(ctx, dq):
+        if ctx.rest == 0:
+            return dq, None
+        return torch.cat((dq, dq.new_zeros(*dq.shape[:-1], ctx.rest)), dim=-1), None
+
+
 class DecoderLinearPath(nn.Module):
+    """`fuse_residual` (default on; LLMFP8_FUSE_RESIDUAL=0 turns it off): the two residual adds ride in the proj / fc2 GEMM epilogues
+    and their gradients in the RMSNorm backward kernels — four [M, H] elementwise passes per layer fewer than the plain
+    `h = h + f(h)` form, which stays available as the reference-shaped path (what te_llama.py:78, 81 spell out)."""
+
     def __init__(self, H: int, I: int, heads: int, kv: int, hd: int, attn_recipe: Recipe, mlp_recipe: Recipe, rms_eps: float = 1e-5,
-                 params_dtype: torch.dtype = torch.bfloat16, device=None):
+                 params_dtype: torch.dtype = torch.bfloat16, device=None, fuse_residual: Optional[bool] = None):
         super().__init__()
         q_out, kv_out = heads * hd, kv * hd
         self.q_out = q_out
+        self.fuse_residual = (os.environ.get("LLMFP8_FUSE_RESIDUAL", "1") != "0") if fuse_residual is None else fuse_residual
         self.attn_recipe, self.mlp_recipe = attn_recipe, mlp_recipe
         # same constructor arguments the reference passes (te_llama.py:45-63): attention without bias and with the model's eps,
         # LayerNormMLP with the TE defaults (bias=True, eps=1e-5)
@@ -64,9 +87,15 @@ class DecoderLinearPath(nn.Module):
         self.layernorm_mlp = LayerNormMLP(H, I, normalization="RMSNorm", activation="swiglu", params_dtype=params_dtype, device=device)
 
     def forward(self, h: torch.Tensor, fp8_group=None) -> torch.Tensor:
+        if self.fuse_residual:
+            with fp8_autocast(enabled=True, fp8_recipe=self.attn_recipe, fp8_group=fp8_group):
+                qkv, h_res = self.layernorm_qkv(h, return_input=True)
+                h = self.proj(_QuerySlice.apply(qkv, self.q_out), residual=h_res)
+            with fp8_autocast(enabled=True, fp8_recipe=self.mlp_recipe, fp8_group=fp8_group):
+                return self.layernorm_mlp(h, add_residual=True)
         with fp8_autocast(enabled=True, fp8_recipe=self.attn_recipe, fp8_group=fp8_group):
             qkv = self.layernorm_qkv(h)
-            a = self.proj(qkv[..., : self.q_out])
+            a = self.proj(_QuerySlice.apply(qkv, self.q_out))
         h = h + a
         with fp8_autocast(enabled=True, fp8_recipe=self.mlp_recipe, fp8_group=fp8_group):
             f = self.layernorm_mlp(h)
@@ -76,7 +105,7 @@ class DecoderLinearPath(nn.Module):
 class LinearPathStack(nn.Module):
     """`layers` DecoderLinearPath blocks back to back (what a data-parallel rank runs per step)."""
 
-    def __init__(self, model: str, scenario: str, layers: Optional[int] = None, device=None, seed: int = 1234):
+    def __init__(self, model: str, scenario: str, layers: Optional[int] = None, device=None, seed: int = 1234, fuse_residual: Optional[bool] = None):
         super().__init__()
         H, I, heads, kv, hd, L = MODEL_SHAPES[model]
         self.H, self.I = H, I
@@ -84,7 +113,8 @@ class LinearPathStack(nn.Module):
         self.params_per_layer = linear_params_per_layer(H, I, heads, kv, hd)
         ar, mr = recipes_for(scenario)
         torch.manual_seed(seed)
-        self.layers = nn.ModuleList(DecoderLinearPath(H, I, heads, kv, hd, ar, mr, device=device) for _ in range(self.n_layers))
+        self.layers = nn.ModuleList(DecoderLinearPath(H, I, heads, kv, hd, ar, mr, device=device, fuse_residual=fuse_residual)
+                                    for _ in range(self.n_layers))
 
     def forward(self, h: torch.Tensor) -> torch.Tensor:
         for layer in self.layers:

@@ -79,14 +79,16 @@ class Linear(_Fp8Module):
             init_method(self.weight)
         self.bias = nn.Parameter(torch.zeros(out_features, dtype=dtype, device=device)) if bias else None
 
-    def forward(self, inp: torch.Tensor, is_first_microbatch=None) -> torch.Tensor:
+    def forward(self, inp: torch.Tensor, is_first_microbatch=None, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """`residual` (an extension over the TE surface): returns residual + Linear(inp), the add fused into the GEMM epilogue —
+        the `h + proj(...)` of TELlamaDecoderLayer.forward (te_llama.py:78) without the separate elementwise pass."""
         _check_active("Linear")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g)
+            return fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False)
         self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g)
+        return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False)
 
 
 class LayerNormLinear(_Fp8Module):
@@ -134,15 +136,17 @@ class LayerNormLinear(_Fp8Module):
         b = torch.cat([getattr(self, n + "bias") for n in self._split], dim=0) if self.use_bias else None
         return w, b
 
-    def forward(self, inp: torch.Tensor, is_first_microbatch=None) -> torch.Tensor:
+    def forward(self, inp: torch.Tensor, is_first_microbatch=None, return_input: bool = False):
+        """`return_input` (an extension over the TE surface): also returns an alias of `inp` to take the residual branch from; its
+        gradient then arrives in this module's backward and is folded into the RMSNorm backward kernel."""
         _check_active("LayerNormLinear")
         recipe = get_fp8_recipe()
         w, b = self._weight_bias()
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g)
+            return fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input)
         self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g)
+        return fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input)
 
 
 class LayerNormMLP(_Fp8Module):
@@ -171,15 +175,18 @@ class LayerNormMLP(_Fp8Module):
         self.fc1_bias = nn.Parameter(torch.zeros(2 * ffn_hidden_size, dtype=dtype, device=device)) if bias else None
         self.fc2_bias = nn.Parameter(torch.zeros(hidden_size, dtype=dtype, device=device)) if bias else None
 
-    def forward(self, inp: torch.Tensor, is_first_microbatch=None) -> torch.Tensor:
+    def forward(self, inp: torch.Tensor, is_first_microbatch=None, add_residual: bool = False) -> torch.Tensor:
+        """`add_residual` (an extension over the TE surface): returns inp + MLP(inp) — the `h + layernorm_mlp(h)` of
+        TELlamaDecoderLayer.forward (te_llama.py:81) with the add in the fc2 GEMM epilogue and its gradient in the RMSNorm backward."""
         _check_active("LayerNormMLP")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g)
+            return fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g,
+                                             add_residual)
         self._apply_extra_state(recipe, inp.device)
         return fn.LayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self._meta,
-                                       recipe, self.eps, g)
+                                       recipe, self.eps, g, add_residual)
 
 
 # ------------------------------------------------------------------------------------------ attention shell (SURVEY.md §8(f) rank 1)

@@ -28,6 +28,24 @@ def _req(t: torch.Tensor, dtype=None):
     return t
 
 
+def _req_rows(t: torch.Tensor, dtype=None):
+    """2D tensor whose rows are contiguous but may be spaced (a column slice of a wider matrix): -> (tensor, row pitch in elements).
+    Anything else is made contiguous by the caller."""
+    if not t.is_cuda:
+        raise RuntimeError("llm_fp8_b200 operates on CUDA tensors only (no CPU fallback)")
+    if dtype is not None and t.dtype != dtype:
+        raise RuntimeError(f"expected {dtype}, got {t.dtype}")
+    if t.dim() != 2 or t.stride(1) != 1 or t.stride(0) < t.shape[1] or t.stride(0) % 8 or t.data_ptr() % 16:
+        raise RuntimeError("llm_fp8_b200 needs a 2D tensor with contiguous, 16 B aligned rows")
+    return t, t.stride(0)
+
+
+def rows_ok(t: torch.Tensor) -> bool:
+    """True when `t` ([R, C]) can be read in place by the strided quantisers (else the caller makes it contiguous)."""
+    return (t.dim() == 2 and t.stride(1) == 1 and t.stride(0) >= t.shape[1] and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
+            and t.shape[1] % 16 == 0)
+
+
 @dataclass
 class QTensor:
     """Per-tensor-scaled fp8 matrix [rows, cols] (bytes) + where its dequant scale lives."""
@@ -61,7 +79,14 @@ def mx_scale_bytes(rows: int, k: int) -> int:
 
 # ------------------------------------------------------------------------------------------ per-tensor quantise
 def quantize(x: torch.Tensor, fmt: int, pool: ScalePool, slot: int) -> QTensor:
-    """K2 with the pool's scale; amax lands in the pool's history row 0."""
+    """K2 with the pool's scale; amax lands in the pool's history row 0.  A 2D x may be a column slice (spaced rows)."""
+    if x.dim() == 2 and not x.is_contiguous():
+        x, ldx = _req_rows(x, torch.bfloat16)
+        q = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+        rc = _lib.load().llmfp8_quant_cast_amax_2d(x.data_ptr(), ldx, q.data_ptr(), x.shape[0], x.shape[1], fmt, pool.scale_ptr(slot), pool.amax_ptr(slot),
+                                                   _stream(x))
+        _lib.check(rc, "quant_cast_amax_2d")
+        return QTensor(q, fmt, pool.scale_inv, slot)
     x = _req(x, torch.bfloat16)
     q = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
     rc = _lib.load().llmfp8_quant_cast_amax(x.data_ptr(), q.data_ptr(), x.numel(), fmt, pool.scale_ptr(slot), pool.amax_ptr(slot), _stream(x))
@@ -71,6 +96,13 @@ def quantize(x: torch.Tensor, fmt: int, pool: ScalePool, slot: int) -> QTensor:
 
 def quantize_raw(x: torch.Tensor, fmt: int, scale: Optional[torch.Tensor], amax: Optional[torch.Tensor]) -> torch.Tensor:
     """K2 with explicit device scalars (tests / benches)."""
+    if x.dim() == 2 and x.is_cuda and not x.is_contiguous():
+        x, ldx = _req_rows(x, torch.bfloat16)
+        q = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
+        rc = _lib.load().llmfp8_quant_cast_amax_2d(x.data_ptr(), ldx, q.data_ptr(), x.shape[0], x.shape[1], fmt, scale.data_ptr() if scale is not None else None,
+                                                   amax.data_ptr() if amax is not None else None, _stream(x))
+        _lib.check(rc, "quant_cast_amax_2d")
+        return q
     x = _req(x, torch.bfloat16)
     q = torch.empty(x.shape, dtype=torch.uint8, device=x.device)
     rc = _lib.load().llmfp8_quant_cast_amax(x.data_ptr(), q.data_ptr(), x.numel(), fmt, scale.data_ptr() if scale is not None else None,
@@ -133,15 +165,23 @@ def rmsnorm_rsigma(x, eps) -> torch.Tensor:
     return rs
 
 
-def rmsnorm_bwd(dy, x, gamma, rsigma) -> Tuple[torch.Tensor, torch.Tensor]:
+def rmsnorm_bwd(dy, x, gamma, rsigma, add: Optional[torch.Tensor] = None) -> Tuple[torch.Tensor, torch.Tensor]:
+    """K5.  `add` (bf16 [M, H]): the gradient of the residual branch around the norm, folded into dx in the same pass."""
     dy, x, gamma = _req(dy, torch.bfloat16), _req(x, torch.bfloat16), _req(gamma, torch.bfloat16)
     M, H = x.shape
     lib = _lib.load()
     dx = torch.empty_like(x)
     dgamma = torch.empty_like(gamma)
     ws = torch.empty(lib.llmfp8_rmsnorm_bwd_ws_rows(M) * H, dtype=torch.float32, device=x.device)
-    rc = lib.llmfp8_rmsnorm_bwd(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), rsigma.data_ptr(), dx.data_ptr(), dgamma.data_ptr(), ws.data_ptr(), M, H,
-                                _stream(x))
+    if add is not None:
+        add = _req(add, torch.bfloat16)
+        if add.numel() != x.numel():
+            raise RuntimeError("rmsnorm_bwd: residual gradient shape mismatch")
+        rc = lib.llmfp8_rmsnorm_bwd_add(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), rsigma.data_ptr(), add.data_ptr(), dx.data_ptr(), dgamma.data_ptr(),
+                                        ws.data_ptr(), M, H, _stream(x))
+    else:
+        rc = lib.llmfp8_rmsnorm_bwd(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), rsigma.data_ptr(), dx.data_ptr(), dgamma.data_ptr(), ws.data_ptr(), M, H,
+                                    _stream(x))
     _lib.check(rc, "rmsnorm_bwd")
     return dx, dgamma
 
@@ -193,7 +233,11 @@ def dswiglu_quant(da, fc1_out, fmt, pool: ScalePool, slot: int, want_dbias=True)
 # ------------------------------------------------------------------------------------------ MXFP8 quantise
 def mx_quantize(x: torch.Tensor, rowwise: bool = True, colwise: bool = True, rsigma: Optional[torch.Tensor] = None,
                 gamma: Optional[torch.Tensor] = None) -> MXTensor:
-    x = _req(x, torch.bfloat16)
+    if x.dim() == 2 and x.is_cuda and not x.is_contiguous():
+        x, ldx = _req_rows(x, torch.bfloat16)          # a column slice: the TMA descriptor carries the row pitch
+    else:
+        x = _req(x, torch.bfloat16)
+        ldx = x.shape[1]
     R, C = x.shape
     dev = x.device
     out = MXTensor(R, C)
@@ -203,7 +247,7 @@ def mx_quantize(x: torch.Tensor, rowwise: bool = True, colwise: bool = True, rsi
     if colwise:
         out.col = torch.empty((R, C), dtype=torch.uint8, device=dev)
         out.sf_col = torch.empty(mx_scale_bytes(C, R), dtype=torch.uint8, device=dev)
-    rc = _lib.load().llmfp8_mx_quantize(x.data_ptr(), R, C, out.row.data_ptr() if rowwise else None, out.sf_row.data_ptr() if rowwise else None,
+    rc = _lib.load().llmfp8_mx_quantize_ld(x.data_ptr(), ldx, R, C, out.row.data_ptr() if rowwise else None, out.sf_row.data_ptr() if rowwise else None,
                                         out.col.data_ptr() if colwise else None, out.sf_col.data_ptr() if colwise else None,
                                         rsigma.data_ptr() if rsigma is not None else None, gamma.data_ptr() if gamma is not None else None, _stream(x))
     _lib.check(rc, "mx_quantize")
@@ -212,8 +256,10 @@ def mx_quantize(x: torch.Tensor, rowwise: bool = True, colwise: bool = True, rsi
 
 # ------------------------------------------------------------------------------------------ GEMMs
 def fp8_gemm(a: QTensor, a_mn: bool, b: QTensor, b_mn: bool, M: int, N: int, K: int, bias: Optional[torch.Tensor] = None,
-             out: Optional[torch.Tensor] = None, accumulate: bool = False, out_dtype: torch.dtype = torch.bfloat16, max_ctas: int = 0) -> torch.Tensor:
-    """D[M,N] = A[M,K] B[N,K]^T * (a.scale_inv * b.scale_inv) (+bias) (+D).  a_mn / b_mn: operand stored [K, M] / [K, N]."""
+             out: Optional[torch.Tensor] = None, accumulate: bool = False, out_dtype: torch.dtype = torch.bfloat16, max_ctas: int = 0,
+             residual: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """D[M,N] = A[M,K] B[N,K]^T * (a.scale_inv * b.scale_inv) (+bias) (+D) (+residual[M,N], bf16, fused into the epilogue).
+    a_mn / b_mn: operand stored [K, M] / [K, N]."""
     dev = a.data.device
     if out is None:
         if accumulate:
@@ -223,6 +269,15 @@ def fp8_gemm(a: QTensor, a_mn: bool, b: QTensor, b_mn: bool, M: int, N: int, K: 
     if out.dtype not in (torch.bfloat16, torch.float32):
         raise RuntimeError("fp8_gemm output must be bf16 or fp32")
     lda, ldb = a.data.shape[-1], b.data.shape[-1]
+    if residual is not None:
+        residual, ldr = _req_rows(residual, torch.bfloat16)
+        if tuple(residual.shape) != (M, N) or out.dtype != torch.bfloat16 or accumulate:
+            raise RuntimeError("fp8_gemm: the fused residual needs a bf16 [M, N] residual, a bf16 output and no accumulate")
+        rc = _lib.load().llmfp8_fp8_gemm_res(a.data.data_ptr(), lda, a.fmt, int(a_mn), b.data.data_ptr(), ldb, b.fmt, int(b_mn), out.data_ptr(), out.stride(0),
+                                             M, N, K, a.scale_inv_ptr, b.scale_inv_ptr, bias.data_ptr() if bias is not None else None,
+                                             residual.data_ptr(), ldr, max_ctas, _stream(out))
+        _lib.check(rc, "fp8_gemm_res")
+        return out
     rc = _lib.load().llmfp8_fp8_gemm(a.data.data_ptr(), lda, a.fmt, int(a_mn), b.data.data_ptr(), ldb, b.fmt, int(b_mn), out.data_ptr(), out.stride(0),
                                      int(out.dtype == torch.float32), M, N, K, a.scale_inv_ptr, b.scale_inv_ptr,
                                      bias.data_ptr() if bias is not None else None, int(accumulate), max_ctas, _stream(out))
@@ -232,13 +287,22 @@ def fp8_gemm(a: QTensor, a_mn: bool, b: QTensor, b_mn: bool, M: int, N: int, K: 
 
 def mxfp8_gemm(a: torch.Tensor, sfa: torch.Tensor, a_mn: bool, b: torch.Tensor, sfb: torch.Tensor, b_mn: bool, M: int, N: int, K: int,
                bias: Optional[torch.Tensor] = None, out: Optional[torch.Tensor] = None, accumulate: bool = False,
-               out_dtype: torch.dtype = torch.bfloat16, max_ctas: int = 0) -> torch.Tensor:
+               out_dtype: torch.dtype = torch.bfloat16, max_ctas: int = 0, residual: Optional[torch.Tensor] = None) -> torch.Tensor:
     dev = a.device
     if out is None:
         if accumulate:
             raise RuntimeError("accumulate=True needs an output tensor")
         out = torch.empty((M, N), dtype=out_dtype, device=dev)
     _req(out)
+    if residual is not None:
+        residual, ldr = _req_rows(residual, torch.bfloat16)
+        if tuple(residual.shape) != (M, N) or out.dtype != torch.bfloat16 or accumulate:
+            raise RuntimeError("mxfp8_gemm: the fused residual needs a bf16 [M, N] residual, a bf16 output and no accumulate")
+        rc = _lib.load().llmfp8_mxfp8_gemm_res(a.data_ptr(), a.shape[-1], int(a_mn), sfa.data_ptr(), b.data_ptr(), b.shape[-1], int(b_mn), sfb.data_ptr(),
+                                               out.data_ptr(), out.stride(0), M, N, K, bias.data_ptr() if bias is not None else None,
+                                               residual.data_ptr(), ldr, max_ctas, _stream(out))
+        _lib.check(rc, "mxfp8_gemm_res")
+        return out
     rc = _lib.load().llmfp8_mxfp8_gemm(a.data_ptr(), a.shape[-1], int(a_mn), sfa.data_ptr(), b.data_ptr(), b.shape[-1], int(b_mn), sfb.data_ptr(),
                                        out.data_ptr(), out.stride(0), int(out.dtype == torch.float32), M, N, K,
                                        bias.data_ptr() if bias is not None else None, int(accumulate), max_ctas, _stream(out))

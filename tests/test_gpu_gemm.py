@@ -244,3 +244,53 @@ def test_gemm_full_shape_checksum(cg, force):
     want = (a.double().cuda().sum(0, keepdim=True) @ b.double().cuda().t()).cpu()[0]
     err = (colsum - want).abs().max().item() / want.abs().max().item()
     assert err < 1e-5, err
+
+
+# ------------------------------------------------------------------------------------------------ fused residual epilogue
+@pytest.mark.parametrize("cg,bn", [(0, 0), (1, 128), (1, 256), (2, 192), (2, 256)])
+def test_fp8_gemm_fused_residual(cg, bn, force):
+    """D = A B^T (+bias) + R with R a bf16 matrix read through its own leading dimension: partial tiles in M and N, R both dense and
+    as a column slice of a wider matrix.  One rounding (fp32 sum -> bf16), so the tolerance is the plain GEMM's."""
+    ops = _ops()
+    force(bn, cg)
+    M, N, K = 1000, 1544, 640
+    a, b = rand_fp8((M, K), E4M3, 61), rand_fp8((N, K), E4M3, 62)
+    g = torch.Generator().manual_seed(63)
+    bias = torch.randn(N, generator=g).bfloat16()
+    wide = (torch.randn(M, N + 72, generator=g) * 20).bfloat16()
+    base = ref_matmul(a.float() * 0.5, b.float() * 0.25)
+    A, B = qt(ops, a, E4M3, 0.5), qt(ops, b, E4M3, 0.25)
+    r_dense = wide[:, :N].contiguous()
+    got = ops.fp8_gemm(A, False, B, False, M, N, K, residual=r_dense.cuda())
+    check(got, base + r_dense.float())
+    r_view = wide.cuda()[:, 8:8 + N]                       # pitch N + 72, 16 B aligned start
+    got = ops.fp8_gemm(A, False, B, False, M, N, K, bias=bias.cuda(), residual=r_view)
+    check(got, base + bias.float() + wide[:, 8:8 + N].float())
+    # no residual given: the plain kernel still runs through the same wrapper
+    check(ops.fp8_gemm(A, False, B, False, M, N, K), base)
+
+
+def test_mxfp8_gemm_fused_residual_full_shape():
+    """Llama-3.1-8B proj fprop (M=6144, N=K=4096) with the residual: equals the unfused result + R up to one bf16 rounding."""
+    ops = _ops()
+    M, N, K = 6144, 4096, 4096
+    x, w = mx_operands(M, K, 71), mx_operands(N, K, 72)
+    g = torch.Generator().manual_seed(73)
+    r = torch.randn(M, N, generator=g).bfloat16().cuda()
+    xq, wq = ops.mx_quantize(x.cuda(), True, False), ops.mx_quantize(w.cuda(), True, False)
+    plain = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, out_dtype=torch.float32)
+    fused = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, residual=r)
+    want = (plain + r.float()).bfloat16()
+    assert torch.equal(fused, want), f"{(fused.float() - want.float()).abs().max().item()}"
+
+
+def test_fused_residual_contract_errors():
+    ops = _ops()
+    M, N, K = 128, 128, 128
+    a, b = rand_fp8((M, K), E4M3, 1), rand_fp8((N, K), E4M3, 2)
+    A, B = qt(ops, a, E4M3, 1.0), qt(ops, b, E4M3, 1.0)
+    r = torch.zeros(M, N, dtype=torch.bfloat16).cuda()
+    with pytest.raises(RuntimeError):
+        ops.fp8_gemm(A, False, B, False, M, N, K, residual=r, out_dtype=torch.float32)
+    with pytest.raises(RuntimeError):
+        ops.fp8_gemm(A, False, qt(ops, b.t().contiguous(), E4M3, 1.0), True, M, N, K, residual=r)     # dgrad layout: not built

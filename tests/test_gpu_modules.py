@@ -214,3 +214,35 @@ def test_decoder_layer_swap_runs():
                 assert p.grad is not None and torch.isfinite(p.grad.float()).all(), n
     finally:
         torch.set_default_dtype(old)
+
+
+@pytest.mark.parametrize("scenario", ["mxfp8", "default", "hybrid"])
+def test_decoder_linear_path_fused_residual_matches_plain(scenario):
+    """DecoderLinearPath with the residual adds fused (proj / fc2 GEMM epilogues, RMSNorm backward) against the plain
+    `h = h + f(h)` form with identical weights: same quantised operands, one bf16 rounding fewer per add — outputs and every
+    gradient agree to bf16 resolution.  The query slice reaches the proj quantiser as a strided view in both."""
+    import llm_fp8_b200 as te
+    from llm_fp8_b200.layer import DecoderLinearPath, recipes_for
+    H, I, heads, kv, hd = 512, 1024, 8, 2, 64
+    ar, mr = recipes_for(scenario)
+    x0 = rnd((2, 128, H), 21).cuda()
+    dy = rnd((2, 128, H), 22, 1e-1).cuda()
+    res = []
+    for fuse in (False, True):
+        te.reset_fp8_state()
+        torch.manual_seed(4)
+        layer = DecoderLinearPath(H, I, heads, kv, hd, ar, mr, device="cuda", fuse_residual=fuse)
+        with torch.no_grad():
+            layer.layernorm_mlp.fc1_bias.copy_(rnd((2 * I,), 5, 0.05))
+            layer.layernorm_mlp.fc2_bias.copy_(rnd((H,), 6, 0.05))
+        for step in range(3):
+            x = x0.clone().requires_grad_(True)
+            layer.zero_grad()
+            y = layer(x)
+            y.backward(dy)
+        res.append((y.detach(), x.grad, {n: p.grad for n, p in layer.named_parameters()}))
+    tol = 2e-2
+    close(res[1][0], res[0][0], tol, "y")
+    close(res[1][1], res[0][1], tol, "dx")
+    for n in res[0][2]:
+        close(res[1][2][n], res[0][2][n], tol, n)

@@ -256,3 +256,52 @@ def test_mx_rmsnorm_quantize(shape):
     assert torch.equal(out.sf_row.cpu(), want["sf_row"])
     assert_fp8_equal(out.col, want["q_col"], E4M3)
     assert torch.equal(out.sf_col.cpu(), want["sf_col"])
+
+
+# ------------------------------------------------------------------------------------------------ column slices (row pitch > cols)
+@pytest.mark.parametrize("R,C,W,off", [(6144, 4096, 6144, 0), (333, 80, 200, 16), (64, 2048, 2048 + 8, 8), (1, 16, 48, 32)])
+def test_quantisers_read_column_slices_in_place(R, C, W, off):
+    """x = wide[:, off:off+C] handed over as a view (the query slice of a fused qkv output): bytes, scales and amax must equal the
+    oracle's on the dense copy — per-tensor cast and the MXFP8 block quantiser."""
+    ops = _ops()
+    wide = gen((R, W), 21, "heavy")
+    x = wide[:, off:off + C].contiguous()
+    view = dev(wide)[:, off:off + C]
+    assert not view.is_contiguous() or W == C
+    scale = 448.0 / fo.amax_of(x).item()
+    for dtype in (E4M3, E5M2):
+        s = torch.tensor([scale], dtype=torch.float32).cuda()
+        amax = torch.zeros(1, dtype=torch.float32).cuda()
+        q = ops.quantize_raw(view, FMT[dtype], s, amax)
+        qo, ao = fo.quantize(x, scale, dtype)
+        assert_fp8_equal(q, qo.view(torch.uint8), dtype)
+        assert amax.item() == ao.item()
+    if C % 32 == 0 and R % 32 == 0:
+        want = co.mx_quantize_f32(x.float())
+        out = ops.mx_quantize(view, True, True)
+        assert_fp8_equal(out.row, want["q_row"], E4M3)
+        assert torch.equal(out.sf_row.cpu(), want["sf_row"])
+        assert_fp8_equal(out.col, want["q_col"], E4M3)
+        assert torch.equal(out.sf_col.cpu(), want["sf_col"])
+
+
+def test_rmsnorm_bwd_with_residual_gradient():
+    """K5 + dres: equals the separate kernel result plus dres up to ONE bf16 rounding of the fp32 sum (checked against the fp32
+    reference), and dgamma is untouched by the residual branch."""
+    ops = _ops()
+    for M, H in ((300, 2048), (6144, 4096), (33, 5120), (7, 136)):
+        x, dy, dres = gen((M, H), 4), gen((M, H), 5), gen((M, H), 6)
+        g = torch.Generator().manual_seed(9)
+        gamma = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+        rs = ops.rmsnorm_rsigma(dev(x), 1e-5)
+        dx0, dg0 = ops.rmsnorm_bwd(dev(dy), dev(x), dev(gamma), rs)
+        dx1, dg1 = ops.rmsnorm_bwd(dev(dy), dev(x), dev(gamma), rs, add=dev(dres))
+        assert torch.equal(dg0, dg1)
+        xf = x.float().requires_grad_(True)
+        y, _ = fo.rmsnorm_ref(xf, gamma.float(), 1e-5)
+        y.backward(dy.float())
+        want = xf.grad + dres.float()
+        assert torch.allclose(dx1.float().cpu(), want, rtol=2e-2, atol=2e-2 * want.abs().max().item())
+        # against the unfused pair: differs by at most the double rounding
+        two_step = (dx0.float() + dev(dres).float())
+        assert (dx1.float() - two_step).abs().max().item() <= 2.0 ** -7 * two_step.abs().max().item()

@@ -119,6 +119,12 @@ def main():
         mem("K3b dswiglu_quant [M,2I]", lambda: ops.dswiglu_quant_raw(da, fc1, 1, scale, amax), 8 * M * I)
         rs = ops.rmsnorm_rsigma(x, 1e-5)
         mem("K5 rmsnorm_bwd [M,H]", lambda: ops.rmsnorm_bwd(x, x, gamma, rs), 6 * M * H)
+        mem("K5 rmsnorm_bwd + dres [M,H]", lambda: ops.rmsnorm_bwd(x, x, gamma, rs, add=x), 8 * M * H)
+        wide = torch.randn(M, QKV, device=dev, generator=g).bfloat16()
+        qv = wide[:, :H]
+        mem("K2 cast_amax query slice of [M,QKV] (pitch)", lambda: ops.quantize_raw(qv, 0, scale, amax), 3 * M * H)
+        mem("K2m mx_quantize row+col query slice of [M,QKV] (pitch)", lambda: ops.mx_quantize(qv, True, True), int(4.0625 * M * H))
+        del wide, qv
         mem("K2m mx_quantize row+col x[M,H]", lambda: ops.mx_quantize(x, True, True), int(4.0625 * M * H))
         mem("K2m mx_quantize row x[M,H]", lambda: ops.mx_quantize(x, True, False), int(3.03125 * M * H))
         mem("K2m mx_quantize row+col W1[2I,H]", lambda: ops.mx_quantize(w1, True, True), int(4.0625 * 2 * I * H))
@@ -146,11 +152,16 @@ def main():
                 emit(r)
 
             rec("G1 fprop fp8", lambda: ops.fp8_gemm(X, False, W, False, M, N, K))
+            if lname in ("proj", "fc2"):
+                resid = torch.randn(M, N, device=dev, dtype=torch.bfloat16)
+                rec("G1 fprop fp8 + residual", lambda: ops.fp8_gemm(X, False, W, False, M, N, K, residual=resid))
             rec("G2 dgrad fp8", lambda: ops.fp8_gemm(DY, False, W, True, M, K, N))
             rec("G3 wgrad fp8", lambda: ops.fp8_gemm(DY, True, X, True, N, K, M))
             sfx = torch.full((ops.mx_scale_bytes(M, K),), 127, device=dev, dtype=torch.uint8)
             sfw = torch.full((ops.mx_scale_bytes(N, K),), 127, device=dev, dtype=torch.uint8)
             rec("G1m fprop mxfp8", lambda: ops.mxfp8_gemm(xq, sfx, False, wq, sfw, False, M, N, K))
+            if lname in ("proj", "fc2"):
+                rec("G1m fprop mxfp8 + residual", lambda: ops.mxfp8_gemm(xq, sfx, False, wq, sfw, False, M, N, K, residual=resid))
             sfdy = torch.full((ops.mx_scale_bytes(M, N),), 127, device=dev, dtype=torch.uint8)
             sfwc = torch.full((ops.mx_scale_bytes(K, N),), 127, device=dev, dtype=torch.uint8)
             rec("G2m dgrad mxfp8", lambda: ops.mxfp8_gemm(dyq, sfdy, False, wq, sfwc, True, M, K, N))
