@@ -351,6 +351,20 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tile_coords(tile, m_blk, n_blk);
                 const int row0 = m_blk * TM + static_cast<int>(rank) * BM + quad * 32;
                 const int n0 = n_blk * BN;
+                // fused residual: this lane's 128 B row segment of R for one chunk lives in rv.  Software-pipelined through that single
+                // buffer: the first chunk is requested BEFORE waiting for the accumulator (its DRAM latency hides under the main loop's
+                // tail — the MX kernel at 256 columns has one accumulator, so its epilogue is exposed), the next chunk right after the
+                // current one has been consumed.
+                uint4 rv[RES ? 8 : 1];
+                auto load_residual = [&](int c) {
+                    const int row = row0 + lane;
+                    const int col = n0 + c * ccols;
+                    const uint16_t* rp = static_cast<const uint16_t*>(p.residual) + static_cast<int64_t>(row) * p.ldr + col;
+#pragma unroll
+                    for (int g = 0; g < (RES ? 8 : 1); g++)
+                        rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
+                };
+                if constexpr (RES) load_residual(half);
                 ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
@@ -360,15 +374,6 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     uint32_t r0[32], r1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
                     if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
-                    // fused residual: this lane's 128 B row segment of R, requested while the TMEM load is in flight
-                    uint4 rv[RES ? 8 : 1];
-                    if constexpr (RES) {
-                        const int row = row0 + lane;
-                        const uint16_t* rp = static_cast<const uint16_t*>(p.residual) + static_cast<int64_t>(row) * p.ldr + col;
-#pragma unroll
-                        for (int g = 0; g < 8; g++)
-                            rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
-                    }
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
                     ptx::tmem_ld_wait();
                     if (c + 2 >= nchunks) release_acc(acc);           // this warp's share of the accumulator is in registers
@@ -410,6 +415,9 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                 o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
                                 *reinterpret_cast<uint4*>(sbuf + ((g ^ sw) << 4)) = o;
                             }
+                        }
+                        if constexpr (RES) {
+                            if (c + 2 < nchunks) load_residual(c + 2);     // rv is free again: next chunk's segment, under the store below
                         }
                         ptx::fence_proxy_async();
                         __syncwarp();

@@ -219,8 +219,11 @@ def test_decoder_layer_swap_runs():
 @pytest.mark.parametrize("scenario", ["mxfp8", "default", "hybrid"])
 def test_decoder_linear_path_fused_residual_matches_plain(scenario):
     """DecoderLinearPath with the residual adds fused (proj / fc2 GEMM epilogues, RMSNorm backward) against the plain
-    `h = h + f(h)` form with identical weights: same quantised operands, one bf16 rounding fewer per add — outputs and every
-    gradient agree to bf16 resolution.  The query slice reaches the proj quantiser as a strided view in both."""
+    `h = h + f(h)` form with identical weights.  The fused form rounds each sum once instead of twice, so h differs by a bf16 ulp in
+    about half its elements, and every such difference can flip an FP8 rounding downstream: the two runs agree within an FP8-noise
+    band (measured 2-6 % of max|ref| on the gradients), not bit for bit.  Exactness of each fused kernel is pinned separately
+    (test_gpu_gemm: fused residual == plain + R after one rounding; test_gpu_quantize: rmsnorm_bwd + dres), the autograd wiring in
+    tests/test_autograd_wiring_cpu.py.  The query slice reaches the proj quantiser as a strided view in both."""
     import llm_fp8_b200 as te
     from llm_fp8_b200.layer import DecoderLinearPath, recipes_for
     H, I, heads, kv, hd = 512, 1024, 8, 2, 64
@@ -241,8 +244,8 @@ def test_decoder_linear_path_fused_residual_matches_plain(scenario):
             y = layer(x)
             y.backward(dy)
         res.append((y.detach(), x.grad, {n: p.grad for n, p in layer.named_parameters()}))
-    tol = 2e-2
-    close(res[1][0], res[0][0], tol, "y")
+    tol = 1e-1
+    close(res[1][0], res[0][0], 2e-2, "y")
     close(res[1][1], res[0][1], tol, "dx")
     for n in res[0][2]:
         close(res[1][2][n], res[0][2][n], tol, n)

@@ -267,7 +267,7 @@ def test_quantisers_read_column_slices_in_place(R, C, W, off):
     wide = gen((R, W), 21, "heavy")
     x = wide[:, off:off + C].contiguous()
     view = dev(wide)[:, off:off + C]
-    assert not view.is_contiguous() or W == C
+    assert R == 1 or not view.is_contiguous()
     scale = 448.0 / fo.amax_of(x).item()
     for dtype in (E4M3, E5M2):
         s = torch.tensor([scale], dtype=torch.float32).cuda()

@@ -21,8 +21,10 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "launch__registers_per_thread", "launch__grid_size", "launch__block_size", "sm__cycles_active.avg", "sm__cycles_elapsed.avg",
         "sm__cycles_elapsed.avg.per_second", "smsp__inst_executed.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
 
+# first match wins (so "dswiglu" is tested before "swiglu")
 ENTRY = {"fp8_gemm_kernel": None, "mx_quantize_kernel": "llmfp8_mx_quantize", "dswiglu_quant_kernel": "llmfp8_dswiglu_quant_bwd",
-         "swiglu_quant_kernel": "llmfp8_swiglu_quant_fwd", "rmsnorm_fwd_kernel": "llmfp8_rmsnorm_quant_fwd", "cast_amax_kernel": "llmfp8_quant_cast_amax"}
+         "swiglu_quant_kernel": "llmfp8_swiglu_quant_fwd", "rmsnorm_fwd_kernel": "llmfp8_rmsnorm_quant_fwd", "rmsnorm_bwd_kernel": "llmfp8_rmsnorm_bwd",
+         "cast_amax_bgrad_kernel": "llmfp8_quant_cast_amax_bgrad", "cast_amax_kernel": "llmfp8_quant_cast_amax"}
 
 
 def to_bytes(v, unit):
@@ -76,11 +78,15 @@ def report(name, tag, traffic):
             for short, entry in ENTRY.items():
                 if short in kn:
                     if entry is None:
-                        entry = "llmfp8_mxfp8_gemm" if re.search(r", 1>\(", kn) or kn.rstrip().endswith("1>") else "llmfp8_fp8_gemm"
-                        m = re.search(r"fp8_gemm_kernel<(.*?)>", kn)
+                        # fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES>: the 4th template argument says block-scaled
+                        entry = "llmfp8_fp8_gemm"
+                        m = re.search(r"fp8_gemm_kernel<(.*?)>\(", kn)
                         if m:
-                            entry = "llmfp8_mxfp8_gemm" if m.group(1).split(",")[-1].strip() in ("1", "true") else "llmfp8_fp8_gemm"
+                            targs = [re.sub(r"\(.*?\)", "", t).strip() for t in m.group(1).split(",")]
+                            if len(targs) >= 4 and targs[3] in ("1", "true"):
+                                entry = "llmfp8_mxfp8_gemm"
                     per[entry].append(b)
+                    break
     for e, v in per.items():
         traffic[e] = {"dram_bytes_per_launch_avg": sum(v) / len(v), "launches_captured": len(v), "source": f"profiles/{tag}_{name}.txt"}
 
