@@ -9,6 +9,7 @@ and their MXFP8 counterparts (K1m/K2m quantisers, block-scaled GEMMs).
 """
 from __future__ import annotations
 
+import os
 from typing import Optional
 
 import torch
@@ -193,6 +194,21 @@ class LayerNormMLPFn(torch.autograd.Function):
 
 
 # ====================================================================================== MXFP8
+# The block-scaled GEMM at 256-column tiles has ONE accumulator in TMEM (the scale factors take the rest), so its epilogue is on the
+# critical path and the residual loads lengthen it: measured at Llama-3.1-8B shapes, +15 us (proj) / +35 us (fc2) against ~20 us for a
+# separate add (profiles/r01_microbench_llama8b_v4_gemm.jsonl).  The MXFP8 functions therefore add the residual with a plain in-place
+# add after the GEMM unless LLMFP8_MX_EPILOGUE_RESIDUAL=1; the per-tensor GEMM (two accumulators, epilogue hidden) fuses it (+7..10 us).
+MX_EPILOGUE_RESIDUAL = os.environ.get("LLMFP8_MX_EPILOGUE_RESIDUAL", "0") == "1"
+
+
+def _mx_gemm_residual(a, sfa, b, sfb, M, N, K, bias, residual):
+    """fprop block-scaled GEMM (+bias) (+residual [M, N] bf16, rows possibly spaced)."""
+    if residual is None or MX_EPILOGUE_RESIDUAL:
+        return ops.mxfp8_gemm(a, sfa, False, b, sfb, False, M, N, K, bias=bias, residual=residual)
+    y = ops.mxfp8_gemm(a, sfa, False, b, sfb, False, M, N, K, bias=bias)
+    return y.add_(residual)
+
+
 def _mx_bgrad(dy2: torch.Tensor) -> torch.Tensor:
     """bias gradient for the MXFP8 path: the per-tensor K2b kernel's column sums, its fp8 output discarded."""
     _, bgrad = ops.quantize_bgrad_raw(dy2, 0, None, None)
@@ -213,8 +229,7 @@ class MXLinearFn(torch.autograd.Function):
         else:
             xq = ops.mx_quantize(x2, True, is_grad_enabled)
         wq = ops.mx_quantize(weight, True, is_grad_enabled)
-        y = ops.mxfp8_gemm(xq.row, xq.sf_row, False, wq.row, wq.sf_row, False, M, N, K, bias=bias,
-                           residual=_rows(residual) if residual is not None else None)
+        y = _mx_gemm_residual(xq.row, xq.sf_row, wq.row, wq.sf_row, M, N, K, bias, _rows(residual) if residual is not None else None)
         if is_grad_enabled:
             ctx.save_for_backward(xq.col, xq.sf_col, wq.col, wq.sf_col, x2 if ln_weight is not None else None, ln_weight, rsigma)
             ctx.has_bias = bias is not None
@@ -263,7 +278,7 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         a = ops.swiglu_bf16(fc1)
         aq = ops.mx_quantize(a, True, g)
         w2q = ops.mx_quantize(w2, True, g)
-        y = ops.mxfp8_gemm(aq.row, aq.sf_row, False, w2q.row, w2q.sf_row, False, M, H, I, bias=b2, residual=x2 if residual else None)
+        y = _mx_gemm_residual(aq.row, aq.sf_row, w2q.row, w2q.sf_row, M, H, I, b2, x2 if residual else None)
         if g:
             ctx.save_for_backward(x2, ln_weight, rsigma, lnq.col, lnq.sf_col, w1q.col, w1q.sf_col, fc1, aq.col, aq.sf_col, w2q.col, w2q.sf_col)
             ctx.has_bias = b1 is not None

@@ -130,8 +130,9 @@ def _close(got, want, what, tol=3e-2):
     assert err <= tol, f"{what}: rel err {err:.3e}"
 
 
-@pytest.mark.parametrize("fuse", [False, True])
-def test_decoder_linear_path_matches_torch_reference(fake_ops, fuse):
+@pytest.mark.parametrize("fuse,epilogue", [(False, False), (True, False), (True, True)])
+def test_decoder_linear_path_matches_torch_reference(fake_ops, monkeypatch, fuse, epilogue):
+    monkeypatch.setattr(fn, "MX_EPILOGUE_RESIDUAL", epilogue)     # residual in the block-scaled GEMM's epilogue vs an add after it
     layer = _layer(fuse)
     g = torch.Generator().manual_seed(11)
     x = torch.randn(2, 24, H, generator=g).bfloat16().requires_grad_(True)
@@ -148,7 +149,7 @@ def test_decoder_linear_path_matches_torch_reference(fake_ops, fuse):
     calls = fake_ops.calls
     assert "mxq:strided" in calls, "the query slice must reach the quantiser as a view (no contiguous copy)"
     if fuse:
-        assert calls.count("gemm:res") == 2 and calls.count("rmsbwd:add") == 2, calls
+        assert calls.count("gemm:res") == (2 if epilogue else 0) and calls.count("rmsbwd:add") == 2, calls
     else:
         assert "gemm:res" not in calls and "rmsbwd:add" not in calls
 

@@ -72,8 +72,10 @@ def main():
     ap.add_argument("--debug", type=int, default=0)
     ap.add_argument("--tag", default="")
     ap.add_argument("--kfilter", default="", help="only run memory-bound kernels whose name contains this substring")
+    ap.add_argument("--ms", default="", help="comma-separated token counts to sweep instead of the model's default M (BASELINE.json config 5: 512..16384)")
+    ap.add_argument("--no-bwd", action="store_true", help="GEMM sweep: fprop forms only")
     args = ap.parse_args()
-    H, I, QKV, M = SHAPES[args.model]
+    H, I, QKV, M0 = SHAPES[args.model]
     hbm, bf16_tf, src = peaks()
     os.makedirs(os.path.dirname(args.out), exist_ok=True)
     out = open(args.out, "a")
@@ -94,6 +96,12 @@ def main():
         out.write(json.dumps(rec) + "\n")
         out.flush()
 
+    for M in ([int(v) for v in args.ms.split(",")] if args.ms else [M0]):
+        run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src)
+    out.close()
+
+
+def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
     dev = "cuda"
     g = torch.Generator(device=dev).manual_seed(1234)
     scale = torch.tensor([32.0], device=dev)
@@ -103,7 +111,7 @@ def main():
         if args.kfilter and args.kfilter not in name:
             return
         med, best = timeit(fn)
-        emit({"kernel": name, "ms": med, "ms_best": best, "GBps": nbytes / med / 1e6, "frac_hbm": nbytes / med / 1e6 / hbm, "peak": src, "bytes": nbytes})
+        emit({"kernel": name, "ms": med, "ms_best": best, "GBps": nbytes / med / 1e6, "frac_hbm": nbytes / med / 1e6 / hbm, "peak": src, "bytes": nbytes, "M": M})
 
     if not args.only or "quant" in args.only:
         x = torch.randn(M, H, device=dev, generator=g).bfloat16()
@@ -144,8 +152,10 @@ def main():
             flops = 2.0 * M * N * K
 
             def rec(name, fn, extra=None):
+                if args.no_bwd and ("dgrad" in name or "wgrad" in name):
+                    return
                 med, best = timeit(fn, iters=8, warm=3, flush=False)
-                r = {"kernel": f"{name} {lname} M={M} N={N} K={K}", "ms": med, "ms_best": best, "TFLOPs": flops / med / 1e9,
+                r = {"kernel": f"{name} {lname} M={M} N={N} K={K}", "M": M, "ms": med, "ms_best": best, "TFLOPs": flops / med / 1e9,
                      "frac_2x_bf16_measured": flops / med / 1e9 / (2 * bf16_tf), "frac_fp8_nominal": flops / med / 1e9 / 4500.0}
                 if extra:
                     r.update(extra)
@@ -183,7 +193,6 @@ def main():
             except Exception as e:  # noqa: BLE001
                 emit({"kernel": f"ref torch._scaled_mm mxfp8 {lname}", "error": str(e)[:300]})
             del xq, wq, dyq, xb, wb
-    out.close()
 
 
 if __name__ == "__main__":
