@@ -385,7 +385,8 @@ def main():
             "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
                        "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,
                        "parallelism": f"dp{world}", "launch": "cuda-graph replay" if graphed else "eager stream launches",
-                       "residual_adds": "fused (GEMM epilogue / RMSNorm backward)" if model.layers[0].fuse_residual else "separate elementwise passes", "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
+                       "residual_adds": (("fused: forward add after the GEMM, gradient in the RMSNorm backward" if a.scenario == "mxfp8"
+                                         else "fused: GEMM epilogue / RMSNorm backward") if model.layers[0].fuse_residual else "separate elementwise passes"), "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
