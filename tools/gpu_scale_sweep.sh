@@ -15,6 +15,6 @@ try:
 except Exception as e: print("   parse failed", e)
 PY
 }
-run default FOO=1
-run maxctas8 NCCL_MAX_CTAS=8
-run maxctas4 NCCL_MAX_CTAS=4
+for cfg in ${2:-16 8 4}; do
+  run maxctas$cfg NCCL_MAX_CTAS=$cfg
+done
