@@ -244,7 +244,7 @@ def main():
         x = x_in.detach().requires_grad_(True)
         y = model(x)
         loss = y.float().square().mean()
-        loss.backward()
+        (loss * reducer.loss_scale if reducer is not None and reducer.prescaled else loss).backward()
         if reducer is not None:
             reducer.finish()
         return loss
@@ -384,7 +384,8 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
                        "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,
-                       "parallelism": f"dp{world}", "launch": "cuda-graph replay" if graphed else "eager stream launches",
+                       "parallelism": f"dp{world}", "grad_reduce": ("sum of 1/N-prescaled gradients" if reducer is not None and reducer.prescaled else "avg") if world > 1 else None,
+                       "launch": "cuda-graph replay" if graphed else "eager stream launches",
                        "residual_adds": (("fused: forward add after the GEMM, gradient in the RMSNorm backward" if a.scenario == "mxfp8"
                                          else "fused: GEMM epilogue / RMSNorm backward") if model.layers[0].fuse_residual else "separate elementwise passes"), "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS},

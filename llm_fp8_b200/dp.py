@@ -56,10 +56,20 @@ class GradAllReducer:
     flat buffer and reduced together in `finish()`.  Call `finish()` after `backward()`; it makes the current stream wait
     for every outstanding reduction."""
 
-    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True):
+    def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True,
+                 prescaled: Optional[bool] = None):
+        """prescaled (default; LLMFP8_GRAD_REDUCE=avg turns it off): the caller multiplies its loss by `loss_scale` (= 1/world) and
+        the gradients are all-reduced with SUM — the same mean as AVG, but SUM is the one reduction NVSwitch can do in the fabric:
+        NCCL's NVLS algorithms have no AVG / pre-multiplied sum, so with AVG it falls back to a 32-channel ring.  Measured at 8 B200s
+        (mxfp8, same box): SUM -> NVLS / 24 channels 170.7 ms per step, AVG -> Ring 175.0 ms.  DDP itself pre-divides
+        (train_multi_gpu.py:355-378).  A caller that ignores `loss_scale` gets summed, not averaged, gradients."""
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
-        self.average = average
+        if prescaled is None:
+            prescaled = os.environ.get("LLMFP8_GRAD_REDUCE", "sum").lower() != "avg"
+        self.prescaled = bool(prescaled) and average and self.world > 1
+        self.loss_scale = 1.0 / self.world if self.prescaled else 1.0
+        self.average = average and not self.prescaled
         self.direct_numel = direct_numel
         self._work: List = []
         self._small: List[torch.nn.Parameter] = []

@@ -30,17 +30,18 @@ def _batch():
     return torch.randn(6, 10, 64, generator=g)          # 6 sequences of 10 tokens
 
 
-def _worker(rank, world, port, out):
+def _worker(rank, world, port, out, prescaled=False):
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     r, w, _ = dp.init_from_env(backend="gloo")
     assert (r, w) == (rank, world) and dist.get_backend() == "gloo"
     model = _model()
-    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128)
+    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128, prescaled=prescaled)
+    assert reducer.prescaled == prescaled and reducer.loss_scale == (1.0 / world if prescaled else 1.0)
     x = _batch()
     mine = dp.shard_tokens(x.shape[0], rank, world)
     xs = x[mine.start:mine.stop]
     # mean loss over the LOCAL shard; DDP semantics average over ranks, which equals the global mean for equal shards
-    model(xs).square().mean().backward()
+    (model(xs).square().mean() * reducer.loss_scale).backward()
     reducer.finish()
     grads = [p.grad.clone() for p in model.parameters()]
     # amax exchange: element-wise MAX of a flat fp32 buffer
@@ -52,9 +53,11 @@ def _worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-def test_two_rank_grad_allreduce_matches_single_process(tmp_path):
+@pytest.mark.parametrize("prescaled", [False, True])
+def test_two_rank_grad_allreduce_matches_single_process(tmp_path, prescaled):
+    """prescaled: loss * 1/world then SUM (the reduction NVSwitch can run in the fabric) — same mean as AVG."""
     out = str(tmp_path / "r0.pt")
-    mp.spawn(_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    mp.spawn(_worker, args=(2, _free_port(), out, prescaled), nprocs=2, join=True)
     got = torch.load(out)
     model = _model()
     model(_batch()).square().mean().backward()
