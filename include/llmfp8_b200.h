@@ -124,6 +124,22 @@ int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, con
 int llmfp8_mxfp8_gemm_res(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
                           int64_t ldd, int M, int N, int K, const void* bias, const void* residual, int64_t ldr, int max_ctas, void* stream);
 
+/* ---- data-parallel exchanges ---------------------------------------------------------------- */
+
+/* The only two collectives on the path, for hosts without torch.distributed.  NCCL is dlopen'ed ("libnccl.so.2") on first use.
+ * Stand in for DDP's gradient all-reduce (train_multi_gpu.py:355-378) and TE's amax reduction at fp8_autocast exit (te_llama.py:76-80).
+ *   llmfp8_nccl_unique_id : rank 0 fills a 128-byte id; the host hands it to every rank (env rendezvous, file, MPI ...).
+ *   llmfp8_nccl_init      : collective; binds the communicator to the calling thread's current CUDA device; *comm is opaque.
+ *   ..._allreduce_max_f32 : in place, n floats — the delayed-scaling amax pool, once per direction per step.
+ *   ..._allreduce_sum_bf16: in place, n bf16 — a weight gradient, straight out of the wgrad GEMM (scale the loss by 1/world for a mean:
+ *                           SUM is the reduction NVSwitch runs in the fabric).
+ * Return 0, < 0 (contract; -4 = NCCL not loadable) or 1000 + ncclResult_t. */
+int llmfp8_nccl_unique_id(void* id128);
+int llmfp8_nccl_init(const void* id128, int rank, int world, void** comm);
+int llmfp8_nccl_allreduce_max_f32(void* comm, float* buf, int64_t n, void* stream);
+int llmfp8_nccl_allreduce_sum_bf16(void* comm, void* buf, int64_t n, void* stream);
+int llmfp8_nccl_destroy(void* comm);
+
 #ifdef __cplusplus
 }
 #endif

@@ -107,6 +107,11 @@ int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, 
 int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
 int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
                     const void*, const void*, const void*, const void*, int64_t, int, int, cudaStream_t);
+int comm_unique_id(void*);
+int comm_init(const void*, int, int, void**);
+int comm_allreduce_max_f32(void*, float*, int64_t, cudaStream_t);
+int comm_allreduce_sum_bf16(void*, void*, int64_t, cudaStream_t);
+int comm_destroy(void*);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
@@ -209,5 +214,11 @@ int llmfp8_mxfp8_gemm_res(const void* a, int64_t lda, int a_mn, const void* sfa,
     return launch_fp8_gemm(a, lda, LLMFP8_E4M3, a_mn, b, ldb, LLMFP8_E4M3, b_mn, d, ldd, 0, M, N, K, nullptr, nullptr, sfa, sfb, bias, residual, ldr, 0,
                            max_ctas, S(stream));
 }
+
+int llmfp8_nccl_unique_id(void* id128) { return comm_unique_id(id128); }
+int llmfp8_nccl_init(const void* id128, int rank, int world, void** comm) { return comm_init(id128, rank, world, comm); }
+int llmfp8_nccl_allreduce_max_f32(void* comm, float* buf, int64_t n, void* stream) { return comm_allreduce_max_f32(comm, buf, n, S(stream)); }
+int llmfp8_nccl_allreduce_sum_bf16(void* comm, void* buf, int64_t n, void* stream) { return comm_allreduce_sum_bf16(comm, buf, n, S(stream)); }
+int llmfp8_nccl_destroy(void* comm) { return comm_destroy(comm); }
 
 }  // extern "C"

@@ -121,3 +121,62 @@ class GradAllReducer:
         for h in self._handles:
             h.remove()
         self._handles = []
+
+
+class CAbiComm:
+    """The path's two collectives through the C ABI's own NCCL communicator (llmfp8_nccl_*: include/llmfp8_b200.h) instead of
+    torch.distributed — what a host without PyTorch's process groups binds.  The 128-byte id is created on rank 0 and handed
+    round either by the caller (`unique_id=`) or over an already initialised torch.distributed group (any backend).
+
+    Collectives run on `stream` (default: the current stream) and are in place; like every C-ABI call they are asynchronous."""
+
+    def __init__(self, rank: int, world: int, device: torch.device, unique_id: Optional[bytes] = None, group=None):
+        import ctypes as C
+
+        from . import _lib
+        self._lib = _lib.load()
+        self.rank, self.world, self.device = rank, world, torch.device(device)
+        if unique_id is None:
+            buf = C.create_string_buffer(128)
+            if rank == 0:
+                _lib.check(self._lib.llmfp8_nccl_unique_id(buf), "nccl_unique_id")
+            if world > 1:
+                if not dist.is_initialized():
+                    raise RuntimeError("CAbiComm needs either unique_id= or an initialised torch.distributed group to hand the id round")
+                box = [buf.raw if rank == 0 else None]
+                dist.broadcast_object_list(box, src=0, group=group)
+                unique_id = box[0]
+            else:
+                unique_id = buf.raw
+        if len(unique_id) != 128:
+            raise ValueError("NCCL unique id must be 128 bytes")
+        self.unique_id = bytes(unique_id)
+        handle = C.c_void_p()
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.llmfp8_nccl_init(self.unique_id, rank, world, C.byref(handle)), "nccl_init")
+        self._comm = handle
+
+    def _stream(self, stream) -> int:
+        return (stream or torch.cuda.current_stream(self.device)).cuda_stream
+
+    def all_reduce_max_f32(self, t: torch.Tensor, stream=None):
+        """amax pools: element-wise MAX of a flat fp32 buffer (fp8.ScalePool.flush)."""
+        from . import _lib
+        if t.dtype != torch.float32 or not t.is_contiguous() or not t.is_cuda:
+            raise RuntimeError("all_reduce_max_f32 needs a contiguous CUDA fp32 tensor")
+        _lib.check(self._lib.llmfp8_nccl_allreduce_max_f32(self._comm, t.data_ptr(), t.numel(), self._stream(stream)), "nccl_allreduce_max_f32")
+        return t
+
+    def all_reduce_sum_bf16(self, t: torch.Tensor, stream=None):
+        """weight gradients: SUM in place (scale the loss by 1/world for the mean)."""
+        from . import _lib
+        if t.dtype != torch.bfloat16 or not t.is_contiguous() or not t.is_cuda:
+            raise RuntimeError("all_reduce_sum_bf16 needs a contiguous CUDA bf16 tensor")
+        _lib.check(self._lib.llmfp8_nccl_allreduce_sum_bf16(self._comm, t.data_ptr(), t.numel(), self._stream(stream)), "nccl_allreduce_sum_bf16")
+        return t
+
+    def destroy(self):
+        if self._comm is not None and self._comm.value:
+            from . import _lib
+            _lib.check(self._lib.llmfp8_nccl_destroy(self._comm), "nccl_destroy")
+        self._comm = None
