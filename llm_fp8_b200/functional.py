@@ -66,6 +66,32 @@ def _rows(x: torch.Tensor) -> torch.Tensor:
     return x2 if (x2.is_contiguous() or ops.rows_ok(x2)) else x2.contiguous()
 
 
+def _weight_pt(wcache, first, key, weight, ff, pf: ScalePool, slot) -> "ops.QTensor":
+    """Per-tensor fp8 copy of a weight.  TE's `is_first_microbatch` contract: None = cast on every
+    call; True = cast and keep; False = reuse the kept copy (gradient accumulation: the weights do not change between the
+    micro-batches of one optimizer step).  A kept copy carries a snapshot of the scale_inv it was cast with, because the pool's
+    slot moves on at the next flush."""
+    if wcache is not None and first is False and key in wcache:
+        return wcache[key]
+    wq = ops.quantize(weight, ff, pf, slot)
+    if wcache is not None and first is not None:
+        wq = ops.QTensor(wq.data, wq.fmt, pf.scale_inv[slot:slot + 1].clone(), 0)
+        wcache[key] = wq
+    return wq
+
+
+def _weight_mx(wcache, first, key, weight, need_col: bool) -> "ops.MXTensor":
+    """MXFP8 copies (rowwise for fprop, colwise for dgrad) of a weight under the same `is_first_microbatch` contract."""
+    if wcache is not None and first is False:
+        hit = wcache.get(key)
+        if hit is not None and (hit.col is not None or not need_col):
+            return hit
+    wq = ops.mx_quantize(weight, True, need_col)
+    if wcache is not None and first is not None:
+        wcache[key] = wq
+    return wq
+
+
 def _wgrad(dyq, xq, N, K, T, weight):
     """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
     return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
@@ -74,7 +100,8 @@ def _wgrad(dyq, xq, N, K, T, weight):
 # ====================================================================================== per-tensor (DelayedScaling)
 class LinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, meta: Fp8Meta, recipe: DelayedScaling, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False):
+    def forward(ctx, x, weight, bias, meta: Fp8Meta, recipe: DelayedScaling, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False,
+                wcache=None, first=None):
         """ln_weight None: plain Linear; else LayerNormLinear (RMSNorm fused into the input cast).
         residual [.., N]: y = residual + x W^T (+b), added in the GEMM epilogue; its gradient is dy itself.
         passthrough: also return an alias of x, so that the gradient of a residual branch taken from it arrives here and is folded
@@ -92,7 +119,7 @@ class LinearFn(torch.autograd.Function):
             xq, rsigma = ops.rmsnorm_quant(x2, ln_weight, eps, ff, pf, f0 + 0)
         else:
             xq = ops.quantize(x2, ff, pf, f0 + 0)
-        wq = ops.quantize(weight, ff, pf, f0 + 1)
+        wq = _weight_pt(wcache, first, ("w", recipe.key()), weight, ff, pf, f0 + 1)
         y = ops.fp8_gemm(xq, False, wq, False, M, N, K, bias=bias, residual=_rows(residual) if residual is not None else None)
         if is_grad_enabled:
             ctx.save_for_backward(xq.data, wq.data, x2 if ln_weight is not None else None, ln_weight, rsigma)
@@ -103,6 +130,7 @@ class LinearFn(torch.autograd.Function):
             ctx.wdtype = weight.dtype
             ctx.needs = (x.requires_grad, weight.requires_grad)
             ctx.has_residual = residual is not None
+            ctx.w_si = (wq.scale_inv, wq.scale_inv_off)
         ctx.set_materialize_grads(False)
         y = y.reshape(*x.shape[:-1], N)
         return (y, x.view_as(x)) if passthrough else y
@@ -110,7 +138,7 @@ class LinearFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, dres=None):
         if dy is None:                       # only the pass-through alias was used downstream
-            return (dres,) + (None,) * 9
+            return (dres,) + (None,) * 11
         xq_d, wq_d, x2, ln_weight, rsigma = ctx.saved_tensors
         s, recipe = ctx.slots, ctx.recipe
         M, N, K = ctx.dims
@@ -118,7 +146,7 @@ class LinearFn(torch.autograd.Function):
         pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
         ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
         xq = ops.QTensor(xq_d, ff, pf.scale_inv, f0 + 0)
-        wq = ops.QTensor(wq_d, ff, pf.scale_inv, f0 + 1)
+        wq = ops.QTensor(wq_d, ff, *ctx.w_si)
         dy2 = _2d(dy).contiguous()
         dbias = None
         if ctx.has_bias:
@@ -133,12 +161,13 @@ class LinearFn(torch.autograd.Function):
         elif dres is not None:
             dx = dx + _2d(dres)
         Fp8Meta.end_bwd(s)
-        return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None, (dy if ctx.has_residual else None), None
+        return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None, (dy if ctx.has_residual else None), None, None, None
 
 
 class LayerNormMLPFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, ln_weight, w1, b1, w2, b2, meta: Fp8Meta, recipe: DelayedScaling, eps, is_grad_enabled, residual=False):
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, meta: Fp8Meta, recipe: DelayedScaling, eps, is_grad_enabled, residual=False,
+                wcache=None, first=None):
         """residual=True: returns x + MLP(x) — the add rides in the fc2 GEMM epilogue, its gradient in the RMSNorm backward."""
         dev = x.device
         s = meta.get(recipe, dev)
@@ -150,15 +179,16 @@ class LayerNormMLPFn(torch.autograd.Function):
         I2 = w1.shape[0]
         I = I2 // 2
         lnq, rsigma = ops.rmsnorm_quant(x2, ln_weight, eps, ff, pf, f0 + 0)
-        w1q = ops.quantize(w1, ff, pf, f0 + 1)
+        w1q = _weight_pt(wcache, first, ("w1", recipe.key()), w1, ff, pf, f0 + 1)
         fc1 = ops.fp8_gemm(lnq, False, w1q, False, M, I2, H, bias=b1)
         aq = ops.swiglu_quant(fc1, ff, pf, f0 + 3)
-        w2q = ops.quantize(w2, ff, pf, f0 + 4)
+        w2q = _weight_pt(wcache, first, ("w2", recipe.key()), w2, ff, pf, f0 + 4)
         y = ops.fp8_gemm(aq, False, w2q, False, M, H, I, bias=b2, residual=x2 if residual else None)
         if is_grad_enabled:
             ctx.save_for_backward(x2, ln_weight, rsigma, lnq.data, w1q.data, fc1, aq.data, w2q.data)
             ctx.recipe, ctx.slots = recipe, s
             ctx.residual = residual
+            ctx.w1_si, ctx.w2_si = (w1q.scale_inv, w1q.scale_inv_off), (w2q.scale_inv, w2q.scale_inv_off)
             ctx.has_bias = b1 is not None
             ctx.shape = x.shape
             ctx.dims = (M, H, I)
@@ -174,9 +204,9 @@ class LayerNormMLPFn(torch.autograd.Function):
         pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
         ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
         lnq = ops.QTensor(lnq_d, ff, pf.scale_inv, f0 + 0)
-        w1q = ops.QTensor(w1q_d, ff, pf.scale_inv, f0 + 1)
+        w1q = ops.QTensor(w1q_d, ff, *ctx.w1_si)
         aq = ops.QTensor(aq_d, ff, pf.scale_inv, f0 + 3)
-        w2q = ops.QTensor(w2q_d, ff, pf.scale_inv, f0 + 4)
+        w2q = ops.QTensor(w2q_d, ff, *ctx.w2_si)
         dy2 = _2d(dy).contiguous()
         db2 = db1 = None
         if ctx.has_bias:
@@ -190,7 +220,7 @@ class LayerNormMLPFn(torch.autograd.Function):
         dw1 = ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype)   # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
         Fp8Meta.end_bwd(s)
-        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None, None, None, None, None
 
 
 # ====================================================================================== MXFP8
@@ -217,8 +247,8 @@ def _mx_bgrad(dy2: torch.Tensor) -> torch.Tensor:
 
 class MXLinearFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, weight, bias, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False):
-        """residual / passthrough: as LinearFn.forward."""
+    def forward(ctx, x, weight, bias, ln_weight, eps, is_grad_enabled, residual=None, passthrough=False, wcache=None, first=None):
+        """residual / passthrough / wcache, first: as LinearFn.forward."""
         x2 = _2d(x).contiguous() if ln_weight is not None else _rows(x)
         M, K = x2.shape
         N = weight.shape[0]
@@ -228,7 +258,7 @@ class MXLinearFn(torch.autograd.Function):
             xq = ops.mx_quantize(x2, True, is_grad_enabled, rsigma, ln_weight)
         else:
             xq = ops.mx_quantize(x2, True, is_grad_enabled)
-        wq = ops.mx_quantize(weight, True, is_grad_enabled)
+        wq = _weight_mx(wcache, first, ("w", "mx"), weight, is_grad_enabled)
         y = _mx_gemm_residual(xq.row, xq.sf_row, wq.row, wq.sf_row, M, N, K, bias, _rows(residual) if residual is not None else None)
         if is_grad_enabled:
             ctx.save_for_backward(xq.col, xq.sf_col, wq.col, wq.sf_col, x2 if ln_weight is not None else None, ln_weight, rsigma)
@@ -242,7 +272,7 @@ class MXLinearFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, dy, dres=None):
         if dy is None:                       # only the pass-through alias was used downstream
-            return (dres,) + (None,) * 7
+            return (dres,) + (None,) * 9
         x_col, x_sfc, w_col, w_sfc, x2, ln_weight, rsigma = ctx.saved_tensors
         M, N, K = ctx.dims
         dy2 = _2d(dy).contiguous()
@@ -257,7 +287,7 @@ class MXLinearFn(torch.autograd.Function):
             dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
         elif dres is not None:
             dx = dx + _2d(dres)
-        return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None, (dy if ctx.has_residual else None), None
+        return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None, (dy if ctx.has_residual else None), None, None, None
 
 
 class MXLayerNormMLPFn(torch.autograd.Function):
@@ -265,7 +295,7 @@ class MXLayerNormMLPFn(torch.autograd.Function):
     reads (one extra bf16 round trip compared with a fully fused activation+MX quantiser: DESIGN.md 'next')."""
 
     @staticmethod
-    def forward(ctx, x, ln_weight, w1, b1, w2, b2, eps, is_grad_enabled, residual=False):
+    def forward(ctx, x, ln_weight, w1, b1, w2, b2, eps, is_grad_enabled, residual=False, wcache=None, first=None):
         x2 = _2d(x).contiguous()
         M, H = x2.shape
         I2 = w1.shape[0]
@@ -273,11 +303,11 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         g = is_grad_enabled
         rsigma = ops.rmsnorm_rsigma(x2, eps)
         lnq = ops.mx_quantize(x2, True, g, rsigma, ln_weight)
-        w1q = ops.mx_quantize(w1, True, g)
+        w1q = _weight_mx(wcache, first, ("w1", "mx"), w1, g)
         fc1 = ops.mxfp8_gemm(lnq.row, lnq.sf_row, False, w1q.row, w1q.sf_row, False, M, I2, H, bias=b1)
         a = ops.swiglu_bf16(fc1)
         aq = ops.mx_quantize(a, True, g)
-        w2q = ops.mx_quantize(w2, True, g)
+        w2q = _weight_mx(wcache, first, ("w2", "mx"), w2, g)
         y = _mx_gemm_residual(aq.row, aq.sf_row, w2q.row, w2q.sf_row, M, H, I, b2, x2 if residual else None)
         if g:
             ctx.save_for_backward(x2, ln_weight, rsigma, lnq.col, lnq.sf_col, w1q.col, w1q.sf_col, fc1, aq.col, aq.sf_col, w2q.col, w2q.sf_col)
@@ -300,4 +330,4 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad
         dw1 = ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype)  # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
-        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None
+        return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None

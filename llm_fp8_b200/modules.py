@@ -37,6 +37,13 @@ class _Fp8Module(nn.Module):
     def __init__(self):
         super().__init__()
         self._meta = fn.Fp8Meta(self._N_FWD, self._N_BWD)
+        # quantised weight copies kept between the micro-batches of one optimizer step (forward(..., is_first_microbatch=True / False);
+        # None = cast on every call, what the reference's training loop gets: it never passes the argument — train_fp8.py:276-291)
+        self._wcache = {}
+
+    def _apply(self, fn_, *args, **kwargs):
+        self._wcache.clear()                 # .cuda() / .to() replace the parameters the copies were cast from
+        return super()._apply(fn_, *args, **kwargs)
 
     def get_extra_state(self):
         out = {}
@@ -86,9 +93,9 @@ class Linear(_Fp8Module):
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False)
+            return fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False, self._wcache, is_first_microbatch)
         self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False)
+        return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False, self._wcache, is_first_microbatch)
 
 
 class LayerNormLinear(_Fp8Module):
@@ -144,9 +151,10 @@ class LayerNormLinear(_Fp8Module):
         w, b = self._weight_bias()
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input)
+            return fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, is_first_microbatch)
         self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input)
+        return fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache,
+                                 is_first_microbatch)
 
 
 class LayerNormMLP(_Fp8Module):
@@ -183,10 +191,10 @@ class LayerNormMLP(_Fp8Module):
         g = torch.is_grad_enabled()
         if isinstance(recipe, MXFP8BlockScaling):
             return fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g,
-                                             add_residual)
+                                             add_residual, self._wcache, is_first_microbatch)
         self._apply_extra_state(recipe, inp.device)
         return fn.LayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self._meta,
-                                       recipe, self.eps, g, add_residual)
+                                       recipe, self.eps, g, add_residual, self._wcache, is_first_microbatch)
 
 
 # ------------------------------------------------------------------------------------------ attention shell
@@ -243,11 +251,12 @@ class MultiheadAttention(nn.Module):
                                              parameters_split=split, params_dtype=params_dtype, device=device, init_method=init_method)
         self.proj = Linear(q_out, hidden_size, bias=bias, params_dtype=params_dtype, device=device, init_method=output_layer_init_method)
 
-    def forward(self, hidden_states: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, rotary_pos_emb=None, **_unused):
+    def forward(self, hidden_states: torch.Tensor, attention_mask: Optional[torch.Tensor] = None, rotary_pos_emb=None,
+                is_first_microbatch=None, **_unused):
         if self.qkv_format == "sbhd":
             hidden_states = hidden_states.transpose(0, 1)
         B, S, _ = hidden_states.shape
-        qkv = self.layernorm_qkv(hidden_states)
+        qkv = self.layernorm_qkv(hidden_states, is_first_microbatch=is_first_microbatch)
         q_out, kv_out = self.num_heads * self.head_dim, self.num_gqa_groups * self.head_dim
         q, k, v = qkv.split([q_out, kv_out, kv_out], dim=-1)
         q = q.reshape(B, S, self.num_heads, self.head_dim)
@@ -267,7 +276,7 @@ class MultiheadAttention(nn.Module):
                                              dropout_p=self.dropout if self.training else 0.0, is_causal=causal and mask is None,
                                              enable_gqa=self.num_gqa_groups != self.num_heads)
         ctx = ctx.transpose(1, 2).reshape(B, S, q_out)
-        out = self.proj(ctx)
+        out = self.proj(ctx, is_first_microbatch=is_first_microbatch)
         if self.qkv_format == "sbhd":
             out = out.transpose(0, 1)
         return out

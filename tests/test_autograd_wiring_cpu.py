@@ -198,3 +198,34 @@ def test_linear_residual_and_passthrough_gradients(fake_ops):
     _, xa4 = fn.MXLinearFn.apply(x4, w, None, gamma, 1e-5, True, None, True)
     xa4.float().sum().backward()
     assert torch.equal(x4.grad, torch.ones_like(x4))
+
+
+def test_weight_copies_are_kept_between_microbatches(fake_ops):
+    """is_first_microbatch (TE contract): None casts the weights on every call, True casts and keeps,
+    False reuses — same outputs and gradients, fewer quantiser launches; .to() / .cuda() drops the kept copies."""
+    torch.manual_seed(1)
+    r = te.MXFP8BlockScaling(fp8_format=te.Format.E4M3)
+    mlp = te.LayerNormMLP(H, I, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16)
+    lin = te.Linear(H, 48, bias=False, params_dtype=torch.bfloat16)
+    x = torch.randn(6, H).bfloat16().requires_grad_(True)
+
+    def run(first):
+        fake_ops.calls.clear()
+        x.grad = None
+        mlp.zero_grad(); lin.zero_grad()
+        with te.fp8_autocast(enabled=True, fp8_recipe=r):
+            y = lin(mlp(x, is_first_microbatch=first), is_first_microbatch=first)
+        y.float().sum().backward()
+        n_q = sum(c.startswith("mxq") for c in fake_ops.calls)
+        return y.detach().clone(), x.grad.clone(), mlp.fc1_weight.grad.clone(), lin.weight.grad.clone(), n_q
+
+    base = run(None)
+    first = run(True)
+    again = run(False)
+    assert base[4] == first[4] == again[4] + 3          # fc1, fc2 and the Linear weight are not cast again
+    for a, b in zip(base[:4], again[:4]):
+        assert torch.equal(a, b)
+    assert set(mlp._wcache) == {("w1", "mx"), ("w2", "mx")} and set(lin._wcache) == {("w", "mx")}
+    mlp.to(torch.bfloat16)
+    assert not mlp._wcache
+    assert run(False)[4] == base[4] - 1                 # mlp casts again (and keeps), lin still reuses

@@ -249,3 +249,49 @@ def test_decoder_linear_path_fused_residual_matches_plain(scenario):
     close(res[1][1], res[0][1], tol, "dx")
     for n in res[0][2]:
         close(res[1][2][n], res[0][2][n], tol, n)
+
+
+@pytest.mark.parametrize("recipe_name", ["MXFP8", "HYBRID"])
+def test_is_first_microbatch_keeps_weight_copies(recipe_name):
+    """Gradient accumulation (TE's is_first_microbatch): micro-batch 2 reuses the fp8 weight copies of micro-batch 1.
+    MXFP8 has no scaling state, so the reused copies give bit-identical results to casting again; with delayed scaling the kept copy
+    carries the scale it was cast with (the pool's slot has moved on), and results stay inside the FP8 band.  Either way the
+    quantiser launches for the weights disappear."""
+    import llm_fp8_b200 as te
+    from llm_fp8_b200 import _lib
+    lib = _lib.load()
+    te.reset_fp8_state()
+    recipe = te.MXFP8BlockScaling(fp8_format=te.Format.E4M3) if recipe_name == "MXFP8" else \
+        te.DelayedScaling(fp8_format=te.Format.HYBRID, amax_history_len=16, amax_compute_algo="max")
+    torch.manual_seed(2)
+    H, I = 512, 1024
+    m = te.LayerNormMLP(H, I, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16, device="cuda")
+    lin = te.Linear(H, 256, bias=False, params_dtype=torch.bfloat16, device="cuda")
+    xs = [rnd((2, 128, H), 30 + i).cuda().requires_grad_(True) for i in range(2)]
+
+    def step(flags):
+        m.zero_grad(); lin.zero_grad()
+        outs, n0 = [], lib.llmfp8_launch_count()
+        for x, first in zip(xs, flags):
+            x.grad = None
+            with te.fp8_autocast(enabled=True, fp8_recipe=recipe):
+                y = lin(m(x, is_first_microbatch=first), is_first_microbatch=first)
+            y.float().pow(2).mean().backward()
+            outs.append((y.detach().clone(), x.grad.clone()))
+        return outs, m.fc1_weight.grad.clone(), lin.weight.grad.clone(), lib.llmfp8_launch_count() - n0
+
+    for _ in range(2):                       # settle the delayed-scaling history
+        step((None, None))
+    base = step((None, None))
+    kept = step((True, False))
+    assert kept[3] == base[3] - 3, (kept[3], base[3])            # fc1, fc2 and the Linear weight are cast once, not twice
+    if recipe_name == "MXFP8":
+        for (ya, ga), (yb, gb) in zip(base[0], kept[0]):
+            assert torch.equal(ya, yb) and torch.equal(ga, gb)
+        assert torch.equal(base[1], kept[1]) and torch.equal(base[2], kept[2])
+    else:
+        for (ya, ga), (yb, gb) in zip(base[0], kept[0]):
+            close(yb, ya, 1e-1, "y")
+            close(gb, ga, 1e-1, "dx")
+        close(kept[1], base[1], 1e-1, "dW1")
+        close(kept[2], base[2], 1e-1, "dW")
