@@ -18,8 +18,8 @@
 // 128 x BN accumulator in its own TMEM.  Shared-memory traffic per MMA cycle drops from 96 B/clk (1-CTA 128x256) to 64 B/clk —
 // the 1-CTA kernel measured shared-memory bound (profiles/r01_*: BN sweep).
 // BN (the UMMA N) is a RUNTIME parameter in {128, 192, 256}: the host picks it per problem to minimise wave quantisation
-// (tiles / 148 CTAs), and MXFP8 uses BN <= 192 so that TWO accumulators (2 x 192 columns) plus the scale-factor columns fit the
-// 512 TMEM columns — the epilogue of tile t then overlaps the mainloop of tile t+1 for both kinds.
+// (tiles / 148 CTAs).  MXFP8 keeps 64 TMEM columns for scale factors: at BN <= 192 two accumulators fit beside them, at BN = 256 the two
+// accumulators overlap by 64 columns (OVL below) — either way the epilogue of tile t overlaps the mainloop of tile t+1.
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
@@ -60,9 +60,11 @@ struct GemmParams {
     int bn;                     // tile columns = UMMA N (128 | 192 | 256)
     int b_rows_cta;             // B rows staged per CTA: bn / CG (K-major) or that rounded up to 128 (MN-major chunks)
     int stages;                 // smem ring depth
-    int acc_stages;             // TMEM accumulator buffers (2, or 1 for MX with bn > 192)
-    int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads
+    int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
+    int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
+                                // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
+    int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
 
 // Shared-memory control block of one CTA.
@@ -74,6 +76,7 @@ struct GemmCtrl {
     alignas(16) uint8_t clc_resp[CLC_ST][16];
     int ring_tile[RING];
     uint32_t tmem_ptr;
+    alignas(8) uint64_t ovl_free;                     // OVL kernels only: the epilogue has drained the TMEM columns both accumulators share
 };
 static_assert(sizeof(GemmCtrl) <= CTRL_BYTES, "control block");
 
@@ -117,7 +120,12 @@ __device__ __forceinline__ void tma3d(const CUtensorMap* m, uint64_t* bar, uint3
 
 // RES: fused residual add in the staged bf16 epilogue (fprop layouts only) — a separate instantiation so the 32 prefetch registers
 // it needs never weigh on the plain kernels.
-template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false>
+// OVL (MX at 256 columns without accumulate / residual; debug bit 4 selects the single-accumulator kernel instead): two accumulators
+// of 256 columns laid 192 apart — [0, 256) and [192, 448) — instead of one, in the 448 TMEM columns the scale factors leave.  They share columns [192, 256); the epilogue of a
+// tile drains that shared chunk first and signals `ovl_free`, after which the MMAs of the next tile may start while the rest of the
+// previous accumulator is still being read: the exposed epilogue shrinks from a whole tile's read-out to one 64-column chunk.
+constexpr int OVL_STRIDE = 192;
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_sfa,
                 const __grid_constant__ CUtensorMap map_sfb, const __grid_constant__ CUtensorMap map_d, const GemmParams p) {
@@ -161,6 +169,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             ptx::mbar_init(&tmem_full[s], 1);
             ptx::mbar_init(&tmem_empty[s], EPI_WARPS * CG);
         }
+        if constexpr (OVL) ptx::mbar_init(&ctrl->ovl_free, (p.out_fp32 ? EPI_WARPS : EPI_WARPS / 2) * CG);   // the warps that own a shared chunk
         for (int s = 0; s < CLC_ST; s++) {
             ptx::mbar_init(&ctrl->clc_full[s], 1);
             ptx::mbar_init(&ctrl->clc_empty[s], CG);                 // the scheduler warp of every CTA of the pair reads each response
@@ -237,6 +246,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         // ================================ MMA issuer (one thread of the leader CTA)
         if (rank == 0) {
             int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
+            int tiles_done = 0;                 // OVL: tiles this cluster has issued so far
             constexpr uint32_t A_LBO = A_MN ? (BK * 128) : 16, B_LBO = B_MN ? (BK * 128) : 16;
             constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K * 128) : UMMA_K;
             int tile = unit, next_tile;
@@ -247,8 +257,12 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 // into a 128-row scale tile (BN = 192) skips the leading 32-row groups by advancing the column address
                 const uint32_t sfb_off = 4 + (((n_blk * BN) & 127) >> 5);
                 ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                if constexpr (OVL) {
+                    if (tiles_done > 0) ptx::mbar_wait(&ctrl->ovl_free, (tiles_done - 1) & 1);   // previous tile's shared columns are in registers
+                    tiles_done++;
+                }
                 ptx::tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * BN;
+                const uint32_t tmem_d = tmem_base + acc * (OVL ? OVL_STRIDE : BN);
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     ptx::tc_fence_after();
@@ -367,16 +381,32 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if constexpr (RES) load_residual(half);
                 ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * BN;
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
+                // OVL: this warp's chunks are walked so that the one lying in the shared columns [192, 256) comes first — the LAST chunk of
+                // the accumulator at column 0 (walk down), the FIRST chunk of the one at column 192 (walk up).  bf16 output: 64-column
+                // chunks, the shared one belongs to one `half`; fp32 output: 32-column chunks, each half owns one of the two shared chunks.
+                const int nmine = (nchunks - half + 1) >> 1;
+                const bool walk_down = OVL && acc == 0;
+                const bool owns_shared = OVL && (p.out_fp32 || half == (acc == 0 ? 1 : 0));
 #pragma unroll 1
-                for (int c = half; c < nchunks; c += 2) {
+                for (int c = walk_down ? half + 2 * (nmine - 1) : half, n = 0; OVL ? (n < nmine) : (c < nchunks); c += walk_down ? -2 : 2, n++) {
                     const int col = n0 + c * ccols;
                     uint32_t r0[32], r1[32];
                     ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
                     if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
                     ptx::tmem_ld_wait();
-                    if (c + 2 >= nchunks) release_acc(acc);           // this warp's share of the accumulator is in registers
+                    if constexpr (OVL) {
+                        if (n == 0 && owns_shared) {                    // the shared columns are in registers: the next tile's MMAs may overwrite them
+                            ptx::tc_fence_before();
+                            __syncwarp();
+                            if (lane == 0) {
+                                if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ctrl->ovl_free), 0));
+                                else ptx::mbar_arrive(&ctrl->ovl_free);
+                            }
+                        }
+                    }
+                    if (OVL ? (n + 1 == nmine) : (c + 2 >= nchunks)) release_acc(acc);           // this warp's share of the accumulator is in registers
                     else __syncwarp();
                     uint8_t* sbuf = stg + lane * 128;
                     const uint32_t sw = lane & 7;
@@ -527,10 +557,10 @@ void gemm_debug(int d) { g_debug = d; }
 void gemm_force_bn(int bn) { g_bn_override = bn; }
 void gemm_force_cg(int cg) { g_cg_override = cg; }
 
-template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false>
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false>
 static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
                           const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES>;
+    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES, OVL>;
     static bool configured = false;   // benign race: the attribute call is idempotent
     if (!configured) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
@@ -562,6 +592,11 @@ static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const 
         if (a_mn || b_mn) { set_error("fp8_gemm: the fused residual is built for the fprop layout only (A, B K-major)"); return -1; }
         if (mx) return launch_variant<CG, false, false, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
         return launch_variant<CG, false, false, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+    }
+    if (p.acc_overlap) {       // MX, 256 columns, two overlapping accumulators
+        if (!a_mn && !b_mn) return launch_variant<CG, false, false, true, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        if (!a_mn && b_mn) return launch_variant<CG, false, true, true, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+        return launch_variant<CG, true, true, true, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
     }
     if (!mx) {
         if (!a_mn && !b_mn) return launch_variant<CG, false, false, false>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
@@ -638,7 +673,9 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     p.debug = g_debug;
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
-    p.acc_stages = (mx && BN > 192) ? 1 : 2;
+    // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
+    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && !residual) ? 1 : 0;
+    p.acc_stages = (mx && BN > 192 && !p.acc_overlap) ? 1 : 2;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;
     int stages = (SMEM_BUDGET - fixed) / stage_bytes;

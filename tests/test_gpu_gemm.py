@@ -246,6 +246,43 @@ def test_gemm_full_shape_checksum(cg, force):
     assert err < 1e-5, err
 
 
+@pytest.mark.parametrize("M,N,K", [(6144, 28672, 4096), (992, 1344, 992), (512, 768, 4096)])
+@pytest.mark.parametrize("layout", ["fprop", "dgrad", "wgrad"])
+def test_mxfp8_gemm_overlapped_accumulators_identical(M, N, K, layout, force):
+    """MX at 256 columns runs two TMEM accumulators that share 64 columns (gemm.cu: OVL); debug bit 4 selects the single-accumulator
+    kernel.  Both issue the same MMAs in the same order, so bf16 and fp32 outputs must be bit-identical — on the Llama-3.1-8B fc1 shape
+    (36 tiles per CTA pair), a ragged shape and a single-CTA shape.  Same calls as tools/gemm_ovl_check.py
+    (profiles/r01c_gemm_ovl_check.txt)."""
+    ops = _ops()
+    from llm_fp8_b200 import _lib
+    lib = _lib.load()
+    force(256, 0)
+    dev = "cuda"
+
+    def run(dt):
+        g = torch.Generator(device=dev).manual_seed(M + 3 * N + 7 * K)
+        r = lambda *s: torch.randint(0, 120, s, device=dev, dtype=torch.uint8, generator=g)
+        sf = lambda rows, k: torch.randint(120, 134, (ops.mx_scale_bytes(rows, k),), device=dev, dtype=torch.uint8, generator=g)
+        x, w, dy = r(M, K), r(N, K), r(M, N)
+        if layout == "fprop":
+            return ops.mxfp8_gemm(x, sf(M, K), False, w, sf(N, K), False, M, N, K, out_dtype=dt)
+        if layout == "dgrad":
+            return ops.mxfp8_gemm(dy, sf(M, N), False, w, sf(K, N), True, M, K, N, out_dtype=dt)
+        return ops.mxfp8_gemm(dy, sf(N, M), True, x, sf(K, M), True, N, K, M, out_dtype=dt)
+
+    try:
+        for dt in (torch.bfloat16, torch.float32):
+            lib.llmfp8_gemm_debug(16)
+            single = run(dt)
+            lib.llmfp8_gemm_debug(0)
+            ovl = run(dt)
+            torch.cuda.synchronize()
+            assert torch.isfinite(ovl.float()).all()
+            assert torch.equal(single, ovl), f"{layout} {dt}"
+    finally:
+        lib.llmfp8_gemm_debug(0)
+
+
 # ------------------------------------------------------------------------------------------------ fused residual epilogue
 @pytest.mark.parametrize("cg,bn", [(0, 0), (1, 128), (1, 256), (2, 192), (2, 256)])
 def test_fp8_gemm_fused_residual(cg, bn, force):
