@@ -1,4 +1,4 @@
-"""Drop-in check: the reference's OWN decoder-swap files (te_llama.py, te_llama_hybrid.py, te_llama_mxfp8.py) are imported
+"""Drop-in check: the reference's OWN decoder-swap files (te_llama.py, te_llama_hybrid.py, te_llama_mxfp8.py, te_qwen.py) are imported
 UNMODIFIED through the in-tree `transformer_engine` shim and build their TELlamaDecoderLayer / TELlamaForCausalLM on it.
 
 Runs where /root/reference exists (the authoring container); skipped on the GPU box, where
@@ -95,3 +95,60 @@ def test_forward_without_gpu_fails_loudly(no_cuda_move):
     layer = ref.TELlamaDecoderLayer(_tiny_config())
     with pytest.raises(RuntimeError, match="CUDA|no CPU"):
         layer(torch.zeros(1, 8, 256))
+
+
+# ------------------------------------------------------------------------------------------------ te_qwen.py
+def _tiny_qwen_config(ref):
+    return ref.Qwen3Config(vocab_size=128, hidden_size=256, num_attention_heads=4, num_key_value_heads=2, intermediate_size=512,
+                           max_position_embeddings=64, rms_norm_eps=1e-6, num_hidden_layers=2, head_dim=64)
+
+
+def test_reference_te_qwen_builds_on_the_shim(no_cuda_move):
+    """te_qwen.py:76-106 builds the same module pair through signature filtering (`_filter_kwargs_by_sig`, :60-66): every keyword
+    it passes must be a NAMED parameter of our constructors or it is silently dropped — num_gqa_groups in particular (:88-90)."""
+    import llm_fp8_b200 as ours
+    ref = _load("te_qwen")
+    cfg = _tiny_qwen_config(ref)
+    layer = ref.TEQwen3DecoderLayer(cfg)
+    mha, mlp = layer.self_attention, layer.layernorm_mlp
+    assert isinstance(mha, ours.MultiheadAttention) and isinstance(mlp, ours.LayerNormMLP)
+    assert mha.num_gqa_groups == 2 and mha.qkv_format == "bshd" and mha.layernorm_qkv.eps == 1e-6 and mha.dropout == 0.0
+    assert mha.layernorm_qkv.query_weight.shape == (256, 256) and mha.layernorm_qkv.key_weight.shape == (128, 256)
+    assert mha.proj.bias is None and mlp.fc1_weight.shape == (1024, 256) and mlp.fc2_weight.shape == (256, 512)
+    assert ref.attn_recipe.fp8_format is ours.Format.HYBRID and ref.mlp_recipe.fp8_format is ours.Format.E4M3   # te_qwen.py:72-73
+    # rope cache without position ids (te_qwen.py:108-133): [S, 1, 1, head_dim] table from RotaryPositionEmbedding(head_dim, rope_theta=?)
+    rope = layer._get_rope_slice(16, torch.device("cpu"), None)
+    assert isinstance(rope, torch.Tensor) and rope.shape == (16, 1, 1, 64)
+    # the forward call filters its keywords by OUR forward signature (te_qwen.py:270-271): the KV-cache keywords must not get through
+    import inspect
+    allowed = set(inspect.signature(mha.forward).parameters)
+    assert {"attention_mask", "rotary_pos_emb"} <= allowed and not ({"past_key_value", "use_cache", "output_attentions"} & allowed)
+    import transformer_engine as te
+    assert te.pytorch.is_fp8_available() in (True, False)            # te_qwen.py:268
+
+
+def test_reference_te_qwen_causal_lm_and_replace_params(no_cuda_move):
+    """TEQwen3ForCausalLM.__new__ (te_qwen.py:298-302) + replace_params (:346-389): gate rows first, then up rows, in fc1_weight."""
+    ref = _load("te_qwen")
+    cfg = _tiny_qwen_config(ref)
+    model = ref.TEQwen3ForCausalLM(cfg)
+    assert all(type(l).__name__ == "TEQwen3DecoderLayer" for l in model.model.layers)
+    torch.manual_seed(0)
+    sd = ref.Qwen3ForCausalLM(cfg).state_dict()
+    ref.replace_params(sd, model.state_dict(), cfg)
+    l1 = model.model.layers[1]
+    I = cfg.intermediate_size
+    assert torch.equal(l1.layernorm_mlp.fc1_weight[:I], sd["model.layers.1.mlp.gate_proj.weight"])
+    assert torch.equal(l1.layernorm_mlp.fc1_weight[I:], sd["model.layers.1.mlp.up_proj.weight"])
+    assert torch.equal(l1.layernorm_mlp.fc2_weight, sd["model.layers.1.mlp.down_proj.weight"])
+    assert torch.equal(l1.self_attention.layernorm_qkv.key_weight, sd["model.layers.1.self_attn.k_proj.weight"])
+    assert torch.equal(l1.self_attention.proj.weight, sd["model.layers.1.self_attn.o_proj.weight"])
+    assert torch.equal(l1.layernorm_mlp.layer_norm_weight, sd["model.layers.1.post_attention_layernorm.weight"])
+
+
+def test_reference_te_qwen_forward_without_gpu_fails_loudly(no_cuda_move):
+    """No CPU fallback behind the Qwen swap either: in training mode (fp8 enabled, te_qwen.py:268-269) a CPU forward raises."""
+    ref = _load("te_qwen")
+    layer = ref.TEQwen3DecoderLayer(_tiny_qwen_config(ref)).train()
+    with pytest.raises(RuntimeError):
+        layer(torch.randn(2, 16, 256, dtype=torch.bfloat16))
