@@ -62,7 +62,8 @@ struct GemmParams {
     int stages;                 // smem ring depth
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
-                                // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL)
+                                // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
+                                // bit 5 = OVL also for the fused-residual MX kernel (unverified on hardware)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
@@ -378,7 +379,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     for (int g = 0; g < (RES ? 8 : 1); g++)
                         rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
                 };
-                if constexpr (RES) load_residual(half);
+                if constexpr (RES) load_residual((OVL && acc == 0) ? half + 2 * (((nchunks - half + 1) >> 1) - 1) : half);   // the chunk the walk below starts with
                 ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
@@ -447,7 +448,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                             }
                         }
                         if constexpr (RES) {
-                            if (c + 2 < nchunks) load_residual(c + 2);     // rv is free again: next chunk's segment, under the store below
+                            // rv is free again: next chunk's segment, under the store below
+                            if (OVL ? (n + 1 < nmine) : (c + 2 < nchunks)) load_residual(c + (walk_down ? -2 : 2));
                         }
                         ptx::fence_proxy_async();
                         __syncwarp();
@@ -590,6 +592,7 @@ static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const 
                     const CUtensorMap& md, const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
     if (p.residual) {
         if (a_mn || b_mn) { set_error("fp8_gemm: the fused residual is built for the fprop layout only (A, B K-major)"); return -1; }
+        if (mx && p.acc_overlap) return launch_variant<CG, false, false, true, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
         if (mx) return launch_variant<CG, false, false, true, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
         return launch_variant<CG, false, false, false, true>(ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
     }
@@ -674,7 +677,8 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
     // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
-    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && !residual) ? 1 : 0;
+    // (with a fused residual only under debug bit 5: that combination has not run on a GPU yet)
+    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || (g_debug & 32))) ? 1 : 0;
     p.acc_stages = (mx && BN > 192 && !p.acc_overlap) ? 1 : 2;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;

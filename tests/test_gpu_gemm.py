@@ -1,4 +1,6 @@
 """FP8 / MXFP8 GEMMs through the C ABI against the oracle's dequantise -> fp32 matmul (BASELINE.json: rel. tol 1e-2 on bf16)."""
+import os
+
 import pytest
 import torch
 
@@ -279,6 +281,38 @@ def test_mxfp8_gemm_overlapped_accumulators_identical(M, N, K, layout, force):
             torch.cuda.synchronize()
             assert torch.isfinite(ovl.float()).all()
             assert torch.equal(single, ovl), f"{layout} {dt}"
+    finally:
+        lib.llmfp8_gemm_debug(0)
+
+
+EXPERIMENTAL = pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
+                                  reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
+
+
+@EXPERIMENTAL
+@pytest.mark.parametrize("M,N,K", [(6144, 4096, 14336), (1000, 1544, 640), (512, 768, 4096)])
+def test_mxfp8_gemm_residual_overlapped_accumulators_identical(M, N, K, force):
+    """Debug bit 5: the fused-residual MX epilogue on the overlapped accumulators (gemm.cu: RES + OVL).  Same MMAs, same fp32 sum,
+    same single bf16 rounding as the single-accumulator residual kernel -> bit-identical."""
+    ops = _ops()
+    from llm_fp8_b200 import _lib
+    lib = _lib.load()
+    force(256, 0)
+    dev = "cuda"
+    g = torch.Generator(device=dev).manual_seed(M + N + K)
+    x = torch.randint(0, 120, (M, K), device=dev, dtype=torch.uint8, generator=g)
+    w = torch.randint(0, 120, (N, K), device=dev, dtype=torch.uint8, generator=g)
+    sx = torch.randint(120, 134, (ops.mx_scale_bytes(M, K),), device=dev, dtype=torch.uint8, generator=g)
+    sw = torch.randint(120, 134, (ops.mx_scale_bytes(N, K),), device=dev, dtype=torch.uint8, generator=g)
+    res = torch.randn(M, N, device=dev, generator=g).bfloat16() * 100
+    bias = torch.randn(N, device=dev, generator=g).bfloat16()
+    try:
+        lib.llmfp8_gemm_debug(0)
+        want = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res)
+        lib.llmfp8_gemm_debug(32)
+        got = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res)
+        torch.cuda.synchronize()
+        assert torch.equal(want, got)
     finally:
         lib.llmfp8_gemm_debug(0)
 
