@@ -92,6 +92,43 @@ def _weight_mx(wcache, first, key, weight, need_col: bool) -> "ops.MXTensor":
     return wq
 
 
+# Experimental, off unless LLMFP8_WGRAD_STREAM=1 (written without a GPU at hand; tests/test_gpu_modules.py has the gated check):
+# dgrad and wgrad of one linear are independent.  With the wgrad GEMM issued on a side stream its CTAs fill the SMs that the dgrad
+# GEMM's last, partial wave leaves idle (an [M, 4096] output at 8B shapes is 5.2 waves of 256 x 256 tiles: 14 % of that launch) and
+# run under the RMSNorm backward / dSwiGLU that follow on the main stream.  The main stream rejoins before backward returns, so
+# autograd (and the gradient all-reduce hooks) see the weight gradient in stream order as before.
+WGRAD_SIDE_STREAM = os.environ.get("LLMFP8_WGRAD_STREAM", "0") == "1"
+_side_streams = {}
+
+
+class _SideWgrad:
+    def __init__(self, device: torch.device):
+        self.on = WGRAD_SIDE_STREAM and device.type == "cuda"
+        self.outs = []
+        if self.on:
+            idx = device.index if device.index is not None else torch.cuda.current_device()
+            self.side = _side_streams.get(idx)
+            if self.side is None:
+                self.side = _side_streams[idx] = torch.cuda.Stream(device=idx)
+            self.main = torch.cuda.current_stream(idx)
+
+    def run(self, fn):
+        """fn() launches one wgrad GEMM and returns its output; its operands were produced on the main stream before this call."""
+        if not self.on:
+            return fn()
+        self.side.wait_stream(self.main)
+        with torch.cuda.stream(self.side):
+            out = fn()
+        self.outs.append(out)
+        return out
+
+    def join(self):
+        if self.on and self.outs:
+            self.main.wait_stream(self.side)
+            for o in self.outs:
+                o.record_stream(self.main)       # allocated from the side stream's pool, consumed on the main stream
+
+
 def _wgrad(dyq, xq, N, K, T, weight):
     """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
     return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
@@ -153,13 +190,15 @@ class LinearFn(torch.autograd.Function):
             dyq, dbias = ops.quantize_bgrad(dy2, bf, pb, b0 + 0)
         else:
             dyq = ops.quantize(dy2, bf, pb, b0 + 0)
+        wg = _SideWgrad(dy2.device)
         dx = ops.fp8_gemm(dyq, False, wq, True, M, K, N)                  # dgrad: contraction over N, W read MN-major
-        dw = ops.fp8_gemm(dyq, True, xq, True, N, K, M, out_dtype=ctx.wdtype)   # wgrad: contraction over tokens
+        dw = wg.run(lambda: ops.fp8_gemm(dyq, True, xq, True, N, K, M, out_dtype=ctx.wdtype))   # wgrad: contraction over tokens
         dgamma = None
         if ln_weight is not None:
             dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
         elif dres is not None:
             dx = dx + _2d(dres)
+        wg.join()
         Fp8Meta.end_bwd(s)
         return dx.reshape(ctx.shape), dw, dbias, None, None, dgamma, None, None, (dy if ctx.has_residual else None), None, None, None
 
@@ -215,10 +254,12 @@ class LayerNormMLPFn(torch.autograd.Function):
             dyq = ops.quantize(dy2, bf, pb, b0 + 2)
         da = ops.fp8_gemm(dyq, False, w2q, True, M, I, H)                        # fc2 dgrad
         dfc1q, db1 = ops.dswiglu_quant(da, fc1, bf, pb, b0 + 0, want_dbias=ctx.has_bias)
-        dw2 = ops.fp8_gemm(dyq, True, aq, True, H, I, M, out_dtype=ctx.wdtype)   # fc2 wgrad
+        wg = _SideWgrad(dy2.device)
+        dw2 = wg.run(lambda: ops.fp8_gemm(dyq, True, aq, True, H, I, M, out_dtype=ctx.wdtype))   # fc2 wgrad
         dln = ops.fp8_gemm(dfc1q, False, w1q, True, M, H, 2 * I)                 # fc1 dgrad
-        dw1 = ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype)   # fc1 wgrad
+        dw1 = wg.run(lambda: ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype))   # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
+        wg.join()
         Fp8Meta.end_bwd(s)
         return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None, None, None, None, None
 
@@ -279,14 +320,16 @@ class MXLinearFn(torch.autograd.Function):
         dbias = _mx_bgrad(dy2) if ctx.has_bias else None
         dyq = ops.mx_quantize(dy2, True, True)
         # dgrad: dX[M,K] = dY[M,N] W[N,K]: dY rowwise (blocks along N), W colwise (blocks along N), W read MN-major
+        wg = _SideWgrad(dy2.device)
         dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N)
         # wgrad: dW[N,K] = dY^T X: both colwise (blocks along tokens), both MN-major
-        dw = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out_dtype=ctx.wdtype)
+        dw = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out_dtype=ctx.wdtype))
         dgamma = None
         if ln_weight is not None:
             dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
         elif dres is not None:
             dx = dx + _2d(dres)
+        wg.join()
         return dx.reshape(ctx.shape), dw, dbias, dgamma, None, None, (dy if ctx.has_residual else None), None, None, None
 
 
@@ -326,8 +369,10 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         da = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w2_col, w2_sfc, True, M, I, H)                       # fc2 dgrad
         dfc1, db1 = ops.dswiglu_bf16(da, fc1, want_dbias=ctx.has_bias)
         dfq = ops.mx_quantize(dfc1, True, True)
-        dw2 = ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype)      # fc2 wgrad
+        wg = _SideWgrad(dy2.device)
+        dw2 = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype))      # fc2 wgrad
         dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad
-        dw1 = ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype)  # fc1 wgrad
+        dw1 = wg.run(lambda: ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype))  # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
+        wg.join()
         return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None

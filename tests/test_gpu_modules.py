@@ -1,5 +1,7 @@
 """Module-level parity: Linear / LayerNormLinear / LayerNormMLP forward + backward against an oracle emulation of the same
 quantise -> GEMM sequence, over several steps so the delayed-scaling state (history, scales) is exercised."""
+import os
+
 import pytest
 import torch
 
@@ -295,3 +297,40 @@ def test_is_first_microbatch_keeps_weight_copies(recipe_name):
             close(gb, ga, 1e-1, "dx")
         close(kept[1], base[1], 1e-1, "dW1")
         close(kept[2], base[2], 1e-1, "dW")
+
+
+@pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
+                    reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
+def test_wgrad_side_stream_matches_main_stream():
+    """functional.WGRAD_SIDE_STREAM: the wgrad GEMMs of every linear on a side stream (joined before backward returns).  Stream
+    placement changes no arithmetic: MXFP8 has no scaling state, so weight / input gradients must be bit-identical over several
+    steps (a missing dependency would show up as a stale operand)."""
+    import llm_fp8_b200 as te
+    from llm_fp8_b200 import functional as fn
+    te.reset_fp8_state()
+    recipe = te.MXFP8BlockScaling(fp8_format=te.Format.E4M3)
+    torch.manual_seed(3)
+    H, I = 1024, 4096
+    m = te.LayerNormMLP(H, I, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16, device="cuda")
+    lin = te.LayerNormLinear(H, 1536, bias=False, normalization="RMSNorm", params_dtype=torch.bfloat16, device="cuda")
+    xs = [rnd((4, 512, H), 60 + i).cuda().requires_grad_(True) for i in range(3)]
+
+    def run(flag):
+        fn.WGRAD_SIDE_STREAM = flag
+        out = []
+        for x in xs:
+            m.zero_grad(); lin.zero_grad(); x.grad = None
+            with te.fp8_autocast(enabled=True, fp8_recipe=recipe):
+                y = lin(m(x))
+            y.float().pow(2).mean().backward()
+            out.append([t.clone() for t in (y.detach(), x.grad, m.fc1_weight.grad, m.fc2_weight.grad, lin.weight.grad, m.layer_norm_weight.grad)])
+        torch.cuda.synchronize()
+        return out
+
+    try:
+        base, side = run(False), run(True)
+    finally:
+        fn.WGRAD_SIDE_STREAM = False
+    for a, b in zip(base, side):
+        for ta, tb in zip(a, b):
+            assert torch.equal(ta, tb)
