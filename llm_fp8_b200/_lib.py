@@ -71,6 +71,9 @@ def load():
                 fn.restype = _RESTYPES.get(name, i32)
             if lib.llmfp8_abi_version() != 1:
                 raise RuntimeError("libllmfp8_b200.so ABI version mismatch")
+            dbg = os.environ.get("LLMFP8_GEMM_DEBUG")          # experiments only: the bits of llmfp8_gemm_debug (include/llmfp8_b200.h)
+            if dbg:
+                lib.llmfp8_gemm_debug(int(dbg, 0))
             _lib = lib
     return _lib
 
