@@ -91,6 +91,19 @@ int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, v
 int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
                           const float* rsigma, const void* gamma, void* stream);
 int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream);
+/* K3m: SwiGLU + MXFP8 quantiser in one pass.  fc1_out bf16 [M, 2I] (gate | up) -> a = bf16(silu(gate) * up) [M, I], never written to
+ * memory -> rowwise and/or colwise MXFP8 copies of a (layouts as llmfp8_mx_quantize).  Bit-identical to llmfp8_swiglu_quant_fwd(fmt = bf16)
+ * followed by llmfp8_mx_quantize.  I % 32 == 0; colwise needs M % 32 == 0.
+ * [LayerNormMLP(activation="swiglu") under MXFP8BlockScaling: TE's swiglu + mxfp8 cast, te_llama_mxfp8.py:93]
+ * Status: not yet run on hardware (written after the round-1 GPU budget was spent); the Python host selects it only with
+ * LLMFP8_MX_FUSED_ACT=1. */
+int llmfp8_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col, void* stream);
+/* K3m backward: da bf16 [M, I], fc1_out bf16 [M, 2I] -> dfc1 = bf16(dgate | dup) [M, 2I], never written to memory -> rowwise and/or
+ * colwise MXFP8 copies of dfc1; dbias[2I] = column sums of the fp32 (dgate | dup) (dbias_ws fp32 [2I] workspace and dbias bf16 [2I] go
+ * together, both NULL = no bias gradient).  Bit-identical (data, scales) to llmfp8_dswiglu_quant_bwd(fmt = bf16) + llmfp8_mx_quantize.
+ * I % 128 == 0; colwise needs M % 32 == 0.  Same status as llmfp8_mx_swiglu_quantize. */
+int llmfp8_mx_dswiglu_quantize(const void* da, const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                               float* dbias_ws, void* dbias, void* stream);
 /* bytes of the swizzled scale tensor of a matrix with `rows` rows and `k` elements along the blocked dimension */
 int64_t llmfp8_mx_scale_bytes(int64_t rows, int64_t k);
 

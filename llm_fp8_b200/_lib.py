@@ -34,6 +34,8 @@ _PROTOTYPES = {
     "llmfp8_amax_scale_update": [vp, vp, vp, vp, i32, i32, i32, vp],
     "llmfp8_mx_quantize": [vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_mx_quantize_ld": [vp, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp],
+    "llmfp8_mx_swiglu_quantize": [vp, i64, i64, vp, vp, vp, vp, vp],
+    "llmfp8_mx_dswiglu_quantize": [vp, vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_rsigma": [vp, vp, i64, i64, f32, vp],
     "llmfp8_mx_scale_bytes": [i64, i64],
     "llmfp8_gemm_force_bn": [i32],
@@ -107,6 +109,12 @@ def _work(name: str, a):
     if name == "llmfp8_mx_quantize":
         rc = float(a[1]) * a[2]
         return "byte", 2.0 * rc + (rc + rc / 32) * ((a[3] is not None) + (a[5] is not None))
+    if name == "llmfp8_mx_swiglu_quantize":       # read gate | up (4 B per output element), write the copies + scales
+        mi = float(a[1]) * a[2]
+        return "byte", 4.0 * mi + (mi + mi / 32) * ((a[3] is not None) + (a[5] is not None))
+    if name == "llmfp8_mx_dswiglu_quantize":      # read da + gate | up (6 B per [M, I] element), write the copies + scales of [M, 2I]
+        mi = float(a[2]) * a[3]
+        return "byte", 6.0 * mi + 2.0 * (mi + mi / 32) * ((a[4] is not None) + (a[6] is not None))
     if name == "llmfp8_mx_quantize_ld":
         rc = float(a[2]) * a[3]
         return "byte", 2.0 * rc + (rc + rc / 32) * ((a[4] is not None) + (a[6] is not None))

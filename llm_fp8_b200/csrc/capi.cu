@@ -105,6 +105,8 @@ int rmsnorm_bwd_grid(int64_t);
 int launch_swiglu_quant_fwd(const void*, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
 int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
 int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
+int launch_mx_swiglu_quantize(const void*, int64_t, int64_t, void*, void*, void*, void*, cudaStream_t);
+int launch_mx_dswiglu_quantize(const void*, const void*, int64_t, int64_t, void*, void*, void*, void*, float*, void*, cudaStream_t);
 int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
                     const void*, const void*, const void*, const void*, int64_t, int, int, cudaStream_t);
 int comm_unique_id(void*);
@@ -169,6 +171,13 @@ int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, v
 int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
                           const float* rsigma, const void* gamma, void* stream) {
     return launch_mx_quantize(x, ldx, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+}
+int llmfp8_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col, void* stream) {
+    return launch_mx_swiglu_quantize(fc1_out, M, I, q_row, sf_row, q_col, sf_col, S(stream));
+}
+int llmfp8_mx_dswiglu_quantize(const void* da, const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                               float* dbias_ws, void* dbias, void* stream) {
+    return launch_mx_dswiglu_quantize(da, fc1_out, M, I, q_row, sf_row, q_col, sf_col, dbias_ws, dbias, S(stream));
 }
 int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream) {
     return launch_rmsnorm_rsigma(x, rsigma, M, H, eps, S(stream));

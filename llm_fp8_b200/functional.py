@@ -272,6 +272,11 @@ class LayerNormMLPFn(torch.autograd.Function):
 MX_EPILOGUE_RESIDUAL = os.environ.get("LLMFP8_MX_EPILOGUE_RESIDUAL", "0") == "1"
 
 
+# SwiGLU / dSwiGLU fused with the block quantiser (csrc/mx_act_quantize.cu): bit-identical by construction to the two-kernel sequences
+# below, minus the bf16 intermediate's round trip through HBM.  Not yet run on hardware -> off unless LLMFP8_MX_FUSED_ACT=1.
+MX_FUSED_ACT = os.environ.get("LLMFP8_MX_FUSED_ACT", "0") == "1"
+
+
 def _mx_gemm_residual(a, sfa, b, sfb, M, N, K, bias, residual):
     """fprop block-scaled GEMM (+bias) (+residual [M, N] bf16, rows possibly spaced)."""
     if residual is None or MX_EPILOGUE_RESIDUAL:
@@ -348,8 +353,11 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         lnq = ops.mx_quantize(x2, True, g, rsigma, ln_weight)
         w1q = _weight_mx(wcache, first, ("w1", "mx"), w1, g)
         fc1 = ops.mxfp8_gemm(lnq.row, lnq.sf_row, False, w1q.row, w1q.sf_row, False, M, I2, H, bias=b1)
-        a = ops.swiglu_bf16(fc1)
-        aq = ops.mx_quantize(a, True, g)
+        if MX_FUSED_ACT:
+            aq = ops.mx_swiglu_quantize(fc1, True, g)
+        else:
+            a = ops.swiglu_bf16(fc1)
+            aq = ops.mx_quantize(a, True, g)
         w2q = _weight_mx(wcache, first, ("w2", "mx"), w2, g)
         y = _mx_gemm_residual(aq.row, aq.sf_row, w2q.row, w2q.sf_row, M, H, I, b2, x2 if residual else None)
         if g:
@@ -367,8 +375,11 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         db2 = _mx_bgrad(dy2) if ctx.has_bias else None
         dyq = ops.mx_quantize(dy2, True, True)
         da = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w2_col, w2_sfc, True, M, I, H)                       # fc2 dgrad
-        dfc1, db1 = ops.dswiglu_bf16(da, fc1, want_dbias=ctx.has_bias)
-        dfq = ops.mx_quantize(dfc1, True, True)
+        if MX_FUSED_ACT and I % 128 == 0:
+            dfq, db1 = ops.mx_dswiglu_quantize(da, fc1, True, True, want_dbias=ctx.has_bias)
+        else:
+            dfc1, db1 = ops.dswiglu_bf16(da, fc1, want_dbias=ctx.has_bias)
+            dfq = ops.mx_quantize(dfc1, True, True)
         wg = _SideWgrad(dy2.device)
         dw2 = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype))      # fc2 wgrad
         dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad

@@ -333,3 +333,45 @@ def dswiglu_bf16(da: torch.Tensor, fc1_out: torch.Tensor, want_dbias: bool = Tru
                                               ws.data_ptr() if want_dbias else None, dbias.data_ptr() if want_dbias else None, _stream(da))
     _lib.check(rc, "dswiglu_quant_bwd(bf16)")
     return d, dbias
+
+
+# ------------------------------------------------------------------------------------------ activation + MXFP8 quantiser in one pass
+# (csrc/mx_act_quantize.cu — not yet run on hardware; functional.py selects these only with LLMFP8_MX_FUSED_ACT=1)
+def _mx_out(R: int, C: int, rowwise: bool, colwise: bool, dev) -> MXTensor:
+    out = MXTensor(R, C)
+    if rowwise:
+        out.row = torch.empty((R, C), dtype=torch.uint8, device=dev)
+        out.sf_row = torch.empty(mx_scale_bytes(R, C), dtype=torch.uint8, device=dev)
+    if colwise:
+        out.col = torch.empty((R, C), dtype=torch.uint8, device=dev)
+        out.sf_col = torch.empty(mx_scale_bytes(C, R), dtype=torch.uint8, device=dev)
+    return out
+
+
+def _p(t: Optional[torch.Tensor]):
+    return t.data_ptr() if t is not None else None
+
+
+def mx_swiglu_quantize(fc1_out: torch.Tensor, rowwise: bool = True, colwise: bool = True) -> MXTensor:
+    """== mx_quantize(swiglu_bf16(fc1_out), rowwise, colwise) without the bf16 activation ever reaching HBM."""
+    fc1_out = _req(fc1_out, torch.bfloat16)
+    M, I2 = fc1_out.shape
+    out = _mx_out(M, I2 // 2, rowwise, colwise, fc1_out.device)
+    rc = _lib.load().llmfp8_mx_swiglu_quantize(fc1_out.data_ptr(), M, I2 // 2, _p(out.row), _p(out.sf_row), _p(out.col), _p(out.sf_col), _stream(fc1_out))
+    _lib.check(rc, "mx_swiglu_quantize")
+    return out
+
+
+def mx_dswiglu_quantize(da: torch.Tensor, fc1_out: torch.Tensor, rowwise: bool = True, colwise: bool = True, want_dbias: bool = True):
+    """== (mx_quantize(d, rowwise, colwise), dbias) for d, dbias = dswiglu_bf16(da, fc1_out, want_dbias), without d reaching HBM."""
+    da, fc1_out = _req(da, torch.bfloat16), _req(fc1_out, torch.bfloat16)
+    M, I = da.shape
+    if tuple(fc1_out.shape) != (M, 2 * I):
+        raise RuntimeError(f"mx_dswiglu_quantize: fc1_out {tuple(fc1_out.shape)} does not match da {tuple(da.shape)}")
+    out = _mx_out(M, 2 * I, rowwise, colwise, da.device)
+    ws = torch.empty(2 * I, dtype=torch.float32, device=da.device) if want_dbias else None
+    dbias = torch.empty(2 * I, dtype=torch.bfloat16, device=da.device) if want_dbias else None
+    rc = _lib.load().llmfp8_mx_dswiglu_quantize(da.data_ptr(), fc1_out.data_ptr(), M, I, _p(out.row), _p(out.sf_row), _p(out.col), _p(out.sf_col),
+                                                _p(ws), _p(dbias), _stream(da))
+    _lib.check(rc, "mx_dswiglu_quantize")
+    return out, dbias

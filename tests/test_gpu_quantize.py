@@ -305,3 +305,74 @@ def test_rmsnorm_bwd_with_residual_gradient():
         # against the unfused pair: differs by at most the double rounding
         two_step = (dx0.float() + dev(dres).float())
         assert (dx1.float() - two_step).abs().max().item() <= 2.0 ** -7 * two_step.abs().max().item()
+
+
+# ------------------------------------------------------------------------------------------------ activation + MX quantiser in one pass
+import os  # noqa: E402
+
+EXPERIMENTAL = pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
+                                  reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
+
+
+def _assert_mx_equal(got, want):
+    for name in ("row", "sf_row", "col", "sf_col"):
+        g, w = getattr(got, name), getattr(want, name)
+        assert (g is None) == (w is None), name
+        if g is not None:
+            assert torch.equal(g, w), f"{name}: {int((g != w).sum())} of {g.numel()} bytes differ"
+
+
+@EXPERIMENTAL
+@pytest.mark.parametrize("M,I", [(128, 128), (256, 512), (1000 // 32 * 32, 1056), (96, 160), (6144, 14336)])
+@pytest.mark.parametrize("kind", ["normal", "heavy", "outlier"])
+def test_mx_swiglu_quantize_matches_two_kernel_sequence(M, I, kind):
+    """llmfp8_mx_swiglu_quantize == llmfp8_swiglu_quant_fwd(bf16) -> llmfp8_mx_quantize (both pinned to the oracle above), byte for
+    byte: data and swizzled E8M0 scales, rowwise and colwise, full and ragged tiles (I not a multiple of 128: the gate tile must
+    zero-fill past column I, not read the up half)."""
+    ops = _ops()
+    if (M, I) == (6144, 14336) and kind != "normal":
+        pytest.skip("full Llama-3.1-8B shape once")
+    fc1 = dev(gen((M, 2 * I), 900 + M + I, kind) * 3)
+    want = ops.mx_quantize(ops.swiglu_bf16(fc1), True, True)
+    got = ops.mx_swiglu_quantize(fc1, True, True)
+    torch.cuda.synchronize()
+    _assert_mx_equal(got, want)
+    row_only = ops.mx_swiglu_quantize(fc1, True, False)
+    assert row_only.col is None and torch.equal(row_only.row, want.row) and torch.equal(row_only.sf_row, want.sf_row)
+
+
+@EXPERIMENTAL
+@pytest.mark.parametrize("M,I", [(128, 128), (256, 512), (992, 1152), (96, 384), (6144, 14336)])
+@pytest.mark.parametrize("kind", ["normal", "heavy"])
+def test_mx_dswiglu_quantize_matches_two_kernel_sequence(M, I, kind):
+    """llmfp8_mx_dswiglu_quantize == llmfp8_dswiglu_quant_bwd(bf16) -> llmfp8_mx_quantize byte for byte; the bias gradient (fp32 column
+    sums accumulated with atomics in both versions, in different orders) within bf16 rounding of an fp64 sum."""
+    ops = _ops()
+    if (M, I) == (6144, 14336) and kind != "normal":
+        pytest.skip("full Llama-3.1-8B shape once")
+    fc1 = dev(gen((M, 2 * I), 700 + M + I, kind) * 3)
+    da = dev(gen((M, I), 701 + M + I, kind))
+    d, db_want = ops.dswiglu_bf16(da, fc1, want_dbias=True)
+    want = ops.mx_quantize(d, True, True)
+    got, db = ops.mx_dswiglu_quantize(da, fc1, True, True, want_dbias=True)
+    torch.cuda.synchronize()
+    _assert_mx_equal(got, want)
+    ref = db_want.float()
+    assert torch.isfinite(db.float()).all()
+    assert (db.float() - ref).abs().max().item() <= 2e-2 * ref.abs().max().item() + 1e-6
+    got2, none = ops.mx_dswiglu_quantize(da, fc1, True, True, want_dbias=False)
+    assert none is None
+    _assert_mx_equal(got2, want)
+
+
+@EXPERIMENTAL
+def test_mx_act_quantize_contract_errors():
+    ops = _ops()
+    fc1 = torch.zeros(64, 2 * 48, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.mx_swiglu_quantize(fc1)                      # I % 32 != 0
+    fc1 = torch.zeros(64, 2 * 96, dtype=torch.bfloat16, device="cuda")
+    with pytest.raises(RuntimeError):
+        ops.mx_dswiglu_quantize(torch.zeros(64, 96, dtype=torch.bfloat16, device="cuda"), fc1)   # I % 128 != 0
+    with pytest.raises(RuntimeError):
+        ops.mx_swiglu_quantize(torch.zeros(40, 2 * 128, dtype=torch.bfloat16, device="cuda"), True, True)   # colwise needs M % 32 == 0

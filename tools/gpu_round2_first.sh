@@ -1,8 +1,9 @@
 #!/bin/bash
-# First GPU call of the next round (one B200, ~6 min of box time): everything that was written after the round-1 GPU budget ran out.
+# First GPU call of the next round (one B200, ~8 min of box time): everything that was written after the round-1 GPU budget ran out.
 #   /usr/local/graft/bin/gpurun --timeout 900 -- 'bash tools/gpu_round2_first.sh'
 # 1. full GPU suite on the default tree (overlapped-accumulator MX GEMM is the default since d2c7555);
-# 2. the gated experiments' own tests (LLMFP8_EXPERIMENTAL=1): RES + OVL epilogue (debug bit 5), wgrad side stream;
+# 2. the gated experiments' own tests (LLMFP8_EXPERIMENTAL=1): RES + OVL epilogue (debug bit 5), SwiGLU/dSwiGLU fused with the MX
+#    quantiser (LLMFP8_MX_FUSED_ACT), wgrad side stream (LLMFP8_WGRAD_STREAM);
 # 3. bench lines: default tree, then each experiment switched on alone, then together (A/B on the same box, same clocks);
 # 4. GEMM A/B at the 8B shapes (debug 16 = single accumulator vs 0 = overlapped) and the ncu launch list + one full capture.
 mkdir -p gpurun_out
@@ -15,6 +16,8 @@ echo "pytest gpu exit $?  $(tail -1 gpurun_out/r02_pytest_gpu.log)" >> $S
 
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_gemm.py -q -m gpu -p no:cacheprovider -k "residual_overlapped" > gpurun_out/r02_exp_res_ovl.log 2>&1
 echo "exp RES+OVL exit $?  $(tail -1 gpurun_out/r02_exp_res_ovl.log)" >> $S
+LLMFP8_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_quantize.py -q -m gpu -p no:cacheprovider -k "mx_swiglu or mx_dswiglu or mx_act" > gpurun_out/r02_exp_fused_act.log 2>&1
+echo "exp fused act exit $?  $(tail -1 gpurun_out/r02_exp_fused_act.log)" >> $S
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_modules.py -q -m gpu -p no:cacheprovider -k "wgrad_side_stream" > gpurun_out/r02_exp_wgrad_stream.log 2>&1
 echo "exp wgrad stream exit $?  $(tail -1 gpurun_out/r02_exp_wgrad_stream.log)" >> $S
 
@@ -22,6 +25,8 @@ B="timeout 170 python bench.py --steps 5 --warmup 3 --no-cpu-baseline"
 $B > gpurun_out/r02_bench_mxfp8.json 2> gpurun_out/r02_bench_mxfp8.err; echo "bench mxfp8 exit $?" >> $S
 LLMFP8_WGRAD_STREAM=1 $B > gpurun_out/r02_bench_mxfp8_wgradstream.json 2> gpurun_out/r02_bench_mxfp8_wgradstream.err; echo "bench mxfp8 +wgrad stream exit $?" >> $S
 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_resovl.json 2> gpurun_out/r02_bench_mxfp8_resovl.err; echo "bench mxfp8 +RES/OVL exit $?" >> $S
+LLMFP8_MX_FUSED_ACT=1 $B > gpurun_out/r02_bench_mxfp8_fusedact.json 2> gpurun_out/r02_bench_mxfp8_fusedact.err; echo "bench mxfp8 +fused act exit $?" >> $S
+LLMFP8_MX_FUSED_ACT=1 LLMFP8_WGRAD_STREAM=1 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_all.json 2> gpurun_out/r02_bench_mxfp8_all.err; echo "bench mxfp8 all experiments exit $?" >> $S
 LLMFP8_GEMM_DEBUG=16 $B > gpurun_out/r02_bench_mxfp8_singleacc.json 2> gpurun_out/r02_bench_mxfp8_singleacc.err; echo "bench mxfp8 single accumulator exit $?" >> $S
 $B --scenario default > gpurun_out/r02_bench_default.json 2> gpurun_out/r02_bench_default.err; echo "bench default exit $?" >> $S
 LLMFP8_WGRAD_STREAM=1 $B --scenario default > gpurun_out/r02_bench_default_wgradstream.json 2> gpurun_out/r02_bench_default_wgradstream.err; echo "bench default +wgrad stream exit $?" >> $S
