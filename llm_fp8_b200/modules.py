@@ -8,6 +8,7 @@ modules raise: this package is the FP8 path only and carries no bf16 fallback im
 from __future__ import annotations
 
 import math
+import os
 from typing import Optional, Tuple, Union
 
 import torch
@@ -98,6 +99,48 @@ class Linear(_Fp8Module):
         return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False, self._wcache, is_first_microbatch)
 
 
+_JOIN_SPLIT_WEIGHTS = os.environ.get("LLMFP8_JOIN_SPLIT_WEIGHTS", "1") != "0"
+
+
+def _joined_rows(params, joined: Optional[torch.Tensor]) -> torch.Tensor:
+    """-> the [sum of rows, in] tensor whose consecutive row slices ARE the storage of `params`.  Parameters are separate tensors after
+    construction and after anything that goes through Module._apply (.cuda(), .to(dtype)) or re-assigns them; whenever the aliasing
+    does not hold (checked by address) the rows are gathered once into a new buffer and each Parameter's .data is re-pointed at its
+    slice.  In-place updates (optimizer steps, load_state_dict, replace_params' .data.copy_: te_llama.py:196-238) keep it."""
+    p0 = params[0]
+    cols, item = p0.shape[1], p0.element_size()
+    ok = joined is not None and joined.device == p0.device and joined.dtype == p0.dtype and joined.shape[1] == cols
+    if ok:
+        addr = joined.data_ptr()
+        for p in params:
+            ok = ok and p.dtype == p0.dtype and p.is_contiguous() and p.data_ptr() == addr
+            addr += p.shape[0] * cols * item
+        ok = ok and addr == joined.data_ptr() + joined.numel() * item
+    if ok:
+        return joined
+    with torch.no_grad():
+        joined = torch.cat([p.detach() for p in params], dim=0)
+        off = 0
+        for p in params:
+            p.data = joined[off:off + p.shape[0]]
+            off += p.shape[0]
+    return joined
+
+
+class _JoinRows(torch.autograd.Function):
+    """joined buffer in, the same memory out — with the split Parameters as autograd inputs, so that the weight gradient [out, in] a
+    linear Function returns is routed to them as row slices (views: no split copies either)."""
+
+    @staticmethod
+    def forward(ctx, joined, *params):
+        ctx.sizes = [p.shape[0] for p in params]
+        return joined.detach()
+
+    @staticmethod
+    def backward(ctx, dw):
+        return (None,) + tuple(dw.split(ctx.sizes, dim=0))
+
+
 class LayerNormLinear(_Fp8Module):
     """RMSNorm fused into the FP8 input cast, then one GEMM.  With `parameters_split` the weight is exposed as separate
     `<name>_weight` Parameters (query/key/value: te_llama.py:198-211) that feed a single GEMM."""
@@ -139,7 +182,14 @@ class LayerNormLinear(_Fp8Module):
     def _weight_bias(self):
         if self._split is None:
             return self.weight, self.bias
-        w = torch.cat([getattr(self, n + "weight") for n in self._split], dim=0)
+        ws = [getattr(self, n + "weight") for n in self._split]
+        if _JOIN_SPLIT_WEIGHTS:
+            # the split Parameters live as row slices of ONE [out, in] buffer: the GEMM path reads it in place (no torch.cat of the
+            # weight per forward: 2 x 50 MB of traffic for the qkv weight at 8B) and the wgrad output is handed back as row slices
+            self._joined = _joined_rows(ws, getattr(self, "_joined", None))
+            w = _JoinRows.apply(self._joined, *ws)
+        else:
+            w = torch.cat(ws, dim=0)
         b = torch.cat([getattr(self, n + "bias") for n in self._split], dim=0) if self.use_bias else None
         return w, b
 
