@@ -27,6 +27,7 @@ LLMFP8_WGRAD_STREAM=1 $B > gpurun_out/r02_bench_mxfp8_wgradstream.json 2> gpurun
 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_resovl.json 2> gpurun_out/r02_bench_mxfp8_resovl.err; echo "bench mxfp8 +RES/OVL exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 $B > gpurun_out/r02_bench_mxfp8_fusedact.json 2> gpurun_out/r02_bench_mxfp8_fusedact.err; echo "bench mxfp8 +fused act exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 LLMFP8_WGRAD_STREAM=1 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_all.json 2> gpurun_out/r02_bench_mxfp8_all.err; echo "bench mxfp8 all experiments exit $?" >> $S
+LLMFP8_JOIN_SPLIT_WEIGHTS=0 $B > gpurun_out/r02_bench_mxfp8_catweights.json 2> gpurun_out/r02_bench_mxfp8_catweights.err; echo "bench mxfp8 torch.cat qkv weights exit $?" >> $S
 LLMFP8_GEMM_DEBUG=16 $B > gpurun_out/r02_bench_mxfp8_singleacc.json 2> gpurun_out/r02_bench_mxfp8_singleacc.err; echo "bench mxfp8 single accumulator exit $?" >> $S
 $B --scenario default > gpurun_out/r02_bench_default.json 2> gpurun_out/r02_bench_default.err; echo "bench default exit $?" >> $S
 LLMFP8_WGRAD_STREAM=1 $B --scenario default > gpurun_out/r02_bench_default_wgradstream.json 2> gpurun_out/r02_bench_default_wgradstream.err; echo "bench default +wgrad stream exit $?" >> $S
