@@ -9,7 +9,10 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libllmfp8_b200.so")
+# LLMFP8_PDL=1 loads the programmatic-dependent-launch build of the same sources (csrc/Makefile, csrc/common.cuh) — same C ABI; that
+# variant has not run on hardware yet, so it is never the default.
+PDL = os.environ.get("LLMFP8_PDL", "0") == "1"
+LIB_PATH = os.path.join(_HERE, "libllmfp8_b200_pdl.so" if PDL else "libllmfp8_b200.so")
 
 _lib = None
 _lock = threading.Lock()

@@ -187,6 +187,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): barrier init, descriptor prefetch, TMEM allocation and the cluster
+    pdl_wait();                // sync above ran under the previous kernel's tail; nothing before this line touches global memory
 
     constexpr int GROUP = GROUP_M / CG;
     auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {
@@ -574,13 +576,18 @@ static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CU
     cfg.blockDim = dim3(GEMM_THREADS);
     cfg.dynamicSmemBytes = smem_bytes;
     cfg.stream = stream;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = CG;
     attr[0].val.clusterDim.y = 1;
     attr[0].val.clusterDim.z = 1;
     cfg.attrs = attr;
     cfg.numAttrs = 1;
+#ifdef LLMFP8_PDL
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = 1;
+    cfg.numAttrs = 2;
+#endif
     cudaError_t e = cudaLaunchKernelEx(&cfg, kern, ma, mb, msa, msb, md, p);
     if (e != cudaSuccess) { set_error("fp8_gemm: launch failed: %s", cudaGetErrorString(e)); return (int)e; }
     LLMFP8_LAUNCH_CHECK("fp8_gemm");

@@ -131,7 +131,9 @@ __global__ void __launch_bounds__(256, 2) mx_swiglu_quantize_kernel(const __grid
         ptx::mbar_init(&s.full_u, 1);
         ptx::fence_barrier_init();
     }
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
+    pdl_wait();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         ptx::mbar_arrive_expect_tx(&s.full_g, AT_IN_BYTES);
@@ -235,7 +237,9 @@ __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(cons
         ptx::mbar_init(&s.full_gu, 1);
         ptx::fence_barrier_init();
     }
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
+    pdl_wait();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         const int c = (t % tiles_c) * AT, r = (t / tiles_c) * AT;
@@ -402,7 +406,7 @@ int launch_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q
     const int grid = ntiles < cap ? ntiles : cap;
     cudaError_t e = cudaFuncSetAttribute(mx_swiglu_quantize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("mx_swiglu_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-    mx_swiglu_quantize_kernel<<<grid, 256, smem, stream>>>(m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, (int)M, (int)I, do_row, do_col);
+    LLMFP8_LAUNCH((mx_swiglu_quantize_kernel), grid, 256, smem, stream, m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, (int)M, (int)I, do_row, do_col);
     LLMFP8_LAUNCH_CHECK("mx_swiglu_quantize");
     return 0;
 }
@@ -439,7 +443,7 @@ int launch_mx_dswiglu_quantize(const void* da, const void* fc1_out, int64_t M, i
     const int grid = ntiles < cap ? ntiles : cap;
     cudaError_t e = cudaFuncSetAttribute(mx_dswiglu_quantize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("mx_dswiglu_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-    mx_dswiglu_quantize_kernel<<<grid, AB_THREADS, smem, stream>>>(m_da, m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, dbias_ws, (int)M,
+    LLMFP8_LAUNCH((mx_dswiglu_quantize_kernel), grid, AB_THREADS, smem, stream, m_da, m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, dbias_ws, (int)M,
                                                                    (int)I, do_row, do_col);
     LLMFP8_LAUNCH_CHECK("mx_dswiglu_quantize");
     if (dbias_ws) return launch_f32_to_bf16(dbias_ws, dbias_bf16, 2 * I, stream);

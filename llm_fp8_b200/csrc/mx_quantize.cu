@@ -46,7 +46,9 @@ __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant_
         ptx::mbar_init(&s.full[1], 1);
         ptx::fence_barrier_init();
     }
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
+    pdl_wait();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         ptx::mbar_arrive_expect_tx(&s.full[0], MX_IN_BYTES);
@@ -238,12 +240,12 @@ int launch_mx_quantize(const void* x, int64_t ldx, int64_t R, int64_t C, void* q
     if (rsigma) {
         e = cudaFuncSetAttribute(mx_quantize_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) { set_error("mx_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-        mx_quantize_kernel<1><<<grid, 256, smem, stream>>>(m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, rsigma, (const uint16_t*)gamma,
+        LLMFP8_LAUNCH((mx_quantize_kernel<1>), grid, 256, smem, stream, m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, rsigma, (const uint16_t*)gamma,
                                                            (int)R, (int)C, do_row, do_col);
     } else {
         e = cudaFuncSetAttribute(mx_quantize_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) { set_error("mx_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-        mx_quantize_kernel<0><<<grid, 256, smem, stream>>>(m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, nullptr, nullptr, (int)R, (int)C,
+        LLMFP8_LAUNCH((mx_quantize_kernel<0>), grid, 256, smem, stream, m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, nullptr, nullptr, (int)R, (int)C,
                                                            do_row, do_col);
     }
     LLMFP8_LAUNCH_CHECK("mx_quantize");

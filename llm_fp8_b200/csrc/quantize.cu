@@ -14,6 +14,8 @@ namespace llmfp8 {
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) cast_amax_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t nunits,
                                                         const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -53,9 +55,9 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
     LLMFP8_REQUIRE(want < (int64_t(1) << 31), "cast_amax: tensor too large (%lld elements)", (long long)n);
     const int grid = static_cast<int>(want);
     if (fmt == FMT_E4M3)
-        cast_amax_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
+        LLMFP8_LAUNCH((cast_amax_kernel<FMT_E4M3, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
     else
-        cast_amax_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
+        LLMFP8_LAUNCH((cast_amax_kernel<FMT_E5M2, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
     LLMFP8_LAUNCH_CHECK("cast_amax");
     return 0;
 }
@@ -65,6 +67,8 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) cast_amax_2d_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, uint32_t nunits, uint32_t cvec,
                                                            int64_t ldvec, const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -110,9 +114,9 @@ int launch_cast_amax_2d(const void* x, int64_t ldx, void* q, int64_t R, int64_t 
     constexpr int UNROLL = 8;
     const int grid = static_cast<int>((nunits + 256 * UNROLL - 1) / (256 * UNROLL));
     if (fmt == FMT_E4M3)
-        cast_amax_2d_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
+        LLMFP8_LAUNCH((cast_amax_2d_kernel<FMT_E4M3, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
     else
-        cast_amax_2d_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
+        LLMFP8_LAUNCH((cast_amax_2d_kernel<FMT_E5M2, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), (uint32_t)nunits, (uint32_t)(C / 8), ldx / 8, scale, amax);
     LLMFP8_LAUNCH_CHECK("cast_amax_2d");
     return 0;
 }
@@ -126,6 +130,8 @@ template <int FMT>
 __global__ void __launch_bounds__(256) cast_amax_bgrad_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t R, int64_t C,
                                                               int64_t rows_per_cta, const float* __restrict__ scale_ptr,
                                                               float* __restrict__ amax, float* __restrict__ colsum_ws) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[8];
     __shared__ float part[BG_RL][BG_COLS + 8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
@@ -175,6 +181,8 @@ __global__ void __launch_bounds__(256) cast_amax_bgrad_kernel(const uint4* __res
 }
 
 __global__ void f32_to_bf16_kernel(const float* __restrict__ in, uint16_t* __restrict__ out, int64_t n) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) out[i] = static_cast<uint16_t>(pack_bf16x2(in[i], 0.f) & 0xffffu);
 }
@@ -196,18 +204,18 @@ int launch_cast_amax_bgrad(const void* x, void* q, int64_t R, int64_t C, int fmt
     ychunks = (R + rows_per_cta - 1) / rows_per_cta;
     dim3 grid(strips, static_cast<unsigned>(ychunks));
     if (fmt == FMT_E4M3)
-        cast_amax_bgrad_kernel<FMT_E4M3><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
+        LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E4M3>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
     else
-        cast_amax_bgrad_kernel<FMT_E5M2><<<grid, 256, 0, stream>>>(static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
+        LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E5M2>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
     LLMFP8_LAUNCH_CHECK("cast_amax_bgrad");
-    f32_to_bf16_kernel<<<static_cast<unsigned>((C + 255) / 256), 256, 0, stream>>>(colsum_ws, static_cast<uint16_t*>(bgrad_bf16), C);
+    LLMFP8_LAUNCH((f32_to_bf16_kernel), static_cast<unsigned>((C + 255) / 256), 256, 0, stream, colsum_ws, static_cast<uint16_t*>(bgrad_bf16), C);
     LLMFP8_LAUNCH_CHECK("cast_amax_bgrad.finalize");
     return 0;
 }
 
 int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t stream) {
     if (n == 0) return 0;
-    f32_to_bf16_kernel<<<static_cast<unsigned>((n + 255) / 256), 256, 0, stream>>>(in, static_cast<uint16_t*>(out), n);
+    LLMFP8_LAUNCH((f32_to_bf16_kernel), static_cast<unsigned>((n + 255) / 256), 256, 0, stream, in, static_cast<uint16_t*>(out), n);
     LLMFP8_LAUNCH_CHECK("f32_to_bf16");
     return 0;
 }
@@ -216,6 +224,8 @@ int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t strea
 // One thread per fp8 tensor slot; hist is [L, T] row-major.  Oracle: orc_amax_scale_update.
 __global__ void amax_scale_update_kernel(float* __restrict__ hist, float* __restrict__ scale, float* __restrict__ scale_inv,
                                          const float* __restrict__ fmax, int L, int T, float margin_div) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= T) return;
     float am = 0.f;
@@ -242,7 +252,7 @@ int launch_amax_scale_update(float* hist, float* scale, float* scale_inv, const 
     LLMFP8_REQUIRE(L >= 1 && T >= 0, "amax_scale_update: bad sizes L=%d T=%d", L, T);
     LLMFP8_REQUIRE(margin >= 0 && margin < 120, "amax_scale_update: bad margin %d", margin);
     if (T == 0) return 0;
-    amax_scale_update_kernel<<<(T + 127) / 128, 128, 0, stream>>>(hist, scale, scale_inv, fmax, L, T, ldexpf(1.0f, margin));
+    LLMFP8_LAUNCH((amax_scale_update_kernel), (T + 127) / 128, 128, 0, stream, hist, scale, scale_inv, fmax, L, T, ldexpf(1.0f, margin));
     LLMFP8_LAUNCH_CHECK("amax_scale_update");
     return 0;
 }

@@ -46,6 +46,8 @@ template <int FMT, int NIT, int OUT_MODE>
 __global__ void __launch_bounds__(RMS_T) rmsnorm_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gamma, uint2* __restrict__ q,
                                                             float* __restrict__ rsigma, int64_t M, int H, float eps,
                                                             const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[2][4];
     __shared__ float red_amax[4];
     const int t = threadIdx.x;
@@ -92,7 +94,7 @@ static int dispatch_rms_fwd(int nit, int grid, cudaStream_t s, const uint4* x, c
 #define RMS_CASE(N)                                                                                              \
     case N:                                                                                                      \
         grid = resident_grid(rmsnorm_fwd_kernel<FMT, N, OUT_MODE>, RMS_T, M);                                    \
-        rmsnorm_fwd_kernel<FMT, N, OUT_MODE><<<grid, RMS_T, 0, s>>>(x, g, q, rs, M, H, eps, scale, amax);        \
+        LLMFP8_LAUNCH((rmsnorm_fwd_kernel<FMT, N, OUT_MODE>), grid, RMS_T, 0, s, x, g, q, rs, M, H, eps, scale, amax);        \
         break;
     switch (nit) {
         RMS_CASE(1) RMS_CASE(2) RMS_CASE(3) RMS_CASE(4) RMS_CASE(5) RMS_CASE(6) RMS_CASE(7) RMS_CASE(8)
@@ -143,6 +145,8 @@ template <int NIT, bool ADD>
 __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
                                                            const float* __restrict__ rsigma, const uint4* __restrict__ dres, uint4* __restrict__ dx,
                                                            float* __restrict__ dgamma_part, int64_t M, int H) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[2][RB_T / 32];
     const int t = threadIdx.x;
     const int nchunk = H / 8;
@@ -254,6 +258,8 @@ __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(c
 constexpr int CR_COLS = 32, CR_LANES = 8;
 __global__ void __launch_bounds__(CR_COLS * CR_LANES) colreduce_bf16_kernel(const float* __restrict__ part, int nparts, int H,
                                                                             uint16_t* __restrict__ out) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[CR_LANES][CR_COLS + 1];
     const int cx = threadIdx.x % CR_COLS, py = threadIdx.x / CR_COLS;
     const int c = blockIdx.x * CR_COLS + cx;
@@ -297,7 +303,7 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
     do {                                                                                                                                       \
         grid = resident_grid(rmsnorm_bwd_kernel<N, ADD>, RB_T, M);                                                                             \
         if (grid > rmsnorm_bwd_grid(M)) grid = rmsnorm_bwd_grid(M);                                                                            \
-        rmsnorm_bwd_kernel<N, ADD><<<grid, RB_T, 0, stream>>>((const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (const uint4*)dres, \
+        LLMFP8_LAUNCH((rmsnorm_bwd_kernel<N, ADD>), grid, RB_T, 0, stream, (const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (const uint4*)dres, \
                                                               (uint4*)dx, ws, M, (int)H);                                                      \
     } while (0)
 #define RMSB_CASE(N)                                                                                                                           \
@@ -312,7 +318,7 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
 #undef RMSB_LAUNCH
 #undef RMSB_CASE
     LLMFP8_LAUNCH_CHECK("rmsnorm_bwd");
-    colreduce_bf16_kernel<<<static_cast<unsigned>((H + CR_COLS - 1) / CR_COLS), CR_COLS * CR_LANES, 0, stream>>>(ws, grid, (int)H, static_cast<uint16_t*>(dgamma_bf16));
+    LLMFP8_LAUNCH((colreduce_bf16_kernel), static_cast<unsigned>((H + CR_COLS - 1) / CR_COLS), CR_COLS * CR_LANES, 0, stream, ws, grid, (int)H, static_cast<uint16_t*>(dgamma_bf16));
     LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
     return 0;
 }

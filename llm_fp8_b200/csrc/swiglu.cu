@@ -46,6 +46,8 @@ __device__ __forceinline__ uint4 bf16x8_p(const f32x2 (&a)[4]) {
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) swiglu_quant_kernel(const uint4* __restrict__ fc1, uint2* __restrict__ q, int64_t M, int64_t ivec /* I/8 */,
                                                            const float* __restrict__ scale_ptr, float* __restrict__ amax) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -102,11 +104,11 @@ int launch_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, 
     LLMFP8_REQUIRE(total < (int64_t(1) << 31), "swiglu_quant_fwd: problem too large (%lld x %lld)", (long long)M, (long long)I);
     const int grid = static_cast<int>(want);
     if (fmt == FMT_E4M3)
-        swiglu_quant_kernel<FMT_E4M3, UNROLL><<<grid, 256, 0, stream>>>((const uint4*)fc1_out, (uint2*)q, M, I / 8, scale, amax);
+        LLMFP8_LAUNCH((swiglu_quant_kernel<FMT_E4M3, UNROLL>), grid, 256, 0, stream, (const uint4*)fc1_out, (uint2*)q, M, I / 8, scale, amax);
     else if (fmt == FMT_E5M2)
-        swiglu_quant_kernel<FMT_E5M2, UNROLL><<<grid, 256, 0, stream>>>((const uint4*)fc1_out, (uint2*)q, M, I / 8, scale, amax);
+        LLMFP8_LAUNCH((swiglu_quant_kernel<FMT_E5M2, UNROLL>), grid, 256, 0, stream, (const uint4*)fc1_out, (uint2*)q, M, I / 8, scale, amax);
     else
-        swiglu_quant_kernel<FMT_BF16, UNROLL><<<grid, 256, 0, stream>>>((const uint4*)fc1_out, (uint2*)q, M, I / 8, nullptr, nullptr);
+        LLMFP8_LAUNCH((swiglu_quant_kernel<FMT_BF16, UNROLL>), grid, 256, 0, stream, (const uint4*)fc1_out, (uint2*)q, M, I / 8, nullptr, nullptr);
     LLMFP8_LAUNCH_CHECK("swiglu_quant_fwd");
     return 0;
 }
@@ -117,6 +119,8 @@ template <int FMT, int UN, int MINB>
 __global__ void __launch_bounds__(256, MINB) dswiglu_quant_kernel(const uint4* __restrict__ da, const uint4* __restrict__ fc1, uint2* __restrict__ q,
                                                             int64_t M, int64_t I, int64_t rows_per_cta, const float* __restrict__ scale_ptr,
                                                             float* __restrict__ amax, float* __restrict__ dbias_ws /* [2I] or null */) {
+    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_wait();
     __shared__ float red[8];
     __shared__ float part[DS_RL][2 * DS_COLS + 8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
@@ -233,11 +237,11 @@ int launch_dswiglu_quant_bwd(const void* da, const void* fc1_out, void* q, int64
 #define DSW_LAUNCH(UN, MINB)                                                                                                                  \
     do {                                                                                                                                      \
         if (fmt == FMT_E4M3)                                                                                                                  \
-            dswiglu_quant_kernel<FMT_E4M3, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
+            LLMFP8_LAUNCH((dswiglu_quant_kernel<FMT_E4M3, UN, MINB>), grid, 256, 0, stream, (const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
         else if (fmt == FMT_E5M2)                                                                                                             \
-            dswiglu_quant_kernel<FMT_E5M2, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
+            LLMFP8_LAUNCH((dswiglu_quant_kernel<FMT_E5M2, UN, MINB>), grid, 256, 0, stream, (const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, scale, amax, dbias_ws); \
         else                                                                                                                                  \
-            dswiglu_quant_kernel<FMT_BF16, UN, MINB><<<grid, 256, 0, stream>>>((const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, nullptr, nullptr, dbias_ws); \
+            LLMFP8_LAUNCH((dswiglu_quant_kernel<FMT_BF16, UN, MINB>), grid, 256, 0, stream, (const uint4*)da, (const uint4*)fc1_out, (uint2*)q, M, I, rows_per_cta, nullptr, nullptr, dbias_ws); \
     } while (0)
     if (variant == 1) DSW_LAUNCH(2, 4);
     else if (variant == 2) DSW_LAUNCH(1, 4);

@@ -29,6 +29,17 @@ def test_library_exports_every_declared_symbol():
     assert lib.llmfp8_abi_version() == 1
 
 
+def test_pdl_build_exports_the_same_abi():
+    """libllmfp8_b200_pdl.so (the -DLLMFP8_PDL build of the same sources, loaded with LLMFP8_PDL=1) is a drop-in for the default library."""
+    path = os.path.join(ROOT, "llm_fp8_b200", "libllmfp8_b200_pdl.so")
+    assert os.path.exists(path), "build first: python -c 'import __graft_entry__ as g; g.build()'"
+    lib = ctypes.CDLL(path)
+    for s in header_symbols():
+        assert hasattr(lib, s), f"{s} missing from the PDL build"
+    lib.llmfp8_abi_version.restype = ctypes.c_int
+    assert lib.llmfp8_abi_version() == 1
+
+
 def test_scale_bytes_matches_oracle():
     from llm_fp8_b200 import _lib, ops
     from oracle import fp8_oracle as fo

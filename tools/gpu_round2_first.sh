@@ -1,6 +1,6 @@
 #!/bin/bash
-# First GPU call of the next round (one B200, ~8 min of box time): everything that was written after the round-1 GPU budget ran out.
-#   /usr/local/graft/bin/gpurun --timeout 900 -- 'bash tools/gpu_round2_first.sh'
+# First GPU call of the next round (one B200, ~12 min of box time): everything that was written after the round-1 GPU budget ran out.
+#   /usr/local/graft/bin/gpurun --timeout 1200 -- 'bash tools/gpu_round2_first.sh'
 # 1. full GPU suite on the default tree (overlapped-accumulator MX GEMM is the default since d2c7555);
 # 2. the gated experiments' own tests (LLMFP8_EXPERIMENTAL=1): RES + OVL epilogue (debug bit 5), SwiGLU/dSwiGLU fused with the MX
 #    quantiser (LLMFP8_MX_FUSED_ACT), wgrad side stream (LLMFP8_WGRAD_STREAM);
@@ -21,12 +21,18 @@ echo "exp fused act exit $?  $(tail -1 gpurun_out/r02_exp_fused_act.log)" >> $S
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_modules.py -q -m gpu -p no:cacheprovider -k "wgrad_side_stream" > gpurun_out/r02_exp_wgrad_stream.log 2>&1
 echo "exp wgrad stream exit $?  $(tail -1 gpurun_out/r02_exp_wgrad_stream.log)" >> $S
 
+# the programmatic-dependent-launch build: the whole GPU suite on it, then its bench line
+LLMFP8_PDL=1 timeout 400 python -m pytest tests/ -x -q -m gpu -p no:cacheprovider > gpurun_out/r02_pytest_gpu_pdl.log 2>&1
+echo "pytest gpu (PDL build) exit $?  $(tail -1 gpurun_out/r02_pytest_gpu_pdl.log)" >> $S
+
 B="timeout 170 python bench.py --steps 5 --warmup 3 --no-cpu-baseline"
 $B > gpurun_out/r02_bench_mxfp8.json 2> gpurun_out/r02_bench_mxfp8.err; echo "bench mxfp8 exit $?" >> $S
 LLMFP8_WGRAD_STREAM=1 $B > gpurun_out/r02_bench_mxfp8_wgradstream.json 2> gpurun_out/r02_bench_mxfp8_wgradstream.err; echo "bench mxfp8 +wgrad stream exit $?" >> $S
 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_resovl.json 2> gpurun_out/r02_bench_mxfp8_resovl.err; echo "bench mxfp8 +RES/OVL exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 $B > gpurun_out/r02_bench_mxfp8_fusedact.json 2> gpurun_out/r02_bench_mxfp8_fusedact.err; echo "bench mxfp8 +fused act exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 LLMFP8_WGRAD_STREAM=1 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_all.json 2> gpurun_out/r02_bench_mxfp8_all.err; echo "bench mxfp8 all experiments exit $?" >> $S
+LLMFP8_PDL=1 $B > gpurun_out/r02_bench_mxfp8_pdl.json 2> gpurun_out/r02_bench_mxfp8_pdl.err; echo "bench mxfp8 PDL build exit $?" >> $S
+LLMFP8_PDL=1 $B --scenario default > gpurun_out/r02_bench_default_pdl.json 2> gpurun_out/r02_bench_default_pdl.err; echo "bench default PDL build exit $?" >> $S
 LLMFP8_JOIN_SPLIT_WEIGHTS=0 $B > gpurun_out/r02_bench_mxfp8_catweights.json 2> gpurun_out/r02_bench_mxfp8_catweights.err; echo "bench mxfp8 torch.cat qkv weights exit $?" >> $S
 LLMFP8_GEMM_DEBUG=16 $B > gpurun_out/r02_bench_mxfp8_singleacc.json 2> gpurun_out/r02_bench_mxfp8_singleacc.err; echo "bench mxfp8 single accumulator exit $?" >> $S
 $B --scenario default > gpurun_out/r02_bench_default.json 2> gpurun_out/r02_bench_default.err; echo "bench default exit $?" >> $S
