@@ -87,3 +87,51 @@ def test_single_process_is_a_noop(monkeypatch):
     m(_batch()).sum().backward()
     red.finish()
     assert red.bytes_reduced == 0
+
+
+# ------------------------------------------------------------------------------------------------ joined qkv weights under the reducer
+class _SplitProbe(torch.nn.Module):
+    """The split query / key / value Parameters of LayerNormLinear (row slices of one buffer, modules._joined_rows) driving a plain
+    matmul: what the gradient all-reducer sees on the FP8 path is the same — three Parameters whose gradients are views of one
+    wgrad output."""
+
+    def __init__(self):
+        super().__init__()
+        import llm_fp8_b200 as te
+        torch.manual_seed(3)
+        self.lnl = te.LayerNormLinear(64, 64 + 2 * 32, bias=False, normalization="RMSNorm",
+                                      parameters_split={"query": 64, "key": 32, "value": 32}, params_dtype=torch.float32)
+
+    def forward(self, x):
+        w, _ = self.lnl._weight_bias()
+        return x @ w.t()
+
+
+def _split_worker(rank, world, port, out):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dp.init_from_env(backend="gloo")
+    model = _SplitProbe()
+    params = [model.lnl.query_weight, model.lnl.key_weight, model.lnl.value_weight]
+    reducer = dp.GradAllReducer(params, direct_numel=32 * 64, prescaled=True)      # every slice goes the direct (in-place) way
+    x = _batch()
+    mine = dp.shard_tokens(x.shape[0], rank, world)
+    for _ in range(2):                                                             # two optimizer steps' worth: fresh gradient views each time
+        for p in params:
+            p.grad = None
+        (model(x[mine.start:mine.stop]).square().mean() * reducer.loss_scale).backward()
+        reducer.finish()
+    if rank == 0:
+        torch.save([p.grad.clone() for p in params], out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_allreduce_of_joined_split_weights(tmp_path):
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_split_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    model = _SplitProbe()
+    model(_batch()).square().mean().backward()
+    want = [model.lnl.query_weight.grad, model.lnl.key_weight.grad, model.lnl.value_weight.grad]
+    for g, w in zip(got, want):
+        assert torch.allclose(g, w, rtol=1e-5, atol=1e-7)
