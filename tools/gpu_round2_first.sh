@@ -16,7 +16,7 @@ echo "pytest gpu exit $?  $(tail -1 gpurun_out/r02_pytest_gpu.log)" >> $S
 
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_gemm.py -q -m gpu -p no:cacheprovider -k "residual_overlapped" > gpurun_out/r02_exp_res_ovl.log 2>&1
 echo "exp RES+OVL exit $?  $(tail -1 gpurun_out/r02_exp_res_ovl.log)" >> $S
-LLMFP8_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_quantize.py -q -m gpu -p no:cacheprovider -k "mx_swiglu or mx_dswiglu or mx_act" > gpurun_out/r02_exp_fused_act.log 2>&1
+LLMFP8_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_quantize.py tests/test_golden.py -q -m gpu -p no:cacheprovider -k "mx_swiglu or mx_dswiglu or mx_act or denormal_quotients" > gpurun_out/r02_exp_fused_act.log 2>&1
 echo "exp fused act exit $?  $(tail -1 gpurun_out/r02_exp_fused_act.log)" >> $S
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_modules.py -q -m gpu -p no:cacheprovider -k "wgrad_side_stream" > gpurun_out/r02_exp_wgrad_stream.log 2>&1
 echo "exp wgrad stream exit $?  $(tail -1 gpurun_out/r02_exp_wgrad_stream.log)" >> $S
