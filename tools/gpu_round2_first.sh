@@ -38,6 +38,7 @@ LLMFP8_GEMM_DEBUG=16 $B > gpurun_out/r02_bench_mxfp8_singleacc.json 2> gpurun_ou
 $B --scenario default > gpurun_out/r02_bench_default.json 2> gpurun_out/r02_bench_default.err; echo "bench default exit $?" >> $S
 LLMFP8_WGRAD_STREAM=1 $B --scenario default > gpurun_out/r02_bench_default_wgradstream.json 2> gpurun_out/r02_bench_default_wgradstream.err; echo "bench default +wgrad stream exit $?" >> $S
 
+timeout 200 python tools/microbench.py --model llama8b --only quant --kfilter K3m --experimental --out gpurun_out/r02_micro_fused_act.jsonl > gpurun_out/r02_micro_fused_act.log 2>&1; echo "microbench fused act exit $?" >> $S
 timeout 120 python tools/gemm_ab.py --modes 16,0 --rounds 4 > gpurun_out/r02_gemm_ab_ovl.txt 2>&1; echo "gemm A/B exit $?" >> $S
 
 CMD="python bench.py --layers 2 --steps 1 --warmup 3 --no-cpu-baseline --no-roofline"

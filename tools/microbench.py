@@ -72,6 +72,7 @@ def main():
     ap.add_argument("--debug", type=int, default=0)
     ap.add_argument("--tag", default="")
     ap.add_argument("--kfilter", default="", help="only run memory-bound kernels whose name contains this substring")
+    ap.add_argument("--experimental", action="store_true", help="also time the code paths that have not been validated on hardware yet")
     ap.add_argument("--ms", default="", help="comma-separated token counts to sweep instead of the model's default M (BASELINE.json config 5: 512..16384)")
     ap.add_argument("--no-bwd", action="store_true", help="GEMM sweep: fprop forms only")
     args = ap.parse_args()
@@ -137,6 +138,15 @@ def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
         mem("K2m mx_quantize row x[M,H]", lambda: ops.mx_quantize(x, True, False), int(3.03125 * M * H))
         mem("K2m mx_quantize row+col W1[2I,H]", lambda: ops.mx_quantize(w1, True, True), int(4.0625 * 2 * I * H))
         mem("K1m rsigma + mx_quantize row+col [M,H]", lambda: ops.mx_quantize(x, True, True, ops.rmsnorm_rsigma(x, 1e-5), gamma), int(4.0625 * M * H))
+        # MXFP8 activation path: the two-kernel sequences and (--experimental) their one-pass replacements (csrc/mx_act_quantize.cu)
+        mem("K3m swiglu_bf16 + mx_quantize row+col [M,I] (two kernels)", lambda: ops.mx_quantize(ops.swiglu_bf16(fc1), True, True),
+            int(10.0625 * M * I))
+        mem("K3mb dswiglu_bf16 + mx_quantize row+col [M,2I] (two kernels)", lambda: ops.mx_quantize(ops.dswiglu_bf16(da, fc1)[0], True, True),
+            int(18.125 * M * I))
+        if args.experimental:
+            mem("K3m mx_swiglu_quantize row+col [M,I] (one pass)", lambda: ops.mx_swiglu_quantize(fc1, True, True), int(6.0625 * M * I))
+            if I % 128 == 0:
+                mem("K3mb mx_dswiglu_quantize row+col [M,2I] (one pass)", lambda: ops.mx_dswiglu_quantize(da, fc1, True, True), int(10.125 * M * I))
         mem("copy bf16 [M,2I] (torch, reference point)", lambda: fc1.clone(), 4 * M * 2 * I)
         mem("copy bf16 [M,H] (torch, reference point for the short kernels)", lambda: x.clone(), 4 * M * H)
         del x, w1, fc1, da
