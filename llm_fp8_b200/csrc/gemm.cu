@@ -187,8 +187,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     else __syncthreads();
     ptx::tc_fence_after();
     const uint32_t tmem_base = *tmem_ptr_smem;
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): barrier init, descriptor prefetch, TMEM allocation and the cluster
-    pdl_wait();                // sync above ran under the previous kernel's tail; nothing before this line touches global memory
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh): barrier init, descriptor prefetch, TMEM allocation and the cluster
+    pdl_launch_dependents();   // sync above ran under the previous kernel's tail; nothing before this line touches global memory
 
     constexpr int GROUP = GROUP_M / CG;
     auto tile_coords = [&](int tile, int& m_blk, int& n_blk) {

@@ -131,9 +131,9 @@ __global__ void __launch_bounds__(256, 2) mx_swiglu_quantize_kernel(const __grid
         ptx::mbar_init(&s.full_u, 1);
         ptx::fence_barrier_init();
     }
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
+    pdl_launch_dependents();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         ptx::mbar_arrive_expect_tx(&s.full_g, AT_IN_BYTES);
@@ -237,9 +237,9 @@ __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(cons
         ptx::mbar_init(&s.full_gu, 1);
         ptx::fence_barrier_init();
     }
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
+    pdl_launch_dependents();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         const int c = (t % tiles_c) * AT, r = (t / tiles_c) * AT;

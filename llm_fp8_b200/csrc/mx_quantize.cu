@@ -46,9 +46,9 @@ __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant_
         ptx::mbar_init(&s.full[1], 1);
         ptx::fence_barrier_init();
     }
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     __syncthreads();
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
+    pdl_launch_dependents();
     if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
         const int t = blockIdx.x;
         ptx::mbar_arrive_expect_tx(&s.full[0], MX_IN_BYTES);

@@ -14,8 +14,8 @@ namespace llmfp8 {
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) cast_amax_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t nunits,
                                                         const float* __restrict__ scale_ptr, float* __restrict__ amax) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -67,8 +67,8 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) cast_amax_2d_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, uint32_t nunits, uint32_t cvec,
                                                            int64_t ldvec, const float* __restrict__ scale_ptr, float* __restrict__ amax) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -130,8 +130,8 @@ template <int FMT>
 __global__ void __launch_bounds__(256) cast_amax_bgrad_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t R, int64_t C,
                                                               int64_t rows_per_cta, const float* __restrict__ scale_ptr,
                                                               float* __restrict__ amax, float* __restrict__ colsum_ws) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[8];
     __shared__ float part[BG_RL][BG_COLS + 8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
@@ -181,8 +181,8 @@ __global__ void __launch_bounds__(256) cast_amax_bgrad_kernel(const uint4* __res
 }
 
 __global__ void f32_to_bf16_kernel(const float* __restrict__ in, uint16_t* __restrict__ out, int64_t n) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     const int64_t i = static_cast<int64_t>(blockIdx.x) * blockDim.x + threadIdx.x;
     if (i < n) out[i] = static_cast<uint16_t>(pack_bf16x2(in[i], 0.f) & 0xffffu);
 }
@@ -224,8 +224,8 @@ int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t strea
 // One thread per fp8 tensor slot; hist is [L, T] row-major.  Oracle: orc_amax_scale_update.
 __global__ void amax_scale_update_kernel(float* __restrict__ hist, float* __restrict__ scale, float* __restrict__ scale_inv,
                                          const float* __restrict__ fmax, int L, int T, float margin_div) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= T) return;
     float am = 0.f;

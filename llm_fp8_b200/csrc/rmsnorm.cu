@@ -46,8 +46,8 @@ template <int FMT, int NIT, int OUT_MODE>
 __global__ void __launch_bounds__(RMS_T) rmsnorm_fwd_kernel(const uint4* __restrict__ x, const uint4* __restrict__ gamma, uint2* __restrict__ q,
                                                             float* __restrict__ rsigma, int64_t M, int H, float eps,
                                                             const float* __restrict__ scale_ptr, float* __restrict__ amax) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[2][4];
     __shared__ float red_amax[4];
     const int t = threadIdx.x;
@@ -145,8 +145,8 @@ template <int NIT, bool ADD>
 __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
                                                            const float* __restrict__ rsigma, const uint4* __restrict__ dres, uint4* __restrict__ dx,
                                                            float* __restrict__ dgamma_part, int64_t M, int H) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[2][RB_T / 32];
     const int t = threadIdx.x;
     const int nchunk = H / 8;
@@ -258,8 +258,8 @@ __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(c
 constexpr int CR_COLS = 32, CR_LANES = 8;
 __global__ void __launch_bounds__(CR_COLS * CR_LANES) colreduce_bf16_kernel(const float* __restrict__ part, int nparts, int H,
                                                                             uint16_t* __restrict__ out) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[CR_LANES][CR_COLS + 1];
     const int cx = threadIdx.x % CR_COLS, py = threadIdx.x / CR_COLS;
     const int c = blockIdx.x * CR_COLS + cx;

@@ -46,8 +46,8 @@ __device__ __forceinline__ uint4 bf16x8_p(const f32x2 (&a)[4]) {
 template <int FMT, int UNROLL>
 __global__ void __launch_bounds__(256) swiglu_quant_kernel(const uint4* __restrict__ fc1, uint2* __restrict__ q, int64_t M, int64_t ivec /* I/8 */,
                                                            const float* __restrict__ scale_ptr, float* __restrict__ amax) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
     const f32x2 scale2 = pk2(scale, scale);
@@ -119,8 +119,8 @@ template <int FMT, int UN, int MINB>
 __global__ void __launch_bounds__(256, MINB) dswiglu_quant_kernel(const uint4* __restrict__ da, const uint4* __restrict__ fc1, uint2* __restrict__ q,
                                                             int64_t M, int64_t I, int64_t rows_per_cta, const float* __restrict__ scale_ptr,
                                                             float* __restrict__ amax, float* __restrict__ dbias_ws /* [2I] or null */) {
-    pdl_launch_dependents();   // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_wait();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
     __shared__ float red[8];
     __shared__ float part[DS_RL][2 * DS_COLS + 8];
     const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
