@@ -79,6 +79,9 @@ def load():
             dbg = os.environ.get("LLMFP8_GEMM_DEBUG")          # experiments only: the bits of llmfp8_gemm_debug (include/llmfp8_b200.h)
             if dbg:
                 lib.llmfp8_gemm_debug(int(dbg, 0))
+            for var, setter in (("LLMFP8_GEMM_FORCE_CG", lib.llmfp8_gemm_force_cg), ("LLMFP8_GEMM_FORCE_BN", lib.llmfp8_gemm_force_bn)):
+                if os.environ.get(var):                       # tuning probes (tools/gpu_round2_scale.sh); never set in normal use
+                    setter(int(os.environ[var]))
             _lib = lib
     return _lib
 

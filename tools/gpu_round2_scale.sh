@@ -1,0 +1,32 @@
+#!/bin/bash
+# 8-GPU probes for the >= 7x weak-scaling target (round 1: 6.87x).  ~2 min of box time per line, charged 8x:
+#   /usr/local/graft/bin/gpurun --gpus 8 --timeout 1500 -- 'bash tools/gpu_round2_scale.sh'
+# Run AFTER tools/gpu_round2_first.sh has validated the switches on one GPU; drop the lines whose switch failed there.
+N=${1:-8}
+mkdir -p gpurun_out
+S=gpurun_out/r02_scale_summary.txt
+: > $S
+run() {  # tag, env assignments...
+  tag=$1; shift
+  env "$@" LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
+      bench.py --gpus $N --steps 4 --warmup 3 --scenario mxfp8 --no-roofline > gpurun_out/r02_scale_${tag}_n$N.json 2> gpurun_out/r02_scale_${tag}_n$N.err
+  echo "$tag n=$N exit $?" >> $S
+  python - >> $S <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/r02_scale_${tag}_n$N.json").read().strip().splitlines()[-1])
+    print("   ${tag}", round(d["value"]), "TF total", round(d["ms_per_step"], 1), "ms/step  e2e", round(d["e2e"]["value"]), d["clocks"])
+except Exception as e:
+    print("   ${tag}: parse failed", e)
+PY
+}
+# single-GPU reference on the same box (ratio denominators must come from the same box)
+timeout 200 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-roofline > gpurun_out/r02_scale_base_n1.json 2> gpurun_out/r02_scale_base_n1.err; echo "base n=1 exit $?" >> $S
+run base LLMFP8_NOOP=1
+run pdl LLMFP8_PDL=1                                   # launch gaps matter more when NCCL kernels interleave
+run wgradstream LLMFP8_WGRAD_STREAM=1
+run cga2 NCCL_CGA_CLUSTER_SIZE=2                       # NCCL CTAs in pairs: fewer TPCs half-occupied (our GEMM needs both SMs of a TPC)
+run cga1 NCCL_CGA_CLUSTER_SIZE=1
+run cg1 LLMFP8_GEMM_FORCE_CG=1                         # single-CTA GEMM tiles: do they coexist better with the all-reduce kernels?
+run fusedact LLMFP8_MX_FUSED_ACT=1
+cat $S
