@@ -565,11 +565,13 @@ template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = fa
 static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
                           const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
     auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES, OVL>;
-    static bool configured = false;   // benign race: the attribute call is idempotent
-    if (!configured) {
+    static bool configured[64] = {};   // per device (the attribute lives in the device's context); benign race: the call is idempotent
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
+    if (dev < 0 || !configured[dev]) {
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, SMEM_BUDGET);
         if (e != cudaSuccess) { set_error("fp8_gemm: smem attribute (%d B): %s", SMEM_BUDGET, cudaGetErrorString(e)); return (int)e; }
-        configured = true;
+        if (dev >= 0) configured[dev] = true;
     }
     cudaLaunchConfig_t cfg = {};
     cfg.gridDim = dim3(grid);
