@@ -57,12 +57,22 @@ class GradAllReducer:
     for every outstanding reduction."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True,
-                 prescaled: Optional[bool] = None):
+                 prescaled: Optional[bool] = None, bucket_bytes: Optional[int] = None):
         """prescaled (default; LLMFP8_GRAD_REDUCE=avg turns it off): the caller multiplies its loss by `loss_scale` (= 1/world) and
         the gradients are all-reduced with SUM — the same mean as AVG, but SUM is the one reduction NVSwitch can do in the fabric:
         NCCL's NVLS algorithms have no AVG / pre-multiplied sum, so with AVG it falls back to a 32-channel ring.  Measured at 8 B200s
         (mxfp8, same box): SUM -> NVLS / 24 channels 170.7 ms per step, AVG -> Ring 175.0 ms.  DDP itself pre-divides
         (train_multi_gpu.py:355-378).  A caller that ignores `loss_scale` gets summed, not averaged, gradients."""
+        # bucket_bytes > 0 (LLMFP8_GRAD_BUCKET_MB; default 0 = one collective per gradient): large gradients are held back until that many
+        # bytes are pending and then all-reduced as ONE coalesced group (ncclGroupStart / End: one fused launch over the gradients' own
+        # memory, still no copies) — 6 collectives per decoder layer become 1-2, at the price of starting each a little later.
+        # Unmeasured (written after the round-1 GPU budget was spent); tools/gpu_round2_scale.sh has the A/B.
+        if bucket_bytes is None:
+            bucket_bytes = int(float(os.environ.get("LLMFP8_GRAD_BUCKET_MB", "0")) * (1 << 20))
+        self.bucket_bytes = max(0, int(bucket_bytes))
+        self._pending: List[torch.Tensor] = []
+        self._pending_bytes = 0
+        self.collectives = 0
         self.group = group
         self.world = dist.get_world_size(group) if dist.is_initialized() else 1
         if prescaled is None:
@@ -89,15 +99,33 @@ class GradAllReducer:
         if g is None:
             return
         if g.numel() >= self.direct_numel and g.is_contiguous():
-            self._work.append((dist.all_reduce(g, op=self._op(), group=self.group, async_op=True), g))
             self.bytes_reduced += g.numel() * g.element_size()
+            if self.bucket_bytes > 0:
+                self._pending.append(g)
+                self._pending_bytes += g.numel() * g.element_size()
+                if self._pending_bytes >= self.bucket_bytes:
+                    self._flush_pending()
+            else:
+                self._work.append((dist.all_reduce(g, op=self._op(), group=self.group, async_op=True), [g]))
+                self.collectives += 1
         else:
             self._small.append(p)
+
+    def _flush_pending(self):
+        if not self._pending:
+            return
+        grads, self._pending, self._pending_bytes = self._pending, [], 0
+        with dist._coalescing_manager(group=self.group, async_ops=True) as cm:
+            for g in grads:
+                dist.all_reduce(g, op=self._op(), group=self.group)
+        self._work.append((cm, grads))
+        self.collectives += 1
 
     def finish(self):
         if self.world == 1:
             return
         post_scale = self.average and self._op() == dist.ReduceOp.SUM
+        self._flush_pending()
         if self._small:
             grads = [p.grad for p in self._small]
             flat = torch.cat([g.reshape(-1).float() for g in grads])
@@ -110,11 +138,13 @@ class GradAllReducer:
                 g.copy_(flat[off:off + n].view_as(g))
                 off += n
             self.bytes_reduced += flat.numel() * 4
+            self.collectives += 1
             self._small = []
-        for w, g in self._work:
+        for w, grads in self._work:
             w.wait()
             if post_scale:
-                g /= self.world
+                for g in grads:
+                    g /= self.world
         self._work = []
 
     def remove(self):

@@ -30,12 +30,12 @@ def _batch():
     return torch.randn(6, 10, 64, generator=g)          # 6 sequences of 10 tokens
 
 
-def _worker(rank, world, port, out, prescaled=False):
+def _worker(rank, world, port, out, prescaled=False, bucket_bytes=0):
     os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
     r, w, _ = dp.init_from_env(backend="gloo")
     assert (r, w) == (rank, world) and dist.get_backend() == "gloo"
     model = _model()
-    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128, prescaled=prescaled)
+    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128, prescaled=prescaled, bucket_bytes=bucket_bytes)
     assert reducer.prescaled == prescaled and reducer.loss_scale == (1.0 / world if prescaled else 1.0)
     x = _batch()
     mine = dp.shard_tokens(x.shape[0], rank, world)
@@ -48,7 +48,7 @@ def _worker(rank, world, port, out, prescaled=False):
     amax = torch.tensor([1.0 + rank, 5.0 - rank, 0.0])
     dist.all_reduce(amax, op=dist.ReduceOp.MAX)
     if rank == 0:
-        torch.save({"grads": grads, "amax": amax, "bytes": reducer.bytes_reduced}, out)
+        torch.save({"grads": grads, "amax": amax, "bytes": reducer.bytes_reduced, "collectives": reducer.collectives}, out)
     dist.barrier()
     dist.destroy_process_group()
 
@@ -65,6 +65,19 @@ def test_two_rank_grad_allreduce_matches_single_process(tmp_path, prescaled):
         assert torch.allclose(g, p.grad, rtol=1e-5, atol=1e-7)
     assert torch.equal(got["amax"], torch.tensor([2.0, 5.0, 0.0]))
     assert got["bytes"] > 0
+
+
+def test_two_rank_grad_allreduce_coalesced_buckets(tmp_path):
+    """bucket_bytes > 0: the large gradients (both Linear weights here) go out as one coalesced group instead of one collective each;
+    same gradients as the single process."""
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_worker, args=(2, _free_port(), out, True, 1 << 30), nprocs=2, join=True)
+    got = torch.load(out)
+    model = _model()
+    model(_batch()).square().mean().backward()
+    for g, p in zip(got["grads"], model.parameters()):
+        assert torch.allclose(g, p.grad, rtol=1e-5, atol=1e-7)
+    assert got["collectives"] == 2          # one coalesced group for the two weights + the packed small gradients
 
 
 def test_shard_tokens_partitions_exactly():

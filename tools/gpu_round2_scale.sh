@@ -28,5 +28,7 @@ run wgradstream LLMFP8_WGRAD_STREAM=1
 run cga2 NCCL_CGA_CLUSTER_SIZE=2                       # NCCL CTAs in pairs: fewer TPCs half-occupied (our GEMM needs both SMs of a TPC)
 run cga1 NCCL_CGA_CLUSTER_SIZE=1
 run cg1 LLMFP8_GEMM_FORCE_CG=1                         # single-CTA GEMM tiles: do they coexist better with the all-reduce kernels?
+run bucket256 LLMFP8_GRAD_BUCKET_MB=256                # coalesced gradient groups: ~2 NCCL launches per decoder layer instead of 6
+run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
 run fusedact LLMFP8_MX_FUSED_ACT=1
 cat $S
