@@ -207,6 +207,15 @@ def reference_arm(a):
 
 
 # ------------------------------------------------------------------------------------------------ our arm
+def _traffic(table, name):
+    """roofline.traffic = dram__bytes_read.sum + dram__bytes_write.sum per launch of that kernel, from the committed ncu --set full
+    capture (profiles/ncu_traffic.json), or null; which capture it came from goes beside it."""
+    t = (table or {}).get(name)
+    if not t:
+        return {"traffic": None}
+    return {"traffic": t.get("dram_bytes_per_launch_avg"), "traffic_unit": "B per launch", "traffic_source": {k: v for k, v in t.items() if k != "dram_bytes_per_launch_avg"}}
+
+
 def main():
     a = parse()
     if a.impl == "reference":
@@ -402,14 +411,14 @@ def main():
                     "peak_note": f"2 x {pk['src']} sustained bf16 cuBLAS TFLOP/s (MEASURED_PEAKS.json has no FP8 figure; FP8 dense = 2 x bf16 on this part)",
                     "frac_of_nominal_fp8_4500": ach / FP8_NOMINAL_TFLOPS, "frac_of_measured_bf16": ach / pk["bf16_sustained"],
                     "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"], "share_of_step": d["ms"] / tot,
-                    "traffic": (traffic or {}).get(gname)}
+                    **_traffic(traffic, gname)}
         qn = max((n for n in by if by[n]["unit"] == "byte"), key=lambda n: by[n]["ms"], default=None)
         if qn:
             d = by[qn]
             ach = d["work"] / (d["ms"] * 1e-3) / 1e9
             roof_q = {"bound": "hbm", "kernel": qn.replace("llmfp8_", ""), "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
                       "peak_note": f"{pk['src']} copy bandwidth", "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
-                      "share_of_step": d["ms"] / tot, "traffic": (traffic or {}).get(qn)}
+                      "share_of_step": d["ms"] / tot, **_traffic(traffic, qn)}
 
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
