@@ -242,7 +242,10 @@ def main():
     H = model.H
     M = a.batch * a.seq
     flops_step = model.linear_flops(M)                 # per rank
-    reducer = dp.GradAllReducer(model.parameters()) if world > 1 else None
+    # LLMFP8_NVLS_REDUCE=1 (opt-in, unmeasured): weight gradients written by the wgrad GEMMs into a symmetric arena and summed in the
+    # NVSwitch fabric by our own kernel (csrc/nvls_reduce.cu) instead of NCCL
+    arena = dp.NvlsGradArena(dp.gemm_weight_buffers(model)) if world > 1 and os.environ.get("LLMFP8_NVLS_REDUCE", "0") == "1" else None
+    reducer = dp.GradAllReducer(model.parameters(), nvls=arena) if world > 1 else None
 
     g = torch.Generator(device=dev).manual_seed(1234 + rank)           # 42 + rank seeding in the reference: train_multi_gpu.py:1003
     x_dev = torch.randn(a.batch, a.seq, H, device=dev, generator=g).bfloat16()
@@ -420,6 +423,10 @@ def main():
                       "peak_note": f"{pk['src']} copy bandwidth", "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
                       "share_of_step": d["ms"] / tot, **_traffic(traffic, qn)}
 
+    if arena is not None:
+        arena.check()                      # a rank meeting that timed out invalidates the run: raise instead of printing a number
+        if reducer.nvls_launches == 0:
+            raise RuntimeError("LLMFP8_NVLS_REDUCE=1 but no gradient went through the in-switch reduce")
     cpu = None
     if rank == 0 and world == 1 and not a.no_cpu_baseline:
         cpu = cpu_port_baseline(a, a.cpu_sample_tokens)
@@ -431,13 +438,13 @@ def main():
             "data": "synthetic",
             "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
                        "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,
-                       "parallelism": f"dp{world}", "grad_reduce": ("sum of 1/N-prescaled gradients" if reducer is not None and reducer.prescaled else "avg") if world > 1 else None,
+                       "parallelism": f"dp{world}", "grad_reduce": (("in-switch sum (multimem.ld_reduce / st, own kernel) of 1/N-prescaled gradients" if arena is not None else "sum of 1/N-prescaled gradients") if reducer is not None and reducer.prescaled else "avg") if world > 1 else None,
                        "launch": "cuda-graph replay" if graphed else "eager stream launches",
                        "residual_adds": (("fused: forward add after the GEMM, gradient in the RMSNorm backward" if a.scenario == "mxfp8"
                                          else "fused: GEMM epilogue / RMSNorm backward") if model.layers[0].fuse_residual else "separate elementwise passes"), "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS,
                        "experiments": {k: os.environ[k] for k in ("LLMFP8_GEMM_DEBUG", "LLMFP8_MX_EPILOGUE_RESIDUAL", "LLMFP8_MX_FUSED_ACT",
-                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB") if k in os.environ}},
+                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB") if k in os.environ}},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
             "cpu_baseline": cpu,

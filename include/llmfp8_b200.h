@@ -155,6 +155,22 @@ int llmfp8_nccl_allreduce_max_f32(void* comm, float* buf, int64_t n, void* strea
 int llmfp8_nccl_allreduce_sum_bf16(void* comm, void* buf, int64_t n, void* stream);
 int llmfp8_nccl_destroy(void* comm);
 
+/* Weight-gradient SUM all-reduce inside the NVSwitch fabric (multimem.ld_reduce / multimem.st), in place, for gradients that every
+ * rank keeps at the SAME offset of a symmetric, multicast-mapped buffer (the host maps it: cuMulticastCreate / cuMemMap, or
+ * torch.distributed._symmetric_memory).  Replaces the bucketed NCCL all-reduce DDP runs behind backward (train_multi_gpu.py:355-378)
+ * for the large gradients: each rank reduces 1/world of the buffer through the switch and broadcasts it, on <= max_ctas CTAs (0 = 8).
+ *   multicast_ptr    : multicast (not unicast) address of the gradient, 16-byte aligned; numel bf16, a multiple of 8.
+ *   signal_pads      : DEVICE array of `world` pointers, entry r = rank r's zero-initialised signal pad (peer-mapped), each
+ *                      signal_pad_bytes >= 4 * world * llmfp8_nvls_grid(numel, world, max_ctas); the slots are 0 again on return,
+ *                      so one pad serves every launch of a stream.  All ranks must issue the same launches in the same order.
+ *   timeout_ms       : a rank whose peers do not arrive gives up after this long (0 = 10 s, < 0 = never) and counts it;
+ *                      llmfp8_nvls_timeouts (synchronises the device) returns the count — non-zero means results are invalid.
+ * NOT yet run on hardware (round 1 ended without GPU time): opt-in through dp.GradAllReducer(nvls=...) / LLMFP8_NVLS_REDUCE=1. */
+int llmfp8_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world,
+                                   int max_ctas, int timeout_ms, void* stream);
+int llmfp8_nvls_grid(int64_t numel, int world, int max_ctas);
+int llmfp8_nvls_timeouts(unsigned int* count);
+
 #ifdef __cplusplus
 }
 #endif

@@ -52,6 +52,9 @@ _PROTOTYPES = {
     "llmfp8_nccl_allreduce_max_f32": [vp, vp, i64, vp],
     "llmfp8_nccl_allreduce_sum_bf16": [vp, vp, i64, vp],
     "llmfp8_nccl_destroy": [vp],
+    "llmfp8_nvls_allreduce_sum_bf16": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
+    "llmfp8_nvls_grid": [i64, i32, i32],
+    "llmfp8_nvls_timeouts": [vp],
     "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }
 _RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
@@ -136,7 +139,7 @@ class _Profiled:
     def __getattr__(self, name):
         fn = getattr(self._lib, name)
         if name in ("llmfp8_gemm_force_bn", "llmfp8_gemm_force_cg", "llmfp8_gemm_debug", "llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
-                    "llmfp8_rmsnorm_bwd_ws_rows") or name.startswith("llmfp8_nccl_"):
+                    "llmfp8_rmsnorm_bwd_ws_rows") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
             return fn
         import torch
 

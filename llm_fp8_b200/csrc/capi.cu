@@ -114,6 +114,9 @@ int comm_init(const void*, int, int, void**);
 int comm_allreduce_max_f32(void*, float*, int64_t, cudaStream_t);
 int comm_allreduce_sum_bf16(void*, void*, int64_t, cudaStream_t);
 int comm_destroy(void*);
+int launch_nvls_allreduce_sum_bf16(void*, int64_t, void* const*, int64_t, int, int, int, int, cudaStream_t);
+int nvls_grid(int64_t, int, int);
+int nvls_timeouts(unsigned int*);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
@@ -229,5 +232,11 @@ int llmfp8_nccl_init(const void* id128, int rank, int world, void** comm) { retu
 int llmfp8_nccl_allreduce_max_f32(void* comm, float* buf, int64_t n, void* stream) { return comm_allreduce_max_f32(comm, buf, n, S(stream)); }
 int llmfp8_nccl_allreduce_sum_bf16(void* comm, void* buf, int64_t n, void* stream) { return comm_allreduce_sum_bf16(comm, buf, n, S(stream)); }
 int llmfp8_nccl_destroy(void* comm) { return comm_destroy(comm); }
+int llmfp8_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world,
+                                   int max_ctas, int timeout_ms, void* stream) {
+    return launch_nvls_allreduce_sum_bf16(multicast_ptr, numel, signal_pads, signal_pad_bytes, rank, world, max_ctas, timeout_ms, S(stream));
+}
+int llmfp8_nvls_grid(int64_t numel, int world, int max_ctas) { return nvls_grid(numel, world, max_ctas); }
+int llmfp8_nvls_timeouts(unsigned int* count) { return nvls_timeouts(count); }
 
 }  // extern "C"

@@ -1,0 +1,151 @@
+// Weight-gradient SUM all-reduce in the NVSwitch fabric (SURVEY.md §8(e) exchange 2): the wgrad GEMMs of every rank
+// write their partial dW = dY_local^T X_local into the SAME offset of a symmetric, multicast-mapped gradient arena; this kernel then
+// has rank r pull the in-switch sum of its 1/world slice through the multicast address (multimem.ld_reduce: the switch reads the
+// slice from all GPUs and adds in fp32) and push the rounded bf16 result back through it (multimem.st: the switch writes all GPUs).
+// Per gradient byte each GPU's SMs touch 2/world bytes instead of the ring's 2(world-1)/world reads + writes + adds, so a handful of
+// CTAs keep up with the rate at which backward produces gradients — the SMs, HBM traffic and power NCCL's 24..32 CTAs take from
+// the GEMMs is what keeps the 8-GPU step at 6.87x instead of >= 7x.  Stands in for DDP's bucketed all-reduce (train_multi_gpu.py:355-378).
+//
+// Ranks meet twice per launch on per-CTA signal slots in peer memory (CAS 0 -> 1 on the peer's slot, CAS 1 -> 0 on one's own: the
+// slots are back at 0 when the kernel ends, so consecutive launches on one stream reuse them without epochs):
+//   entry (relaxed): every rank's wgrad GEMM for this gradient has completed (its reduce kernel is stream-ordered after it);
+//   exit  (release / acquire): every rank's multimem.st has landed before any rank's next kernel reads or overwrites the gradient.
+// A rank that waits longer than `timeout_ns` (%globaltimer) gives up, counts it in g_nvls_timeouts (llmfp8_nvls_timeouts) and leaves — the
+// result is then wrong and the host must raise, but the GPU is never left spinning.
+//
+// STATUS: compiled for sm_100a; written after the round-1 GPU budget was spent, NOT yet run on hardware -> opt-in (LLMFP8_NVLS_REDUCE=1).
+#include "common.cuh"
+
+namespace llmfp8 {
+
+namespace {
+
+constexpr int kThreads = 512;
+constexpr int kUnroll = 4;
+constexpr int kMaxWorld = 32;
+
+__device__ unsigned int g_nvls_timeouts = 0;
+
+__device__ __forceinline__ uint32_t cas_relaxed_sys(uint32_t* p, uint32_t cmp, uint32_t val) {
+    uint32_t old;
+    asm volatile("atom.relaxed.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ uint32_t cas_release_sys(uint32_t* p, uint32_t cmp, uint32_t val) {
+    uint32_t old;
+    asm volatile("atom.release.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+__device__ __forceinline__ uint32_t cas_acquire_sys(uint32_t* p, uint32_t cmp, uint32_t val) {
+    uint32_t old;
+    asm volatile("atom.acquire.sys.global.cas.b32 %0, [%1], %2, %3;" : "=r"(old) : "l"(p), "r"(cmp), "r"(val) : "memory");
+    return old;
+}
+
+__device__ __forceinline__ long long now_ns() {
+    long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
+// thread t < world of each CTA pairs with CTA blockIdx.x of rank t.  Returns false on timeout.
+template <bool ORDER>
+__device__ __forceinline__ bool meet_ranks(uint32_t* const* pads, int rank, int world, long long timeout_ns) {
+    bool ok = true;
+    if (static_cast<int>(threadIdx.x) < world) {
+        const int peer = threadIdx.x;
+        uint32_t* put = pads[peer] + static_cast<size_t>(blockIdx.x) * world + rank;    // my slot on the peer
+        uint32_t* get = pads[rank] + static_cast<size_t>(blockIdx.x) * world + peer;    // the peer's slot on me
+        const long long t0 = now_ns();
+        while ((ORDER ? cas_release_sys(put, 0u, 1u) : cas_relaxed_sys(put, 0u, 1u)) != 0u)
+            if (timeout_ns > 0 && now_ns() - t0 > timeout_ns) { ok = false; break; }
+        while (ok && (ORDER ? cas_acquire_sys(get, 1u, 0u) : cas_relaxed_sys(get, 1u, 0u)) != 1u)
+            if (timeout_ns > 0 && now_ns() - t0 > timeout_ns) { ok = false; break; }
+        if (!ok) atomicAdd(&g_nvls_timeouts, 1u);
+    }
+    return ok;
+}
+
+__device__ __forceinline__ uint4 multimem_sum_bf16x8(const void* mc) {
+    uint4 v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.bf16x2 {%0, %1, %2, %3}, [%4];"
+                 : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+                 : "l"(mc)
+                 : "memory");
+    return v;
+}
+__device__ __forceinline__ void multimem_store16(void* mc, const uint4& v) {
+    asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(mc), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+
+// mc: multicast address of the gradient (16-byte aligned); nvec: its length in 16-byte vectors (8 bf16 each)
+__global__ void __launch_bounds__(kThreads) nvls_allreduce_sum_bf16_kernel(uint4* mc, int64_t nvec, uint32_t* const* pads, int rank, int world,
+                                                                           long long timeout_ns) {
+    pdl_wait();
+    pdl_launch_dependents();
+    __shared__ int alive;
+    if (threadIdx.x == 0) alive = 1;
+    __syncthreads();
+    if (!meet_ranks<false>(pads, rank, world, timeout_ns)) alive = 0;
+    __syncthreads();
+    if (alive) {
+        const int64_t per = (nvec + world - 1) / world;
+        const int64_t lo = per * rank;
+        const int64_t hi = lo + per < nvec ? lo + per : nvec;
+        const int64_t stride = static_cast<int64_t>(gridDim.x) * kThreads;
+        for (int64_t i = lo + static_cast<int64_t>(blockIdx.x) * kThreads + threadIdx.x; i < hi; i += stride * kUnroll) {
+            uint4 v[kUnroll];
+#pragma unroll
+            for (int u = 0; u < kUnroll; u++)
+                if (i + u * stride < hi) v[u] = multimem_sum_bf16x8(mc + i + u * stride);
+#pragma unroll
+            for (int u = 0; u < kUnroll; u++)
+                if (i + u * stride < hi) multimem_store16(mc + i + u * stride, v[u]);
+        }
+    }
+    __syncthreads();                       // every thread's stores are ordered before the releasing CAS of threads < world
+    if (alive) meet_ranks<true>(pads, rank, world, timeout_ns);
+}
+
+}  // namespace
+
+int nvls_grid(int64_t numel, int world, int max_ctas) {
+    const int64_t nvec = numel / 8;
+    const int64_t per = (nvec + world - 1) / world;
+    int64_t ctas = (per + static_cast<int64_t>(kThreads) * kUnroll - 1) / (static_cast<int64_t>(kThreads) * kUnroll);
+    const int cap = max_ctas > 0 ? max_ctas : 8;
+    if (ctas > cap) ctas = cap;
+    if (ctas < 1) ctas = 1;
+    return static_cast<int>(ctas);
+}
+
+int launch_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* const* signal_pads, int64_t pad_bytes, int rank, int world, int max_ctas,
+                                   int timeout_ms, cudaStream_t stream) {
+    LLMFP8_REQUIRE(world >= 2 && world <= kMaxWorld && rank >= 0 && rank < world, "nvls_allreduce_sum_bf16: bad rank %d of %d", rank, world);
+    LLMFP8_REQUIRE(numel >= 0 && numel % 8 == 0, "nvls_allreduce_sum_bf16: numel %lld must be a multiple of 8 (16-byte vectors)", (long long)numel);
+    if (numel == 0) return 0;
+    LLMFP8_REQUIRE(multicast_ptr != nullptr && (reinterpret_cast<uintptr_t>(multicast_ptr) & 15) == 0,
+                   "nvls_allreduce_sum_bf16: the multicast address must be non-null and 16-byte aligned");
+    LLMFP8_REQUIRE(signal_pads != nullptr, "nvls_allreduce_sum_bf16: null signal pads");
+    const int ctas = nvls_grid(numel, world, max_ctas);
+    LLMFP8_REQUIRE(static_cast<int64_t>(ctas) * world * 4 <= pad_bytes, "nvls_allreduce_sum_bf16: %d CTAs x %d ranks need %lld bytes of signal pad, have %lld",
+                   ctas, world, (long long)ctas * world * 4, (long long)pad_bytes);
+    // 0 -> 10 s (far beyond any rank skew of a healthy step), < 0 -> wait for ever (what NCCL does)
+    const long long timeout_ns = timeout_ms == 0 ? 10000000000LL : (timeout_ms < 0 ? 0LL : static_cast<long long>(timeout_ms) * 1000000LL);
+    LLMFP8_LAUNCH(nvls_allreduce_sum_bf16_kernel, dim3(ctas), dim3(kThreads), 0, stream, static_cast<uint4*>(multicast_ptr), numel / 8,
+                  reinterpret_cast<uint32_t* const*>(signal_pads), rank, world, timeout_ns);
+    LLMFP8_LAUNCH_CHECK("nvls_allreduce_sum_bf16");
+    return 0;
+}
+
+int nvls_timeouts(unsigned int* count) {
+    LLMFP8_REQUIRE(count != nullptr, "nvls_timeouts: null output");
+    cudaError_t e = cudaMemcpyFromSymbol(count, g_nvls_timeouts, sizeof(unsigned int));     // synchronises: diagnostics only
+    if (e != cudaSuccess) {
+        set_error("nvls_timeouts: %s", cudaGetErrorString(e));
+        return static_cast<int>(e);
+    }
+    return 0;
+}
+
+}  // namespace llmfp8

@@ -11,8 +11,9 @@ tensor is the all-reduce buffer.
 """
 from __future__ import annotations
 
+import bisect
 import os
-from typing import Iterable, List, Optional
+from typing import Iterable, List, Optional, Sequence, Tuple
 
 import torch
 import torch.distributed as dist
@@ -57,7 +58,7 @@ class GradAllReducer:
     for every outstanding reduction."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True,
-                 prescaled: Optional[bool] = None, bucket_bytes: Optional[int] = None):
+                 prescaled: Optional[bool] = None, bucket_bytes: Optional[int] = None, nvls: Optional["NvlsGradArena"] = None):
         """prescaled (default; LLMFP8_GRAD_REDUCE=avg turns it off): the caller multiplies its loss by `loss_scale` (= 1/world) and
         the gradients are all-reduced with SUM — the same mean as AVG, but SUM is the one reduction NVSwitch can do in the fabric:
         NCCL's NVLS algorithms have no AVG / pre-multiplied sum, so with AVG it falls back to a 32-channel ring.  Measured at 8 B200s
@@ -85,6 +86,14 @@ class GradAllReducer:
         self._small: List[torch.nn.Parameter] = []
         self._handles = []
         self.bytes_reduced = 0
+        # nvls: gradients that the wgrad GEMMs wrote into the symmetric arena are summed in the NVSwitch fabric by our own kernel
+        # (csrc/nvls_reduce.cu) on a side stream instead of going through NCCL; everything else takes the paths below.
+        self.nvls = nvls if self.world > 1 else None
+        self.nvls_launches = 0
+        self._nvls_stream = None
+        self._nvls_busy = False
+        if self.nvls is not None and not self.prescaled:
+            raise RuntimeError("the in-switch gradient reduce is a plain SUM: it needs prescaled=True (loss scaled by 1/world)")
         if self.world > 1:
             for p in params:
                 if p.requires_grad:
@@ -98,6 +107,18 @@ class GradAllReducer:
         g = p.grad
         if g is None:
             return
+        if self.nvls is not None and g.is_contiguous():
+            where = self.nvls.locate(g)
+            if where is not None:
+                if self._nvls_stream is None:
+                    self._nvls_stream = self.nvls.new_stream()
+                self._nvls_stream.wait_stream(self.nvls.current_stream())      # the wgrad GEMM that wrote g is on the current stream
+                self.nvls.reduce(where, g, self._nvls_stream)
+                self._nvls_busy = True
+                self.nvls_launches += 1
+                self.collectives += 1
+                self.bytes_reduced += g.numel() * g.element_size()
+                return
         if g.numel() >= self.direct_numel and g.is_contiguous():
             self.bytes_reduced += g.numel() * g.element_size()
             if self.bucket_bytes > 0:
@@ -125,6 +146,9 @@ class GradAllReducer:
         if self.world == 1:
             return
         post_scale = self.average and self._op() == dist.ReduceOp.SUM
+        if self._nvls_busy:
+            self.nvls.current_stream().wait_stream(self._nvls_stream)
+            self._nvls_busy = False
         self._flush_pending()
         if self._small:
             grads = [p.grad for p in self._small]
@@ -151,6 +175,155 @@ class GradAllReducer:
         for h in self._handles:
             h.remove()
         self._handles = []
+
+
+# ------------------------------------------------------------------------------------------ in-switch gradient reduce (NVLS)
+def gemm_weight_buffers(module: torch.nn.Module) -> List[Tuple[torch.Tensor, List[torch.nn.Parameter]]]:
+    """Every [out, in] buffer that a wgrad GEMM of the path writes a gradient for, with the Parameters living in it: Linear.weight,
+    LayerNormLinear.weight (or the joined buffer of its split query / key / value weights: te_llama.py:198-211), LayerNormMLP's
+    fc1_weight and fc2_weight.  Call it after the module is on its device (the joined buffer is established here if needed)."""
+    from . import modules as m
+    out = []
+    for mod in module.modules():
+        if isinstance(mod, m.LayerNormMLP):
+            out += [(mod.fc1_weight, [mod.fc1_weight]), (mod.fc2_weight, [mod.fc2_weight])]
+        elif isinstance(mod, m.LayerNormLinear):
+            if mod._split is None:
+                out.append((mod.weight, [mod.weight]))
+            elif m._JOIN_SPLIT_WEIGHTS:
+                ws = [getattr(mod, n + "weight") for n in mod._split]
+                mod._joined = m._joined_rows(ws, getattr(mod, "_joined", None))
+                out.append((mod._joined, ws))
+        elif isinstance(mod, m.Linear):
+            out.append((mod.weight, [mod.weight]))
+    return [(w, ps) for w, ps in out if all(p.requires_grad for p in ps)]
+
+
+def plan_arena(sizes: Sequence[int], chunk_bytes: int, align: int = 256) -> Tuple[List[Tuple[int, int]], List[int]]:
+    """Packs buffers of `sizes` bytes, in order, into chunks of at most chunk_bytes (a buffer larger than that gets a chunk of its
+    own) -> ([(chunk index, byte offset)] per buffer, [chunk size in bytes]).  Offsets are multiples of `align` (>= the 16 bytes the
+    reduce kernel's vectors need).  Deterministic in its inputs: every rank computes the same plan, which is what makes the arena
+    symmetric."""
+    place, chunks = [], []
+    used = None
+    for n in sizes:
+        n = -(-int(n) // align) * align
+        if used is None or (used > 0 and used + n > chunk_bytes):
+            chunks.append(0)
+            used = 0
+        place.append((len(chunks) - 1, used))
+        used += n
+        chunks[-1] = used
+    return place, chunks
+
+
+class NvlsGradArena:
+    """Symmetric, multicast-mapped home of the large weight gradients (one identical layout on every rank).
+
+    The wgrad GEMMs store dW straight into it (functional.wgrad_out), autograd adopts those views as `.grad`, and
+    GradAllReducer(nvls=arena) sums each one across ranks inside the NVSwitch fabric with llmfp8_nvls_allreduce_sum_bf16
+    (csrc/nvls_reduce.cu) — `max_ctas` CTAs (default 8, LLMFP8_NVLS_CTAS) instead of NCCL's 24-32 — on a side stream, overlapped with
+    the rest of backward.  torch.distributed._symmetric_memory does the plumbing only: the VMM allocation, the peer / multicast
+    mappings and the zeroed signal pads; every byte is moved by our kernel.
+
+    bf16 gradients only; one arena per model; collective constructor (same buffers, same order on all ranks).
+    STATUS: not yet run on hardware (written after round 1's GPU budget was spent): opt-in, bench.py builds it with LLMFP8_NVLS_REDUCE=1."""
+
+    def __init__(self, buffers: Sequence[Tuple[torch.Tensor, List[torch.nn.Parameter]]], group=None, chunk_bytes: Optional[int] = None,
+                 max_ctas: Optional[int] = None, timeout_ms: int = 0):
+        if not (dist.is_initialized() and torch.cuda.is_available()):
+            raise RuntimeError("NvlsGradArena needs CUDA and an initialised NCCL process group")
+        import torch.distributed._symmetric_memory as symm
+
+        from . import _lib
+        self._lib = _lib.load()
+        self.group = group if group is not None else dist.group.WORLD
+        self.rank, self.world = dist.get_rank(self.group), dist.get_world_size(self.group)
+        buffers = [(w, ps) for w, ps in buffers if w.dtype == torch.bfloat16 and w.is_cuda and w.numel() % 8 == 0]
+        if not buffers:
+            raise RuntimeError("NvlsGradArena: no bf16 CUDA weight buffers to host")
+        self.device = buffers[0][0].device
+        if chunk_bytes is None:
+            chunk_bytes = int(float(os.environ.get("LLMFP8_NVLS_CHUNK_MB", "1024")) * (1 << 20))
+        self.max_ctas = int(os.environ.get("LLMFP8_NVLS_CTAS", "8")) if max_ctas is None else int(max_ctas)
+        self.timeout_ms = int(timeout_ms)
+        place, chunks = plan_arena([w.numel() * 2 for w, _ in buffers], chunk_bytes)
+        try:
+            symm.enable_symm_mem_for_group(self.group.group_name)
+        except Exception:
+            pass                                       # newer torch enables it implicitly
+        self.pad_bytes = int(symm.get_signal_pad_size())
+        self._chunks = []                              # (base address, bytes, multicast address, device array of signal-pad pointers, tensor, handle)
+        with torch.cuda.device(self.device):
+            for nbytes in chunks:
+                t = symm.empty(nbytes // 2, dtype=torch.bfloat16, device=self.device)
+                hdl = symm.rendezvous(t, group=self.group)
+                mc = int(hdl.multicast_ptr or 0)
+                if mc == 0:
+                    raise RuntimeError("NvlsGradArena: this system has no NVLink multicast (NVLS) mapping for symmetric memory")
+                t.zero_()
+                self._chunks.append((t.data_ptr(), nbytes, mc, int(hdl.signal_pad_ptrs_dev), t, hdl))
+            torch.cuda.synchronize(self.device)
+        dist.barrier(group=self.group)
+        self._bases = [c[0] for c in self._chunks]
+        order = sorted(range(len(self._chunks)), key=lambda i: self._bases[i])
+        self._chunks = [self._chunks[i] for i in order]
+        self._bases = [c[0] for c in self._chunks]
+        remap = {old: new for new, old in enumerate(order)}
+        self.homes = []
+        from . import functional as fn
+        for (w, ps), (ci, off) in zip(buffers, place):
+            t = self._chunks[remap[ci]][4]
+            home = t[off // 2: off // 2 + w.numel()]
+            self.homes.append(home)
+            fn._WGRAD_OUT[w.data_ptr()] = (home, list(ps))
+        self._keys = [w.data_ptr() for w, _ in buffers]
+        self.bytes = sum(chunks)
+
+    # -- used by GradAllReducer
+    def current_stream(self):
+        return torch.cuda.current_stream(self.device)
+
+    def new_stream(self):
+        return torch.cuda.Stream(device=self.device)
+
+    def locate(self, g: torch.Tensor) -> Optional[Tuple[int, int]]:
+        """(chunk, byte offset) if g lies wholly inside the arena and the reduce kernel can take it, else None."""
+        return locate_in_chunks(self._bases, [c[1] for c in self._chunks], g.data_ptr(), g.numel() * g.element_size()) \
+            if (g.dtype == torch.bfloat16 and g.numel() % 8 == 0) else None
+
+    def reduce(self, where: Tuple[int, int], g: torch.Tensor, stream) -> None:
+        from . import _lib
+        ci, off = where
+        _, _, mc, pads, _, _ = self._chunks[ci]
+        rc = self._lib.llmfp8_nvls_allreduce_sum_bf16(mc + off, g.numel(), pads, self.pad_bytes, self.rank, self.world, self.max_ctas, self.timeout_ms,
+                                                      stream.cuda_stream)
+        _lib.check(rc, "nvls_allreduce_sum_bf16")
+
+    def check(self) -> None:
+        """Raises if any reduce launch gave up waiting for its peers (synchronises the device)."""
+        import ctypes as C
+
+        from . import _lib
+        n = C.c_uint(0)
+        with torch.cuda.device(self.device):
+            _lib.check(self._lib.llmfp8_nvls_timeouts(C.byref(n)), "nvls_timeouts")
+        if n.value:
+            raise RuntimeError(f"in-switch gradient reduce: {n.value} rank meetings timed out — gradients of this step are invalid")
+
+    def release(self) -> None:
+        from . import functional as fn
+        for k in self._keys:
+            fn._WGRAD_OUT.pop(k, None)
+        self._keys = []
+
+
+def locate_in_chunks(bases: Sequence[int], sizes: Sequence[int], addr: int, nbytes: int) -> Optional[Tuple[int, int]]:
+    """bases ascending.  -> (chunk index, byte offset) of [addr, addr + nbytes) if one chunk contains it and the offset is 16-byte aligned."""
+    i = bisect.bisect_right(bases, addr) - 1
+    if i < 0 or addr + nbytes > bases[i] + sizes[i] or (addr - bases[i]) % 16:
+        return None
+    return i, addr - bases[i]
 
 
 class CAbiComm:

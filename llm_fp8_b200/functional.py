@@ -129,6 +129,25 @@ class _SideWgrad:
                 o.record_stream(self.main)       # allocated from the side stream's pool, consumed on the main stream
 
 
+# Where a wgrad GEMM writes: by default a fresh tensor.  A data-parallel host may register, per weight buffer (keyed by its address — for
+# the split qkv weights that is the joined buffer), a home for the gradient inside a symmetric, multicast-mapped arena
+# (dp.NvlsGradArena): the GEMM's epilogue then stores dW straight into the memory the in-switch all-reduce works on, no copy in between.
+# Empty unless such an arena exists; a miss (weights moved since) just allocates as before.  Entries: address -> (home, parameters whose
+# gradient lives there).  While one of them still holds a .grad (accumulation over micro-batches) the home IS that gradient and must
+# not be overwritten: the GEMM then gets a fresh tensor and autograd adds it in.
+_WGRAD_OUT = {}
+
+
+def wgrad_out(key: int, N: int, K: int, dtype: torch.dtype) -> Optional[torch.Tensor]:
+    entry = _WGRAD_OUT.get(key)
+    if entry is None:
+        return None
+    home, params = entry
+    if home.dtype != dtype or home.numel() != N * K or any(p.grad is not None for p in params):
+        return None
+    return home.view(N, K)          # a fresh alias: autograd keeps it as .grad without a copy (sole owner, contiguous)
+
+
 def _wgrad(dyq, xq, N, K, T, weight):
     """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
     return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
@@ -165,6 +184,7 @@ class LinearFn(torch.autograd.Function):
             ctx.shape = x.shape
             ctx.dims = (M, N, K)
             ctx.wdtype = weight.dtype
+            ctx.wkey = weight.data_ptr()
             ctx.needs = (x.requires_grad, weight.requires_grad)
             ctx.has_residual = residual is not None
             ctx.w_si = (wq.scale_inv, wq.scale_inv_off)
@@ -192,7 +212,7 @@ class LinearFn(torch.autograd.Function):
             dyq = ops.quantize(dy2, bf, pb, b0 + 0)
         wg = _SideWgrad(dy2.device)
         dx = ops.fp8_gemm(dyq, False, wq, True, M, K, N)                  # dgrad: contraction over N, W read MN-major
-        dw = wg.run(lambda: ops.fp8_gemm(dyq, True, xq, True, N, K, M, out_dtype=ctx.wdtype))   # wgrad: contraction over tokens
+        dw = wg.run(lambda: ops.fp8_gemm(dyq, True, xq, True, N, K, M, out=wgrad_out(ctx.wkey, N, K, ctx.wdtype), out_dtype=ctx.wdtype))   # wgrad: contraction over tokens
         dgamma = None
         if ln_weight is not None:
             dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
@@ -232,6 +252,7 @@ class LayerNormMLPFn(torch.autograd.Function):
             ctx.shape = x.shape
             ctx.dims = (M, H, I)
             ctx.wdtype = w1.dtype
+            ctx.wkey = (w1.data_ptr(), w2.data_ptr())
         return y.reshape(x.shape)
 
     @staticmethod
@@ -255,9 +276,9 @@ class LayerNormMLPFn(torch.autograd.Function):
         da = ops.fp8_gemm(dyq, False, w2q, True, M, I, H)                        # fc2 dgrad
         dfc1q, db1 = ops.dswiglu_quant(da, fc1, bf, pb, b0 + 0, want_dbias=ctx.has_bias)
         wg = _SideWgrad(dy2.device)
-        dw2 = wg.run(lambda: ops.fp8_gemm(dyq, True, aq, True, H, I, M, out_dtype=ctx.wdtype))   # fc2 wgrad
+        dw2 = wg.run(lambda: ops.fp8_gemm(dyq, True, aq, True, H, I, M, out=wgrad_out(ctx.wkey[1], H, I, ctx.wdtype), out_dtype=ctx.wdtype))   # fc2 wgrad
         dln = ops.fp8_gemm(dfc1q, False, w1q, True, M, H, 2 * I)                 # fc1 dgrad
-        dw1 = wg.run(lambda: ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out_dtype=ctx.wdtype))   # fc1 wgrad
+        dw1 = wg.run(lambda: ops.fp8_gemm(dfc1q, True, lnq, True, 2 * I, H, M, out=wgrad_out(ctx.wkey[0], 2 * I, H, ctx.wdtype), out_dtype=ctx.wdtype))   # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
         wg.join()
         Fp8Meta.end_bwd(s)
@@ -310,6 +331,7 @@ class MXLinearFn(torch.autograd.Function):
             ctx.save_for_backward(xq.col, xq.sf_col, wq.col, wq.sf_col, x2 if ln_weight is not None else None, ln_weight, rsigma)
             ctx.has_bias = bias is not None
             ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, N, K), weight.dtype
+            ctx.wkey = weight.data_ptr()
             ctx.has_residual = residual is not None
         ctx.set_materialize_grads(False)
         y = y.reshape(*x.shape[:-1], N)
@@ -328,7 +350,7 @@ class MXLinearFn(torch.autograd.Function):
         wg = _SideWgrad(dy2.device)
         dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N)
         # wgrad: dW[N,K] = dY^T X: both colwise (blocks along tokens), both MN-major
-        dw = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out_dtype=ctx.wdtype))
+        dw = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out=wgrad_out(ctx.wkey, N, K, ctx.wdtype), out_dtype=ctx.wdtype))
         dgamma = None
         if ln_weight is not None:
             dx, dgamma = ops.rmsnorm_bwd(dx, x2, ln_weight, rsigma, add=_2d(dres).contiguous() if dres is not None else None)
@@ -365,6 +387,7 @@ class MXLayerNormMLPFn(torch.autograd.Function):
             ctx.has_bias = b1 is not None
             ctx.residual = residual
             ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, H, I), w1.dtype
+            ctx.wkey = (w1.data_ptr(), w2.data_ptr())
         return y.reshape(x.shape)
 
     @staticmethod
@@ -381,9 +404,9 @@ class MXLayerNormMLPFn(torch.autograd.Function):
             dfc1, db1 = ops.dswiglu_bf16(da, fc1, want_dbias=ctx.has_bias)
             dfq = ops.mx_quantize(dfc1, True, True)
         wg = _SideWgrad(dy2.device)
-        dw2 = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out_dtype=ctx.wdtype))      # fc2 wgrad
+        dw2 = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, a_col, a_sfc, True, H, I, M, out=wgrad_out(ctx.wkey[1], H, I, ctx.wdtype), out_dtype=ctx.wdtype))      # fc2 wgrad
         dln = ops.mxfp8_gemm(dfq.row, dfq.sf_row, False, w1_col, w1_sfc, True, M, H, 2 * I)                  # fc1 dgrad
-        dw1 = wg.run(lambda: ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out_dtype=ctx.wdtype))  # fc1 wgrad
+        dw1 = wg.run(lambda: ops.mxfp8_gemm(dfq.col, dfq.sf_col, True, ln_col, ln_sfc, True, 2 * I, H, M, out=wgrad_out(ctx.wkey[0], 2 * I, H, ctx.wdtype), out_dtype=ctx.wdtype))  # fc1 wgrad
         dx, dgamma = ops.rmsnorm_bwd(dln, x2, ln_weight, rsigma, add=dy2 if ctx.residual else None)
         wg.join()
         return dx.reshape(ctx.shape), dgamma, dw1, db1, dw2, db2, None, None, None, None, None

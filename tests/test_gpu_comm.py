@@ -63,3 +63,86 @@ def test_cabi_nccl_single_rank_roundtrip():
     torch.cuda.synchronize()
     assert a.tolist() == [2.0, 0.5] and torch.equal(g.cpu(), torch.arange(64).bfloat16())
     comm.destroy()
+
+
+# ------------------------------------------------------------------------------------------------ in-switch gradient reduce (NVLS)
+EXPERIMENTAL = pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
+                                  reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
+
+
+def _nvls_worker(rank, world, port, out):
+    """(1) llmfp8_nvls_allreduce_sum_bf16 on arena homes of awkward sizes, launched back to back on a side stream (signal pads reused),
+    against the sum computed on the host; (2) a 2-block FP8 stack stepped once with the NCCL reducer and once with the in-switch
+    reducer: same weight gradients (bf16 rounding of a different summation order apart), and the gradients live in the arena."""
+    import torch.distributed as dist
+
+    from llm_fp8_b200 import dp
+    from llm_fp8_b200.layer import LinearPathStack
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                      LLMFP8_DIST_TIMEOUT_S="60")
+    dp.init_from_env(backend="nccl")
+    dev = torch.device("cuda", rank)
+    res = {}
+    # -- (1) the kernel alone
+    shapes = [(1, 8), (3, 40), (257, 1032), (4096, 4096)]
+    ws = [torch.nn.Parameter(torch.empty(s, dtype=torch.bfloat16, device=dev)) for s in shapes]
+    arena = dp.NvlsGradArena([(w, [w]) for w in ws], chunk_bytes=1 << 20, timeout_ms=20000)
+    side = torch.cuda.Stream()
+    ok = True
+    for rep in range(3):                                  # pads must be clean again after every launch
+        gen = torch.Generator().manual_seed(11 + rep)
+        bases = [torch.randn(s, generator=gen) for s in shapes]
+        for home, b in zip(arena.homes, bases):
+            home.copy_((b * (rank + 1)).bfloat16().reshape(-1))
+        side.wait_stream(torch.cuda.current_stream())
+        for home in arena.homes:
+            where = arena.locate(home)
+            assert where is not None
+            arena.reduce(where, home, side)
+        torch.cuda.current_stream().wait_stream(side)
+        torch.cuda.synchronize()
+        dist.barrier()
+        for home, b in zip(arena.homes, bases):
+            want = sum((b * (r + 1)).bfloat16().float() for r in range(world)).reshape(-1)
+            ok = ok and torch.allclose(home.float().cpu(), want, rtol=2 ** -7, atol=1e-6)
+        dist.barrier()
+    arena.check()
+    arena.release()
+    res["kernel_ok"] = ok
+    # -- (2) the reducer on the FP8 path
+    grads = {}
+    for mode in ("nccl", "nvls"):
+        model = LinearPathStack("llama-3.2-1b", "mxfp8", 2, device=dev)
+        ar = dp.NvlsGradArena(dp.gemm_weight_buffers(model), timeout_ms=20000) if mode == "nvls" else None
+        red = dp.GradAllReducer(model.parameters(), nvls=ar)
+        g = torch.Generator(device=dev).manual_seed(100 + rank)
+        x = torch.randn(2, 256, model.H, device=dev, generator=g).bfloat16().requires_grad_(True)
+        (model(x).float().square().mean() * red.loss_scale).backward()
+        red.finish()
+        torch.cuda.synchronize()
+        grads[mode] = [p.grad.float().cpu() for p in model.parameters() if p.dim() == 2]
+        if ar is not None:
+            ar.check()
+            res["in_arena"] = all(ar.locate(p.grad) is not None for p in model.parameters() if p.dim() == 2)
+            res["launches"] = red.nvls_launches
+            ar.release()
+        red.remove()
+        dist.barrier()
+    res["grad_err"] = max(float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)) for a, b in zip(grads["nvls"], grads["nccl"]))
+    if rank == 0:
+        torch.save(res, out)
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@EXPERIMENTAL
+@pytest.mark.timeout(300)
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_nvls_gradient_reduce_two_gpus(tmp_path):
+    import torch.multiprocessing as mp
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_nvls_worker, args=(2, _free_port(), out), nprocs=2, join=True)
+    got = torch.load(out)
+    assert got["kernel_ok"], got
+    assert got["in_arena"] and got["launches"] == 2 * 6, got          # per block: q, k, v (row slices of one home), proj, fc1, fc2
+    assert got["grad_err"] <= 2 ** -6, got
