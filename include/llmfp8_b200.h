@@ -158,7 +158,8 @@ int llmfp8_nccl_destroy(void* comm);
 /* Weight-gradient SUM all-reduce inside the NVSwitch fabric (multimem.ld_reduce / multimem.st), in place, for gradients that every
  * rank keeps at the SAME offset of a symmetric, multicast-mapped buffer (the host maps it: cuMulticastCreate / cuMemMap, or
  * torch.distributed._symmetric_memory).  Replaces the bucketed NCCL all-reduce DDP runs behind backward (train_multi_gpu.py:355-378)
- * for the large gradients: each rank reduces 1/world of the buffer through the switch and broadcasts it, on <= max_ctas CTAs (0 = 8).
+ * for the large gradients: each rank reduces 1/world of the buffer through the switch and broadcasts it, on <= max_ctas CTAs of 128 threads (0 = 32),
+ * small enough to sit beside a resident GEMM CTA on the same SM.
  *   multicast_ptr    : multicast (not unicast) address of the gradient, 16-byte aligned; numel bf16, a multiple of 8.
  *   signal_pads      : DEVICE array of `world` pointers, entry r = rank r's zero-initialised signal pad (peer-mapped), each
  *                      signal_pad_bytes >= 4 * world * llmfp8_nvls_grid(numel, world, max_ctas); the slots are 0 again on return,

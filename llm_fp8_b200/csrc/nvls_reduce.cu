@@ -2,8 +2,8 @@
 // write their partial dW = dY_local^T X_local into the SAME offset of a symmetric, multicast-mapped gradient arena; this kernel then
 // has rank r pull the in-switch sum of its 1/world slice through the multicast address (multimem.ld_reduce: the switch reads the
 // slice from all GPUs and adds in fp32) and push the rounded bf16 result back through it (multimem.st: the switch writes all GPUs).
-// Per gradient byte each GPU's SMs touch 2/world bytes instead of the ring's 2(world-1)/world reads + writes + adds, so a handful of
-// CTAs keep up with the rate at which backward produces gradients — the SMs, HBM traffic and power NCCL's 24..32 CTAs take from
+// Per gradient byte each GPU's SMs touch 2/world bytes instead of the ring's 2(world-1)/world reads + writes + adds, so a few
+// small CTAs keep up with the rate at which backward produces gradients — the SMs, HBM traffic and power NCCL's 24..32 CTAs take from
 // the GEMMs is what keeps the 8-GPU step at 6.87x instead of >= 7x.  Stands in for DDP's bucketed all-reduce (train_multi_gpu.py:355-378).
 //
 // Ranks meet twice per launch on per-CTA signal slots in peer memory (CAS 0 -> 1 on the peer's slot, CAS 1 -> 0 on one's own: the
@@ -20,7 +20,9 @@ namespace llmfp8 {
 
 namespace {
 
-constexpr int kThreads = 512;
+// 128 threads x 40 registers = 5 K registers and no shared memory: such a CTA fits on an SM BESIDE a resident GEMM CTA (352 threads x <= 168
+// registers = 59 K of the 64 K), so the reduce does not wait for GEMM CTAs to drain and takes no SM away from them — only issue slots.
+constexpr int kThreads = 128;
 constexpr int kUnroll = 4;
 constexpr int kMaxWorld = 32;
 
@@ -113,7 +115,7 @@ int nvls_grid(int64_t numel, int world, int max_ctas) {
     const int64_t nvec = numel / 8;
     const int64_t per = (nvec + world - 1) / world;
     int64_t ctas = (per + static_cast<int64_t>(kThreads) * kUnroll - 1) / (static_cast<int64_t>(kThreads) * kUnroll);
-    const int cap = max_ctas > 0 ? max_ctas : 8;
+    const int cap = max_ctas > 0 ? max_ctas : 32;
     if (ctas > cap) ctas = cap;
     if (ctas < 1) ctas = 1;
     return static_cast<int>(ctas);

@@ -222,7 +222,8 @@ class NvlsGradArena:
 
     The wgrad GEMMs store dW straight into it (functional.wgrad_out), autograd adopts those views as `.grad`, and
     GradAllReducer(nvls=arena) sums each one across ranks inside the NVSwitch fabric with llmfp8_nvls_allreduce_sum_bf16
-    (csrc/nvls_reduce.cu) — `max_ctas` CTAs (default 8, LLMFP8_NVLS_CTAS) instead of NCCL's 24-32 — on a side stream, overlapped with
+    (csrc/nvls_reduce.cu) — `max_ctas` CTAs of 128 threads (default 32, LLMFP8_NVLS_CTAS; small enough to share an SM with a resident GEMM CTA, where NCCL's
+    24-32 CTAs each take a whole one) — on a side stream, overlapped with
     the rest of backward.  torch.distributed._symmetric_memory does the plumbing only: the VMM allocation, the peer / multicast
     mappings and the zeroed signal pads; every byte is moved by our kernel.
 
@@ -245,7 +246,7 @@ class NvlsGradArena:
         self.device = buffers[0][0].device
         if chunk_bytes is None:
             chunk_bytes = int(float(os.environ.get("LLMFP8_NVLS_CHUNK_MB", "1024")) * (1 << 20))
-        self.max_ctas = int(os.environ.get("LLMFP8_NVLS_CTAS", "8")) if max_ctas is None else int(max_ctas)
+        self.max_ctas = int(os.environ.get("LLMFP8_NVLS_CTAS", "32")) if max_ctas is None else int(max_ctas)
         self.timeout_ms = int(timeout_ms)
         place, chunks = plan_arena([w.numel() * 2 for w, _ in buffers], chunk_bytes)
         try:

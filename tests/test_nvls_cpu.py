@@ -16,7 +16,7 @@ import torch.multiprocessing as mp
 from llm_fp8_b200 import _lib, dp
 from llm_fp8_b200 import functional as fn
 
-THREADS, UNROLL = 512, 4          # kThreads / kUnroll of csrc/nvls_reduce.cu
+THREADS, UNROLL = 128, 4          # kThreads / kUnroll of csrc/nvls_reduce.cu
 
 
 # ------------------------------------------------------------------------------------------------ C ABI contract (no launch happens)
@@ -31,7 +31,7 @@ def test_cabi_rejects_bad_arguments_before_launching():
     assert call(None, 64, pads, 9216, 0, 2, 0, 0, None) == -1                 # no multicast address
     assert call(0x1008, 64, pads, 9216, 0, 2, 0, 0, None) == -1               # misaligned
     assert call(0x1000, 64, None, 9216, 0, 2, 0, 0, None) == -1               # no signal pads
-    assert call(0x1000, 1 << 30, pads, 32, 0, 8, 0, 0, None) == -1            # pad too small for 8 CTAs x 8 ranks
+    assert call(0x1000, 1 << 30, pads, 32, 0, 8, 0, 0, None) == -1            # pad too small for 32 CTAs x 8 ranks
     assert b"signal pad" in lib.llmfp8_last_error()
 
 
@@ -42,7 +42,7 @@ def test_grid_is_the_same_function_on_every_rank(world):
         for cap in (0, 1, 4, 16):
             g = lib.llmfp8_nvls_grid(numel, world, cap)
             per = -(-(numel // 8) // world)
-            want = max(1, min(cap or 8, -(-per // (THREADS * UNROLL))))
+            want = max(1, min(cap or 32, -(-per // (THREADS * UNROLL))))
             assert g == want
 
 

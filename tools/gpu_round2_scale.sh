@@ -32,7 +32,7 @@ run bucket256 LLMFP8_GRAD_BUCKET_MB=256                # coalesced gradient grou
 run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
 run fusedact LLMFP8_MX_FUSED_ACT=1
 # in-switch gradient reduce (own multimem kernel, csrc/nvls_reduce.cu) — only after tools/gpu_nvls2.sh passed on two GPUs
-run nvls8 LLMFP8_NVLS_REDUCE=1
-run nvls4 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=4
-run nvls16 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=16
+run nvls32 LLMFP8_NVLS_REDUCE=1
+run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
+run nvls96 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=96
 cat $S
