@@ -338,8 +338,10 @@ def main():
         zero()
 
     # warm-up (also fills the delayed-scaling history enough for real scales)
-    for _ in range(max(a.warmup, 3)):
+    for i in range(max(a.warmup, 3)):
         resident_step()
+        if arena is not None and i == 0:
+            arena.check()                  # fail after one step, not after hundreds of timed-out rank meetings
 
     graphed = False
     eager_resident_step, eager_e2e_step = resident_step, e2e_step
