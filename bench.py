@@ -345,7 +345,9 @@ def main():
 
     graphed = False
     eager_resident_step, eager_e2e_step = resident_step, e2e_step
-    if a.graph and world == 1:
+    # world > 1 only as a probe (LLMFP8_GRAPH_DP=1, tools/gpu_round2_scale.sh): NCCL's / our gradient reduces are captured with the step, so
+    # every rank replays the same launch sequence with no host jitter between ranks — unmeasured
+    if a.graph and (world == 1 or os.environ.get("LLMFP8_GRAPH_DP", "0") == "1"):
         # the same step, captured once into a CUDA graph (every kernel of forward + backward, the weight-gradient writes included)
         # and replayed: the host issues one launch per step instead of ~1500
         try:
@@ -446,7 +448,7 @@ def main():
                                          else "fused: GEMM epilogue / RMSNorm backward") if model.layers[0].fuse_residual else "separate elementwise passes"), "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS,
                        "experiments": {k: os.environ[k] for k in ("LLMFP8_GEMM_DEBUG", "LLMFP8_MX_EPILOGUE_RESIDUAL", "LLMFP8_MX_FUSED_ACT",
-                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB") if k in os.environ}},
+                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB", "LLMFP8_GRAPH_DP") if k in os.environ}},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
             "cpu_baseline": cpu,

@@ -35,4 +35,8 @@ run fusedact LLMFP8_MX_FUSED_ACT=1
 run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
 run nvls96 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=96
+# whole data-parallel step (collectives included) replayed from one CUDA graph: no host launch jitter between ranks
+tag=graphdp; env LLMFP8_GRAPH_DP=1 LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
+    bench.py --gpus $N --steps 4 --warmup 3 --scenario mxfp8 --no-roofline --graph 1 > gpurun_out/r02_scale_${tag}_n$N.json 2> gpurun_out/r02_scale_${tag}_n$N.err
+echo "$tag n=$N exit $?  $(tail -c 300 gpurun_out/r02_scale_${tag}_n$N.json | tr -d '\n' | grep -o '"ms_per_step": [0-9.]*')" >> $S
 cat $S
