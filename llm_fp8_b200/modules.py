@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from . import functional as fn
 from .fp8 import get_fp8_recipe, is_fp8_enabled
-from .recipe import DelayedScaling, MXFP8BlockScaling
+from .recipe import DelayedScaling, MXFP8BlockScaling, fwd_fmt
 
 
 def _init_weight(shape, dtype, device, std=0.023):
@@ -44,7 +44,42 @@ class _Fp8Module(nn.Module):
 
     def _apply(self, fn_, *args, **kwargs):
         self._wcache.clear()                 # .cuda() / .to() replace the parameters the copies were cast from
+        self._prefetched = False
         return super()._apply(fn_, *args, **kwargs)
+
+    # ---- weight copies quantised ahead of the forward that uses them (prefetch.WeightPrefetcher; opt-in, unmeasured)
+    _prefetched = False          # the copies for the coming forward already sit in _wcache
+    _last_recipe = None          # recipe of the latest forward: what a prefetch for the next step casts with
+
+    def _prefetch_targets(self):
+        """-> [(cache name, weight [out, in], forward slot of the weight)] as the autograd Functions of this module key them"""
+        raise NotImplementedError
+
+    def prefetch_weights(self, recipe, device, need_col: bool = True) -> None:
+        """Casts this module's weights exactly as its forward would (same kernels, same cache keys, same amax / scale slots) and keeps
+        the copies; the next forward(is_first_microbatch=None) picks them up instead of casting."""
+        with torch.no_grad():
+            for name, w, slot in self._prefetch_targets():
+                if isinstance(recipe, MXFP8BlockScaling):
+                    fn._weight_mx(self._wcache, True, (name, "mx"), w, need_col)
+                else:
+                    s = self._meta.get(recipe, device)
+                    fn._weight_pt(self._wcache, True, (name, recipe.key()), w, fwd_fmt(recipe.fp8_format), s["pf"], s["f0"] + slot)
+
+    def _wcache_tensors(self):
+        for v in self._wcache.values():
+            for t in (getattr(v, a, None) for a in ("data", "scale_inv", "row", "sf_row", "col", "sf_col")):
+                if isinstance(t, torch.Tensor):
+                    yield t
+
+    def _take_prefetched(self, is_first_microbatch, recipe):
+        """-> (is_first_microbatch to run with, drop the copies afterwards)"""
+        self._last_recipe = recipe
+        if self._prefetched:
+            self._prefetched = False
+            if is_first_microbatch is None:
+                return False, True           # reuse the kept copies (the TE contract's `False`), then let them go
+        return is_first_microbatch, False
 
     def get_extra_state(self):
         out = {}
@@ -93,10 +128,18 @@ class Linear(_Fp8Module):
         _check_active("Linear")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
+        first, drop = self._take_prefetched(is_first_microbatch, recipe)
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False, self._wcache, is_first_microbatch)
-        self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False, self._wcache, is_first_microbatch)
+            out = fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False, self._wcache, first)
+        else:
+            self._apply_extra_state(recipe, inp.device)
+            out = fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False, self._wcache, first)
+        if drop:
+            self._wcache.clear()
+        return out
+
+    def _prefetch_targets(self):
+        return [("w", self.weight, 1)]
 
 
 _JOIN_SPLIT_WEIGHTS = os.environ.get("LLMFP8_JOIN_SPLIT_WEIGHTS", "1") != "0"
@@ -200,11 +243,24 @@ class LayerNormLinear(_Fp8Module):
         recipe = get_fp8_recipe()
         w, b = self._weight_bias()
         g = torch.is_grad_enabled()
+        first, drop = self._take_prefetched(is_first_microbatch, recipe)
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, is_first_microbatch)
-        self._apply_extra_state(recipe, inp.device)
-        return fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache,
-                                 is_first_microbatch)
+            out = fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, first)
+        else:
+            self._apply_extra_state(recipe, inp.device)
+            out = fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, first)
+        if drop:
+            self._wcache.clear()
+        return out
+
+    def _prefetch_targets(self):
+        if self._split is None:
+            return [("w", self.weight, 1)]
+        ws = [getattr(self, n + "weight") for n in self._split]
+        if _JOIN_SPLIT_WEIGHTS:
+            self._joined = _joined_rows(ws, getattr(self, "_joined", None))
+            return [("w", self._joined, 1)]
+        return [("w", torch.cat([w.detach() for w in ws], dim=0), 1)]
 
 
 class LayerNormMLP(_Fp8Module):
@@ -239,12 +295,20 @@ class LayerNormMLP(_Fp8Module):
         _check_active("LayerNormMLP")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
+        first, drop = self._take_prefetched(is_first_microbatch, recipe)
         if isinstance(recipe, MXFP8BlockScaling):
-            return fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g,
-                                             add_residual, self._wcache, is_first_microbatch)
-        self._apply_extra_state(recipe, inp.device)
-        return fn.LayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self._meta,
-                                       recipe, self.eps, g, add_residual, self._wcache, is_first_microbatch)
+            out = fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g,
+                                            add_residual, self._wcache, first)
+        else:
+            self._apply_extra_state(recipe, inp.device)
+            out = fn.LayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self._meta,
+                                          recipe, self.eps, g, add_residual, self._wcache, first)
+        if drop:
+            self._wcache.clear()
+        return out
+
+    def _prefetch_targets(self):
+        return [("w1", self.fc1_weight, 1), ("w2", self.fc2_weight, 4)]
 
 
 # ------------------------------------------------------------------------------------------ attention shell

@@ -235,3 +235,39 @@ def test_flush_exchanges_amax_so_every_rank_derives_the_same_scales(tmp_path):
     assert r0["reduced"] == r1["reduced"] == [f32div(448.0, 2.0), f32div(448.0, 5.0), 1.0]       # MAX over ranks; an unused slot keeps scale 1
     assert r0["local"] == [448.0, f32div(448.0, 5.0), 1.0] and r1["local"] == [f32div(448.0, 2.0), f32div(448.0, 4.0), 1.0]   # reduce_amax=False stays local
     assert r0["calls"] == r1["calls"] == [3, 3]
+
+
+# ------------------------------------------------------------------------------------------------ weight prefetch, delayed scaling
+def test_prefetch_casts_with_the_slots_and_keys_the_forward_uses(host_only, monkeypatch):
+    """modules.prefetch_weights (prefetch.WeightPrefetcher) under DelayedScaling: the weight of a Linear / LayerNormLinear sits in
+    forward slot 1 of its module, fc1 / fc2 of a LayerNormMLP in slots 1 and 4 (functional.LinearFn / LayerNormMLPFn), cached under
+    (name, recipe key) with a snapshot of the scale_inv they were cast with — what `is_first_microbatch=False` then reuses."""
+    from llm_fp8_b200 import ops
+    seen = []
+
+    def fake_quantize(x, fmt, pool, slot):
+        seen.append((tuple(x.shape), fmt, pool, slot))
+        return ops.QTensor(torch.zeros(x.shape, dtype=torch.uint8), fmt, pool.scale_inv, slot)
+
+    monkeypatch.setattr(ops, "quantize", fake_quantize)
+    r = DelayedScaling(fp8_format=Format.HYBRID, amax_history_len=4)
+    lin = te.Linear(16, 24, bias=False, params_dtype=torch.bfloat16, device="cpu")
+    qkv = te.LayerNormLinear(16, 32, eps=1e-5, bias=False, normalization="RMSNorm", parameters_split={"query": 16, "key": 8, "value": 8},
+                             params_dtype=torch.bfloat16, device="cpu")
+    mlp = te.LayerNormMLP(16, 32, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16, device="cpu")
+    for m in (lin, qkv, mlp):
+        m.prefetch_weights(r, CPU)
+    pf = fp8.get_pool(r, True, CPU)
+    s_lin, s_qkv, s_mlp = lin._meta.get(r, CPU), qkv._meta.get(r, CPU), mlp._meta.get(r, CPU)
+    assert [(s, f, p is pf, sl) for s, f, p, sl in seen] == [((24, 16), 0, True, s_lin["f0"] + 1), ((32, 16), 0, True, s_qkv["f0"] + 1),
+                                                             ((64, 16), 0, True, s_mlp["f0"] + 1), ((16, 32), 0, True, s_mlp["f0"] + 4)]
+    assert set(lin._wcache) == {("w", r.key())} and set(qkv._wcache) == {("w", r.key())} and set(mlp._wcache) == {("w1", r.key()), ("w2", r.key())}
+    kept = mlp._wcache[("w2", r.key())]
+    assert kept.scale_inv.numel() == 1 and kept.scale_inv.data_ptr() != pf.scale_inv.data_ptr()      # a snapshot, not the live slot
+    assert qkv.query_weight.data_ptr() == qkv._joined.data_ptr()                                     # cast from the joined buffer, in place
+    # the consuming side: a prefetched module runs its forward with `first=False` once, then lets the copies go
+    mlp._prefetched = True
+    assert mlp._take_prefetched(None, r) == (False, True) and not mlp._prefetched
+    assert mlp._take_prefetched(None, r) == (None, False)
+    mlp._prefetched = True
+    assert mlp._take_prefetched(True, r) == (True, False)          # a caller that manages micro-batches itself keeps control

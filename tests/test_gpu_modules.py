@@ -334,3 +334,47 @@ def test_wgrad_side_stream_matches_main_stream():
     for a, b in zip(base, side):
         for ta, tb in zip(a, b):
             assert torch.equal(ta, tb)
+
+
+@pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
+                    reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
+@pytest.mark.parametrize("scenario", ["mxfp8", "default"])
+def test_weight_prefetch_matches_inline_casts(scenario):
+    """prefetch.WeightPrefetcher: layer i+1's weight casts issued on a side stream when layer i starts.  Same kernels, same scale and
+    amax slots -> outputs, input gradients and weight gradients must be bit-identical to the inline run over several steps, with the
+    weights changing between steps (a missing stream dependency would show up as a stale copy); the delayed-scaling state must end
+    up identical too."""
+    import llm_fp8_b200 as te
+    from llm_fp8_b200 import fp8
+    from llm_fp8_b200.layer import LinearPathStack
+    from llm_fp8_b200.prefetch import WeightPrefetcher
+
+    def run(prefetch):
+        te.reset_fp8_state()
+        model = LinearPathStack("llama-3.2-1b", scenario, 5, device="cuda")
+        pf = WeightPrefetcher(model.layers) if prefetch else None
+        out = []
+        for step in range(4):
+            x = rnd((2, 256, model.H), 80 + step).cuda().requires_grad_(True)
+            for p in model.parameters():
+                p.grad = None
+            y = model(x)
+            y.float().pow(2).mean().backward()
+            out.append([y.detach().clone(), x.grad.clone()] + [p.grad.clone() for p in model.parameters()])
+            with torch.no_grad():                     # an optimizer step's worth of change, on the main stream
+                for p in model.parameters():
+                    p.add_(p.grad, alpha=-1e-3)
+        torch.cuda.synchronize()
+        state = [(p.scale[:p.used].clone(), p.amax_history[:, :p.used].clone()) for p in fp8.all_pools()]
+        if pf is not None:
+            assert (pf.issued, pf.consumed) == (9, 9)     # steps 2-4, layers 2-4
+        return out, state
+
+    base, st0 = run(False)
+    pre, st1 = run(True)
+    for a, b in zip(base, pre):
+        for ta, tb in zip(a, b):
+            assert torch.equal(ta, tb)
+    assert len(st0) == len(st1)
+    for (s0, h0), (s1, h1) in zip(st0, st1):
+        assert torch.equal(s0, s1) and torch.equal(h0, h1)

@@ -20,6 +20,8 @@ LLMFP8_EXPERIMENTAL=1 timeout 300 python -m pytest tests/test_gpu_quantize.py te
 echo "exp fused act exit $?  $(tail -1 gpurun_out/r02_exp_fused_act.log)" >> $S
 LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_modules.py -q -m gpu -p no:cacheprovider -k "wgrad_side_stream" > gpurun_out/r02_exp_wgrad_stream.log 2>&1
 echo "exp wgrad stream exit $?  $(tail -1 gpurun_out/r02_exp_wgrad_stream.log)" >> $S
+LLMFP8_EXPERIMENTAL=1 timeout 200 python -m pytest tests/test_gpu_modules.py -q -m gpu -p no:cacheprovider -k "weight_prefetch" > gpurun_out/r02_exp_wprefetch.log 2>&1
+echo "exp weight prefetch exit $?  $(tail -1 gpurun_out/r02_exp_wprefetch.log)" >> $S
 
 # the programmatic-dependent-launch build: the whole GPU suite on it, then its bench line
 LLMFP8_PDL=1 timeout 400 python -m pytest tests/ -x -q -m gpu -p no:cacheprovider > gpurun_out/r02_pytest_gpu_pdl.log 2>&1
@@ -31,6 +33,8 @@ LLMFP8_WGRAD_STREAM=1 $B > gpurun_out/r02_bench_mxfp8_wgradstream.json 2> gpurun
 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_resovl.json 2> gpurun_out/r02_bench_mxfp8_resovl.err; echo "bench mxfp8 +RES/OVL exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 $B > gpurun_out/r02_bench_mxfp8_fusedact.json 2> gpurun_out/r02_bench_mxfp8_fusedact.err; echo "bench mxfp8 +fused act exit $?" >> $S
 LLMFP8_MX_FUSED_ACT=1 LLMFP8_WGRAD_STREAM=1 LLMFP8_MX_EPILOGUE_RESIDUAL=1 LLMFP8_GEMM_DEBUG=32 $B > gpurun_out/r02_bench_mxfp8_all.json 2> gpurun_out/r02_bench_mxfp8_all.err; echo "bench mxfp8 all experiments exit $?" >> $S
+LLMFP8_WEIGHT_PREFETCH=1 $B > gpurun_out/r02_bench_mxfp8_wprefetch.json 2> gpurun_out/r02_bench_mxfp8_wprefetch.err; echo "bench mxfp8 +weight prefetch exit $?" >> $S
+LLMFP8_WEIGHT_PREFETCH=1 $B --scenario default > gpurun_out/r02_bench_default_wprefetch.json 2> gpurun_out/r02_bench_default_wprefetch.err; echo "bench default +weight prefetch exit $?" >> $S
 LLMFP8_PDL=1 $B > gpurun_out/r02_bench_mxfp8_pdl.json 2> gpurun_out/r02_bench_mxfp8_pdl.err; echo "bench mxfp8 PDL build exit $?" >> $S
 LLMFP8_PDL=1 $B --scenario default > gpurun_out/r02_bench_default_pdl.json 2> gpurun_out/r02_bench_default_pdl.err; echo "bench default PDL build exit $?" >> $S
 LLMFP8_JOIN_SPLIT_WEIGHTS=0 $B > gpurun_out/r02_bench_mxfp8_catweights.json 2> gpurun_out/r02_bench_mxfp8_catweights.err; echo "bench mxfp8 torch.cat qkv weights exit $?" >> $S
