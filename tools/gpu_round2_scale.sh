@@ -31,6 +31,7 @@ run cg1 LLMFP8_GEMM_FORCE_CG=1                         # single-CTA GEMM tiles: 
 run bucket256 LLMFP8_GRAD_BUCKET_MB=256                # coalesced gradient groups: ~2 NCCL launches per decoder layer instead of 6
 run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
 run fusedact LLMFP8_MX_FUSED_ACT=1
+run wprefetch LLMFP8_WEIGHT_PREFETCH=1
 # in-switch gradient reduce (own multimem kernel, csrc/nvls_reduce.cu) — only after tools/gpu_nvls2.sh passed on two GPUs
 run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
