@@ -11,6 +11,11 @@ path is the validated one.  Same kernels, same scale / amax slots, same bytes: r
 Layers 0 and 1 of every step cast inline: delayed scaling updates its pools when the first layer of a step runs, and a cast issued
 before that would use last step's scales.  A layer whose recipe is not known yet (first step) or whose prefetch was not issued casts
 inline as well — a miss is always just the default behaviour.
+
+A prefetched copy is only used if nothing can have changed the weights since it was cast: it must come from the same pass over the
+layers (a pass starts whenever layer 0 runs) and the parameters' version counters must be where they were (optimizer steps are
+in-place updates).  Copies issued by a re-run of a layer outside the normal order (activation recomputation in backward) therefore
+never reach the next step; they are dropped.
 """
 from __future__ import annotations
 
@@ -28,7 +33,8 @@ class WeightPrefetcher:
         self._mods: List[List[_Fp8Module]] = [[m for m in layer.modules() if isinstance(m, _Fp8Module)] for layer in self.layers]
         self._ready = {}                 # layer index -> CUDA event (or True on CPU) of an issued, not yet consumed prefetch
         self._side = {}                  # device index -> side stream
-        self.issued = self.consumed = 0
+        self.issued = self.consumed = self.rejected = 0
+        self._pass = 0
         self._handles = [layer.register_forward_pre_hook(functools.partial(self._pre, i)) for i, layer in enumerate(self.layers)]
 
     def remove(self):
@@ -38,15 +44,23 @@ class WeightPrefetcher:
 
     # -- forward pre-hook of layer idx: take what was prefetched for it, then start the next layer's casts
     def _pre(self, idx, module, args):
-        ev = self._ready.pop(idx, None)
-        if ev is not None:
+        if idx == 0:
+            self._pass += 1
+        entry = self._ready.pop(idx, None)
+        if entry is not None:
+            ev, issued_in, versions = entry
             mods = self._mods[idx]
             if ev is not True:
-                torch.cuda.current_stream(ev_device(mods)).wait_event(ev)
-            for m in mods:
-                if m._wcache:
-                    m._prefetched = True
-            self.consumed += 1
+                torch.cuda.current_stream(ev_device(mods)).wait_event(ev)      # also orders the release of rejected copies
+            if issued_in == self._pass and versions == _versions(mods):
+                for m in mods:
+                    if m._wcache:
+                        m._prefetched = True
+                self.consumed += 1
+            else:
+                for m in mods:
+                    m._wcache.clear()
+                self.rejected += 1
         if idx >= 1 and idx + 1 < len(self.layers):
             self._issue(idx + 1)
 
@@ -59,7 +73,7 @@ class WeightPrefetcher:
         if dev.type != "cuda":           # CPU wiring tests: no streams, same bookkeeping
             for m in mods:
                 m.prefetch_weights(m._last_recipe, dev, need_col)
-            self._ready[j] = True
+            self._ready[j] = (True, self._pass, _versions(self._mods[j]))
             self.issued += 1
             return
         main = torch.cuda.current_stream(dev)
@@ -75,8 +89,12 @@ class WeightPrefetcher:
         for m in mods:
             for t in m._wcache_tensors():
                 t.record_stream(main)    # allocated from the side stream's pool, consumed (and freed) on the main stream
-        self._ready[j] = ev
+        self._ready[j] = (ev, self._pass, _versions(self._mods[j]))
         self.issued += 1
+
+
+def _versions(mods):
+    return [p._version for m in mods for p in m.parameters(recurse=False)]
 
 
 def ev_device(mods) -> torch.device:

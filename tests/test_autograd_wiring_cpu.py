@@ -300,3 +300,59 @@ def test_prefetched_copies_are_cast_before_the_previous_layer_runs(fake_ops):
             assert fake_ops.calls[start[2] - 4:start[2]] == ["mxq"] * 4
     assert (pf.issued, pf.consumed) == (2, 2)
     pf.remove()
+
+
+def test_prefetched_copies_never_cross_a_weight_update_or_a_pass(fake_ops):
+    """a copy cast before the weights changed (optimizer step: in-place update) or left over from another pass over the layers
+    (a layer re-run out of order, as activation recomputation does) is never used: it is either replaced by the fresh prefetch of the
+    next pass or dropped, and the layer casts inline"""
+    from llm_fp8_b200.prefetch import WeightPrefetcher
+    layers = torch.nn.ModuleList(_layer(True) for _ in range(4))
+    pf = WeightPrefetcher(layers)
+    x = torch.randn(1, 4, H, generator=torch.Generator().manual_seed(2)).bfloat16()
+
+    def forward(mods):
+        y = x
+        with torch.no_grad():
+            for layer in mods:
+                y = layer(y)
+        return y
+
+    def plain_result(scale):
+        plain = torch.nn.ModuleList(_layer(True) for _ in range(4))
+        with torch.no_grad():
+            for p in plain.parameters():
+                p.mul_(scale)
+        return forward(plain)
+
+    forward(layers)                                     # pass 1: recipes become known
+    y_ref = forward(layers)                             # pass 2: layers 2, 3 prefetched and consumed
+    assert (pf.issued, pf.consumed, pf.rejected) == (2, 2, 0)
+    # a re-run of layer 2 alone leaves a prefetch for layer 3 that nobody takes in this pass ...
+    forward([layers[2]])
+    assert 3 in pf._ready
+    with torch.no_grad():                               # ... then the weights move
+        for p in layers.parameters():
+            p.mul_(1.5)
+    y_new = forward(layers)                             # pass 3: the left-over is replaced by a fresh cast before layer 3 runs
+    assert torch.equal(y_new, plain_result(1.5)) and not torch.equal(y_new, y_ref)
+    # a left-over from an earlier pass that is NOT re-issued (layer 3 entered without its predecessor): dropped
+    forward([layers[2]])                                # issues layer 3's casts in pass 3
+    forward([layers[0]])                                # a new pass begins
+    before = pf.rejected
+    h = forward(layers[:3])[0:1]                        # (this pass re-issues and layer 3 is not run: entry of pass 5 stays)
+    forward([layers[0]])                                # pass 6
+    with torch.no_grad():
+        y3 = layers[3](h)
+    assert pf.rejected == before + 1
+    # same pass, but a weight updated between issue and use (version counter moved): dropped as well
+    with torch.no_grad():
+        h = forward(layers[:3])                         # layer 2's pre-hook issued layer 3's casts
+        layers[3].proj.weight.mul_(2.0)
+        before = pf.rejected
+        y_upd = layers[3](h)
+    assert pf.rejected == before + 1
+    with torch.no_grad():
+        y_inline = layers[3](h)                         # no prefetch pending: inline casts of the updated weights
+    assert torch.equal(y_upd, y_inline)
+    assert all(not m._wcache and not m._prefetched for mods in pf._mods for m in mods)
