@@ -6,8 +6,12 @@ N=${1:-8}
 mkdir -p gpurun_out
 S=gpurun_out/r02_scale_summary.txt
 : > $S
+# Every line costs ~2 min x 8 GPUs = 16 GPU-minutes of the round's 180: run a SHORT list.  LINES="tag tag ..." selects (default below);
+# LINES=all runs everything (only with budget to spare).
+LINES=${LINES:-"base nvls32 wgradstream bucket256"}
 run() {  # tag, env assignments...
   tag=$1; shift
+  case " $LINES " in *" all "*|*" $tag "*) ;; *) return 0;; esac
   env "$@" LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29511 \
       bench.py --gpus $N --steps 4 --warmup 3 --scenario mxfp8 --no-roofline > gpurun_out/r02_scale_${tag}_n$N.json 2> gpurun_out/r02_scale_${tag}_n$N.err
   echo "$tag n=$N exit $?" >> $S
@@ -37,6 +41,7 @@ run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
 run nvls96 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=96
 # whole data-parallel step (collectives included) replayed from one CUDA graph: no host launch jitter between ranks
+case " $LINES " in *" all "*|*" graphdp "*) ;; *) cat $S; exit 0;; esac
 tag=graphdp; env LLMFP8_GRAPH_DP=1 LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
     bench.py --gpus $N --steps 4 --warmup 3 --scenario mxfp8 --no-roofline --graph 1 > gpurun_out/r02_scale_${tag}_n$N.json 2> gpurun_out/r02_scale_${tag}_n$N.err
 echo "$tag n=$N exit $?  $(tail -c 300 gpurun_out/r02_scale_${tag}_n$N.json | tr -d '\n' | grep -o '"ms_per_step": [0-9.]*')" >> $S
