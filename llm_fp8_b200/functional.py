@@ -101,9 +101,14 @@ WGRAD_SIDE_STREAM = os.environ.get("LLMFP8_WGRAD_STREAM", "0") == "1"
 _side_streams = {}
 
 
+def _streams_on(device: torch.device) -> bool:
+    """side-stream scheduling applies (tests/_streams.py replaces this together with torch.cuda's stream objects to check the ordering)"""
+    return device.type == "cuda"
+
+
 class _SideWgrad:
     def __init__(self, device: torch.device):
-        self.on = WGRAD_SIDE_STREAM and device.type == "cuda"
+        self.on = WGRAD_SIDE_STREAM and _streams_on(device)
         self.outs = []
         if self.on:
             idx = device.index if device.index is not None else torch.cuda.current_device()

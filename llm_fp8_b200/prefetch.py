@@ -24,6 +24,7 @@ from typing import List, Sequence
 
 import torch
 
+from . import functional as fn
 from .modules import _Fp8Module
 
 
@@ -70,7 +71,7 @@ class WeightPrefetcher:
             return
         dev = ev_device(mods)
         need_col = torch.is_grad_enabled()
-        if dev.type != "cuda":           # CPU wiring tests: no streams, same bookkeeping
+        if not fn._streams_on(dev):      # CPU wiring tests: no streams, same bookkeeping
             for m in mods:
                 m.prefetch_weights(m._last_recipe, dev, need_col)
             self._ready[j] = (True, self._pass, _versions(self._mods[j]))
