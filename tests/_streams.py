@@ -76,19 +76,23 @@ _STATE = {"current": None, "main": None}
 class Tracker:
     def __init__(self):
         self.launches = []                   # (name, stream id, index, clock, reads, writes)
-        self._keep = []                      # every tensor seen stays alive: the CPU allocator must not hand its address to a new one
+        self._keep = []                      # every storage seen stays alive (the CPU allocator must not hand its address to a new
+                                             # tensor) — the storage, not the tensor: autograd adopts a gradient only if it is its sole owner
 
     @staticmethod
     def _keys(tensors):
         out = set()
         for t in tensors:
-            if isinstance(t, torch.Tensor) and t.numel():
-                out.add(t.untyped_storage().data_ptr())
+            if isinstance(t, torch.Tensor):
+                if t.numel():
+                    out.add(t.untyped_storage().data_ptr())
+            elif t is not None:
+                out.add(t)                   # any hashable names a finer-grained resource (one slot of a pool, ...)
         return out
 
     def op(self, name, reads, writes):
         reads, writes = list(reads), list(writes)
-        self._keep += reads + writes
+        self._keep += [t.untyped_storage() for t in reads + writes if isinstance(t, torch.Tensor)]
         sid, idx, clock = _STATE["current"].launch()
         self.launches.append((name, sid, idx, clock, self._keys(reads), self._keys(writes)))
 
