@@ -356,3 +356,45 @@ def test_prefetched_copies_never_cross_a_weight_update_or_a_pass(fake_ops):
         y_inline = layers[3](h)                         # no prefetch pending: inline casts of the updated weights
     assert torch.equal(y_upd, y_inline)
     assert all(not m._wcache and not m._prefetched for mods in pf._mods for m in mods)
+
+
+@pytest.mark.parametrize("ffn", [128, 96])
+def test_fused_activation_branch_is_wired_like_the_two_kernel_sequence(fake_ops, monkeypatch, ffn):
+    """functional.MX_FUSED_ACT (LLMFP8_MX_FUSED_ACT=1): SwiGLU / dSwiGLU fused with the block quantiser (ops.mx_swiglu_quantize /
+    ops.mx_dswiglu_quantize) must see the same operands and hand on the same tensors as swiglu_bf16 -> mx_quantize and
+    dswiglu_bf16 -> mx_quantize; an ffn size that is not a multiple of 128 keeps the two-kernel backward (the C ABI's contract)."""
+    used = []
+
+    def mx_swiglu_quantize(fc1, rowwise=True, colwise=True):
+        used.append("fwd")
+        return _FakeOps.mx_quantize(_FakeOps.swiglu_bf16(fc1), rowwise, colwise)
+
+    def mx_dswiglu_quantize(da, fc1, rowwise=True, colwise=True, want_dbias=True):
+        used.append("bwd")
+        d, db = _FakeOps.dswiglu_bf16(da, fc1, want_dbias)
+        return _FakeOps.mx_quantize(d, rowwise, colwise), db
+
+    monkeypatch.setattr(ops, "mx_swiglu_quantize", mx_swiglu_quantize, raising=False)
+    monkeypatch.setattr(ops, "mx_dswiglu_quantize", mx_dswiglu_quantize, raising=False)
+    torch.manual_seed(2)
+    r = te.MXFP8BlockScaling(fp8_format=te.Format.E4M3)
+    mlp = te.LayerNormMLP(H, ffn, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16)
+    with torch.no_grad():
+        mlp.fc1_bias.normal_(0, 0.05)
+    x = torch.randn(6, H, generator=torch.Generator().manual_seed(3)).bfloat16()
+
+    def run(flag):
+        monkeypatch.setattr(fn, "MX_FUSED_ACT", flag)
+        mlp.zero_grad()
+        h = x.clone().requires_grad_(True)
+        with te.fp8_autocast(enabled=True, fp8_recipe=r):
+            y = mlp(h)
+        y.float().square().mean().backward()
+        return [y.detach().clone(), h.grad.clone()] + [p.grad.clone() for p in mlp.parameters()]
+
+    base = run(False)
+    assert used == []
+    fused = run(True)
+    assert used == (["fwd", "bwd"] if ffn % 128 == 0 else ["fwd"])
+    for a, b in zip(base, fused):
+        assert torch.equal(a, b)
