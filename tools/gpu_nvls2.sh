@@ -7,6 +7,9 @@ mkdir -p gpurun_out
 LLMFP8_EXPERIMENTAL=1 timeout 280 python -m pytest tests/test_gpu_comm.py -x -q -m gpu -p no:cacheprovider -k nvls > gpurun_out/r02_test_nvls2.log 2>&1
 rc=$?; echo "test_nvls exit $rc"; tail -25 gpurun_out/r02_test_nvls2.log
 [ $rc -ne 0 ] && exit $rc
+LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
+    tools/nvls_bench.py --out gpurun_out/r02_nvls_bench_n2.jsonl > gpurun_out/r02_nvls_bench_n2.log 2>&1
+echo "nvls_bench exit $?"; tail -20 gpurun_out/r02_nvls_bench_n2.log
 for mode in 0 1; do
   LLMFP8_NVLS_REDUCE=$mode LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
       --master-port 29521 bench.py --gpus 2 --steps 4 --warmup 3 --scenario mxfp8 --no-roofline > gpurun_out/r02_nvls${mode}_n2.json 2> gpurun_out/r02_nvls${mode}_n2.err
