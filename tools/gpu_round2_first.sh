@@ -1,6 +1,8 @@
 #!/bin/bash
-# First GPU call of the next round (one B200, ~12 min of box time): everything that was written after the round-1 GPU budget ran out.
-#   /usr/local/graft/bin/gpurun --timeout 1200 -- 'bash tools/gpu_round2_first.sh'
+# First GPU call of the next round (one B200, 25-30 min of box time: 16 bench lines of ~1 min, two GPU suites, ncu): everything that was
+# written after the round-1 GPU budget ran out.  Every step has its own timeout; results are written as they come, so a cut-off call
+# still leaves gpurun_out/r02_* behind.
+#   /usr/local/graft/bin/gpurun --timeout 2400 -- 'bash tools/gpu_round2_first.sh'
 # 1. full GPU suite on the default tree (overlapped-accumulator MX GEMM is the default since d2c7555);
 # 2. the gated experiments' own tests (LLMFP8_EXPERIMENTAL=1): RES + OVL epilogue (debug bit 5), SwiGLU/dSwiGLU fused with the MX
 #    quantiser (LLMFP8_MX_FUSED_ACT), wgrad side stream (LLMFP8_WGRAD_STREAM);
