@@ -20,7 +20,7 @@ namespace llmfp8 {
 
 namespace {
 
-// 128 threads x 40 registers = 5 K registers and no shared memory: such a CTA fits on an SM BESIDE a resident GEMM CTA (352 threads x <= 168
+// 128 threads x <= 40 registers = 5 K registers and no shared memory of its own: such a CTA fits on an SM BESIDE a resident GEMM CTA (352 threads x <= 168
 // registers = 59 K of the 64 K), so the reduce does not wait for GEMM CTAs to drain and takes no SM away from them — only issue slots.
 constexpr int kThreads = 128;
 constexpr int kUnroll = 4;
@@ -85,11 +85,8 @@ __global__ void __launch_bounds__(kThreads) nvls_allreduce_sum_bf16_kernel(uint4
                                                                            long long timeout_ns) {
     pdl_wait();
     pdl_launch_dependents();
-    __shared__ int alive;
-    if (threadIdx.x == 0) alive = 1;
-    __syncthreads();
-    if (!meet_ranks<false>(pads, rank, world, timeout_ns)) alive = 0;
-    __syncthreads();
+    // CTA-wide verdict without shared memory (the kernel's footprint beside a GEMM CTA is registers and the 1 KB the system reserves)
+    const int alive = __syncthreads_and(meet_ranks<false>(pads, rank, world, timeout_ns) ? 1 : 0);
     if (alive) {
         const int64_t per = (nvec + world - 1) / world;
         const int64_t lo = per * rank;
