@@ -170,6 +170,14 @@ int llmfp8_nccl_destroy(void* comm);
 int llmfp8_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world,
                                    int max_ctas, int timeout_ms, void* stream);
 int llmfp8_nvls_grid(int64_t numel, int world, int max_ctas);
+/* llmfp8_nccl_allreduce_max_f32 + llmfp8_amax_scale_update in ONE launch, for an amax history [history_len, num_tensors] that every rank
+ * keeps in symmetric, multicast-mapped memory: each slot's row-0 amax is maximised over ranks in the switch (multimem.ld_reduce.max.u32 on
+ * the bit patterns of the non-negative floats) and the scale / scale_inv / history roll of llmfp8_amax_scale_update follow in the same
+ * kernel — what TE does at fp8_autocast exit (te_llama.py:76-80) with an NCCL collective and a separate kernel.  row0_multicast: multicast
+ * address of the history's row 0; signal pads, timeout and the not-yet-run-on-hardware status as above (opt-in: LLMFP8_NVLS_AMAX=1). */
+int llmfp8_nvls_amax_scale_update(float* amax_history, const void* row0_multicast, float* scale, float* scale_inv, const float* fmax, int history_len,
+                                  int num_tensors, int margin, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world, int timeout_ms,
+                                  void* stream);
 int llmfp8_nvls_timeouts(unsigned int* count);
 
 #ifdef __cplusplus

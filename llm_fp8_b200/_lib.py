@@ -54,6 +54,7 @@ _PROTOTYPES = {
     "llmfp8_nccl_destroy": [vp],
     "llmfp8_nvls_allreduce_sum_bf16": [vp, i64, vp, i64, i32, i32, i32, i32, vp],
     "llmfp8_nvls_grid": [i64, i32, i32],
+    "llmfp8_nvls_amax_scale_update": [vp, vp, vp, vp, vp, i32, i32, i32, vp, i64, i32, i32, i32, vp],
     "llmfp8_nvls_timeouts": [vp],
     "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }

@@ -116,6 +116,7 @@ int comm_allreduce_sum_bf16(void*, void*, int64_t, cudaStream_t);
 int comm_destroy(void*);
 int launch_nvls_allreduce_sum_bf16(void*, int64_t, void* const*, int64_t, int, int, int, int, cudaStream_t);
 int nvls_grid(int64_t, int, int);
+int launch_nvls_amax_scale_update(float*, const void*, float*, float*, const float*, int, int, int, void* const*, int64_t, int, int, int, cudaStream_t);
 int nvls_timeouts(unsigned int*);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
@@ -237,6 +238,12 @@ int llmfp8_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* con
     return launch_nvls_allreduce_sum_bf16(multicast_ptr, numel, signal_pads, signal_pad_bytes, rank, world, max_ctas, timeout_ms, S(stream));
 }
 int llmfp8_nvls_grid(int64_t numel, int world, int max_ctas) { return nvls_grid(numel, world, max_ctas); }
+int llmfp8_nvls_amax_scale_update(float* amax_history, const void* row0_multicast, float* scale, float* scale_inv, const float* fmax, int history_len,
+                                  int num_tensors, int margin, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world, int timeout_ms,
+                                  void* stream) {
+    return launch_nvls_amax_scale_update(amax_history, row0_multicast, scale, scale_inv, fmax, history_len, num_tensors, margin, signal_pads,
+                                         signal_pad_bytes, rank, world, timeout_ms, S(stream));
+}
 int llmfp8_nvls_timeouts(unsigned int* count) { return nvls_timeouts(count); }
 
 }  // extern "C"

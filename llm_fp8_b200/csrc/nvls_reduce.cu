@@ -13,6 +13,11 @@
 // A rank that waits longer than `timeout_ns` (%globaltimer) gives up, counts it in g_nvls_timeouts (llmfp8_nvls_timeouts) and leaves — the
 // result is then wrong and the host must raise, but the GPU is never left spinning.
 //
+// The same file holds the other exchange of the path (exchange 1): the delayed-scaling amax MAX all-reduce fused with the scale update it
+// feeds (K4) — nvls_amax_scale_update_kernel: meet, one multimem.ld_reduce.max.u32 per fp8 tensor slot (non-negative floats order like
+// their bit patterns), meet again (every rank has read every row 0 before any rank rolls its history), then the K4 arithmetic of
+// quantize.cu on the reduced value.  One launch instead of an NCCL collective + a kernel, twice per step (LLMFP8_NVLS_AMAX=1).
+//
 // STATUS: compiled for sm_100a; written after the round-1 GPU budget was spent, NOT yet run on hardware -> opt-in (LLMFP8_NVLS_REDUCE=1).
 #include "common.cuh"
 
@@ -106,6 +111,49 @@ __global__ void __launch_bounds__(kThreads) nvls_allreduce_sum_bf16_kernel(uint4
     if (alive) meet_ranks<true>(pads, rank, world, timeout_ns);
 }
 
+__device__ __forceinline__ uint32_t multimem_max_u32(const void* mc) {
+    uint32_t v;
+    asm volatile("multimem.ld_reduce.relaxed.sys.global.max.u32 %0, [%1];" : "=r"(v) : "l"(mc) : "memory");
+    return v;
+}
+
+// hist: this rank's amax history [L, T] row-major (row 0 = the amaxes recorded since the last update), symmetric across ranks;
+// row0_mc: multicast address of row 0.  After the launch every rank holds the same scale / scale_inv and a rolled history whose newest
+// entry is the maximum over ranks.  The update itself restates amax_scale_update_kernel (quantize.cu; oracle: orc_amax_scale_update)
+// with the reduced value in place of the local row 0 — kept apart so that the validated kernel's binary does not change.
+__global__ void __launch_bounds__(kThreads) nvls_amax_scale_update_kernel(float* __restrict__ hist, const uint32_t* row0_mc, float* __restrict__ scale,
+                                                                          float* __restrict__ scale_inv, const float* __restrict__ fmax, int L, int T,
+                                                                          float margin_div, uint32_t* const* pads, int rank, int world,
+                                                                          long long timeout_ns) {
+    pdl_wait();
+    pdl_launch_dependents();
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    int alive = __syncthreads_and(meet_ranks<false>(pads, rank, world, timeout_ns) ? 1 : 0);
+    uint32_t m = 0;
+    if (alive && t < T) m = multimem_max_u32(row0_mc + t);
+    __syncthreads();
+    if (alive) alive = __syncthreads_and(meet_ranks<true>(pads, rank, world, timeout_ns) ? 1 : 0);     // nobody rolls before everybody has read
+    if (!alive || t >= T) return;                      // timed out: state untouched, the host sees llmfp8_nvls_timeouts != 0
+    const float first = __uint_as_float(m);
+    float am = 0.f;
+    bool nonfinite = false;
+    for (int l = 0; l < L; l++) {
+        const float h = l == 0 ? first : hist[l * T + t];
+        nonfinite |= !isfinite(h);
+        am = (h > am) ? h : am;
+        if (l + 1 < L) hist[l * T + t] = hist[(l + 1) * T + t];
+    }
+    hist[(L - 1) * T + t] = first;
+    hist[t] = 0.f;
+    const float old = scale[t];
+    float sf = __fdiv_rn(__fdiv_rn(fmax[t], am), margin_div);
+    if (!(am > 0.f)) sf = old;
+    if (nonfinite) sf = old;
+    if (isinf(sf)) sf = 3.402823466e38f;
+    scale[t] = sf;
+    scale_inv[t] = __fdiv_rn(1.0f, sf);
+}
+
 }  // namespace
 
 int nvls_grid(int64_t numel, int world, int max_ctas) {
@@ -134,6 +182,26 @@ int launch_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* con
     LLMFP8_LAUNCH(nvls_allreduce_sum_bf16_kernel, dim3(ctas), dim3(kThreads), 0, stream, static_cast<uint4*>(multicast_ptr), numel / 8,
                   reinterpret_cast<uint32_t* const*>(signal_pads), rank, world, timeout_ns);
     LLMFP8_LAUNCH_CHECK("nvls_allreduce_sum_bf16");
+    return 0;
+}
+
+int launch_nvls_amax_scale_update(float* hist, const void* row0_multicast, float* scale, float* scale_inv, const float* fmax, int L, int T, int margin,
+                                  void* const* signal_pads, int64_t pad_bytes, int rank, int world, int timeout_ms, cudaStream_t stream) {
+    LLMFP8_REQUIRE(L >= 1 && T >= 0, "nvls_amax_scale_update: bad sizes L=%d T=%d", L, T);
+    LLMFP8_REQUIRE(margin >= 0 && margin < 120, "nvls_amax_scale_update: bad margin %d", margin);
+    LLMFP8_REQUIRE(world >= 2 && world <= kMaxWorld && rank >= 0 && rank < world, "nvls_amax_scale_update: bad rank %d of %d", rank, world);
+    if (T == 0) return 0;
+    LLMFP8_REQUIRE(hist && scale && scale_inv && fmax, "nvls_amax_scale_update: null state pointer");
+    LLMFP8_REQUIRE(row0_multicast != nullptr && (reinterpret_cast<uintptr_t>(row0_multicast) & 3) == 0,
+                   "nvls_amax_scale_update: the multicast address of row 0 must be non-null and 4-byte aligned");
+    LLMFP8_REQUIRE(signal_pads != nullptr, "nvls_amax_scale_update: null signal pads");
+    const int ctas = (T + kThreads - 1) / kThreads;
+    LLMFP8_REQUIRE(static_cast<int64_t>(ctas) * world * 4 <= pad_bytes, "nvls_amax_scale_update: %d CTAs x %d ranks need %lld bytes of signal pad, have %lld",
+                   ctas, world, (long long)ctas * world * 4, (long long)pad_bytes);
+    const long long timeout_ns = timeout_ms == 0 ? 10000000000LL : (timeout_ms < 0 ? 0LL : static_cast<long long>(timeout_ms) * 1000000LL);
+    LLMFP8_LAUNCH(nvls_amax_scale_update_kernel, dim3(ctas), dim3(kThreads), 0, stream, hist, static_cast<const uint32_t*>(row0_multicast), scale, scale_inv,
+                  fmax, L, T, ldexpf(1.0f, margin), reinterpret_cast<uint32_t* const*>(signal_pads), rank, world, timeout_ns);
+    LLMFP8_LAUNCH_CHECK("nvls_amax_scale_update");
     return 0;
 }
 

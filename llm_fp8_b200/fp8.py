@@ -14,6 +14,7 @@ computed from amaxes of steps < t), with 2 collectives per step instead of 2 per
 """
 from __future__ import annotations
 
+import os
 import threading
 from contextlib import contextmanager
 from typing import Dict, List, Optional
@@ -24,6 +25,11 @@ from . import _lib
 from .recipe import DelayedScaling, Format, MXFP8BlockScaling, Recipe, get_default_fp8_recipe
 
 _POOL_CAP = 4096
+# LLMFP8_NVLS_AMAX=1 (opt-in; not yet run on hardware): the amax history of every pool lives in symmetric, multicast-mapped memory and
+# flush() is ONE launch — in-switch MAX over the data-parallel ranks + the scale update (csrc/nvls_reduce.cu: nvls_amax_scale_update_kernel)
+# — instead of an NCCL all-reduce followed by K4.  Pools are created in the same order on every rank (first use in forward), which is
+# what the collective set-up needs.
+NVLS_AMAX = os.environ.get("LLMFP8_NVLS_AMAX", "0") == "1"
 
 
 class ScalePool:
@@ -41,6 +47,30 @@ class ScalePool:
         self.pending = False          # amaxes recorded and their region closed, update not yet applied
         self.epoch = 0                # number of flushes
         self.group = None
+        self._nvls = None             # (multicast address of row 0, device array of signal-pad pointers, pad bytes, rank, world, handle, flat tensor)
+        if NVLS_AMAX and device.type == "cuda" and recipe.reduce_amax and torch.distributed.is_available() \
+                and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1:
+            self._setup_nvls(L)
+
+    def _setup_nvls(self, L: int):
+        """collective over the default group: re-homes amax_history in symmetric memory"""
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        group = dist.group.WORLD
+        try:
+            symm.enable_symm_mem_for_group(group.group_name)
+        except Exception:
+            pass
+        flat = symm.empty(L * _POOL_CAP, dtype=torch.float32, device=self.device)
+        hdl = symm.rendezvous(flat, group=group)
+        if not hdl.multicast_ptr:
+            raise RuntimeError("LLMFP8_NVLS_AMAX=1: no NVLink multicast mapping for symmetric memory on this system")
+        flat.zero_()
+        torch.cuda.synchronize(self.device)
+        dist.barrier(group=group)
+        self.amax_history = flat.view(L, _POOL_CAP)
+        self._nvls = (int(hdl.multicast_ptr), int(hdl.signal_pad_ptrs_dev), int(symm.get_signal_pad_size()), dist.get_rank(group), dist.get_world_size(group),
+                      hdl, flat)
 
     def claim(self, n: int) -> int:
         if self.used + n > _POOL_CAP:
@@ -65,6 +95,16 @@ class ScalePool:
             self.pending = False
             return
         T = self.used
+        if self._nvls is not None and self.group in (None, torch.distributed.group.WORLD):
+            mc, pads, pad_bytes, rank, world, _, _ = self._nvls
+            L, cap = self.amax_history.shape
+            stream = torch.cuda.current_stream(self.device).cuda_stream
+            rc = _lib.load().llmfp8_nvls_amax_scale_update(self.amax_history.data_ptr(), mc, self.scale.data_ptr(), self.scale_inv.data_ptr(),
+                                                           self.fmax.data_ptr(), L, cap, self.recipe.margin, pads, pad_bytes, rank, world, 0, stream)
+            _lib.check(rc, "nvls_amax_scale_update")
+            self.pending = False
+            self.epoch += 1
+            return
         if self.recipe.reduce_amax and torch.distributed.is_available() and torch.distributed.is_initialized():
             group = self.group
             if torch.distributed.get_world_size(group) > 1:

@@ -128,6 +128,41 @@ def _nvls_worker(rank, world, port, out):
             ar.release()
         red.remove()
         dist.barrier()
+    # -- (3) the amax exchange fused with the scale update (LLMFP8_NVLS_AMAX): against the oracle's update of the elementwise maximum
+    from llm_fp8_b200 import fp8
+    from llm_fp8_b200.recipe import DelayedScaling, Format
+    from oracle import fp8_oracle as fo
+    fp8.reset_fp8_state()
+    fp8.NVLS_AMAX = True
+    try:
+        r = DelayedScaling(fp8_format=Format.HYBRID, amax_history_len=4)
+        pool = fp8.get_pool(r, True, dev)
+        assert pool._nvls is not None
+        off = pool.claim(5)
+        gen = torch.Generator().manual_seed(5)
+        want_hist = torch.zeros(4, 5)
+        want_scale, want_inv, fmax = torch.ones(5), torch.ones(5), torch.full((5,), 448.0)
+        ok3 = True
+        for it in range(6):                                # more updates than the history is long: the roll wraps
+            per_rank = [torch.rand(5, generator=gen) * (10.0 ** (it - 2)) for _ in range(world)]
+            per_rank[it % world][2] = 0.0
+            pool.amax_history[0, off:off + 5] = per_rank[rank].to(dev)
+            pool.pending = True
+            pool.flush()
+            torch.cuda.synchronize()
+            want_hist[0] = torch.stack(per_rank).max(0).values
+            fo.amax_scale_update(want_hist, want_scale, want_inv, fmax, 0)
+            ok3 = ok3 and torch.equal(pool.scale[off:off + 5].cpu(), want_scale) and torch.equal(pool.scale_inv[off:off + 5].cpu(), want_inv) \
+                and torch.equal(pool.amax_history[:, off:off + 5].cpu(), want_hist)
+            dist.barrier()
+        res["amax_ok"] = ok3
+        n = __import__("ctypes").c_uint(0)
+        from llm_fp8_b200 import _lib
+        _lib.check(_lib.load().llmfp8_nvls_timeouts(__import__("ctypes").byref(n)), "nvls_timeouts")
+        res["amax_timeouts"] = n.value
+    finally:
+        fp8.NVLS_AMAX = False
+        fp8.reset_fp8_state()
     res["grad_err"] = max(float((a - b).abs().max() / b.abs().max().clamp_min(1e-30)) for a, b in zip(grads["nvls"], grads["nccl"]))
     if rank == 0:
         torch.save(res, out)
@@ -146,3 +181,4 @@ def test_nvls_gradient_reduce_two_gpus(tmp_path):
     assert got["kernel_ok"], got
     assert got["in_arena"] and got["launches"] == 2 * 6, got          # per block: q, k, v (row slices of one home), proj, fc1, fc2
     assert got["grad_err"] <= 2 ** -6, got
+    assert got["amax_ok"] and got["amax_timeouts"] == 0, got

@@ -35,6 +35,32 @@ def test_cabi_rejects_bad_arguments_before_launching():
     assert b"signal pad" in lib.llmfp8_last_error()
 
 
+def test_cabi_amax_update_rejects_bad_arguments_before_launching():
+    lib = _lib.load()
+    pads = C.c_void_p(0x1000)
+    call = lib.llmfp8_nvls_amax_scale_update
+    ok = (0x2000, 0x3000, 0x4000, 0x5000, 0x6000)          # history, multicast row 0, scale, scale_inv, fmax
+    assert call(*ok, 16, 0, 0, pads, 9216, 0, 2, 0, None) == 0                 # no slots: nothing to do
+    assert call(*ok, 0, 64, 0, pads, 9216, 0, 2, 0, None) == -1                # empty history
+    assert call(*ok, 16, 64, 200, pads, 9216, 0, 2, 0, None) == -1             # margin out of range
+    assert call(*ok, 16, 64, 0, pads, 9216, 0, 1, 0, None) == -1               # world 1 has no peers
+    assert call(0x2000, None, 0x4000, 0x5000, 0x6000, 16, 64, 0, pads, 9216, 0, 2, 0, None) == -1     # no multicast address
+    assert call(0x2000, 0x3002, 0x4000, 0x5000, 0x6000, 16, 64, 0, pads, 9216, 0, 2, 0, None) == -1   # misaligned
+    assert call(None, 0x3000, 0x4000, 0x5000, 0x6000, 16, 64, 0, pads, 9216, 0, 2, 0, None) == -1     # no state
+    assert call(*ok, 16, 64, 0, None, 9216, 0, 2, 0, None) == -1               # no signal pads
+    assert call(*ok, 16, 4096, 0, pads, 64, 0, 8, 0, None) == -1               # 32 CTAs x 8 ranks do not fit a 64-byte pad
+
+
+def test_pools_stay_in_plain_memory_unless_asked(monkeypatch):
+    from llm_fp8_b200 import fp8
+    from llm_fp8_b200.recipe import DelayedScaling
+    assert fp8.NVLS_AMAX is False                          # opt-in only (LLMFP8_NVLS_AMAX=1)
+    fp8.reset_fp8_state()
+    pool = fp8.get_pool(DelayedScaling(amax_history_len=4), True, torch.device("cpu", 0))
+    assert pool._nvls is None and pool.amax_history.shape == (4, fp8._POOL_CAP)
+    fp8.reset_fp8_state()
+
+
 @pytest.mark.parametrize("world", [2, 4, 8])
 def test_grid_is_the_same_function_on_every_rank(world):
     lib = _lib.load()

@@ -10,6 +10,10 @@ rc=$?; echo "test_nvls exit $rc"; tail -25 gpurun_out/r02_test_nvls2.log
 LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
     tools/nvls_bench.py --out gpurun_out/r02_nvls_bench_n2.jsonl > gpurun_out/r02_nvls_bench_n2.log 2>&1
 echo "nvls_bench exit $?"; tail -20 gpurun_out/r02_nvls_bench_n2.log
+# per-tensor scenario with the fused in-switch amax + scale update (and the in-switch gradient reduce)
+LLMFP8_NVLS_AMAX=1 LLMFP8_NVLS_REDUCE=1 LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
+    --master-port 29522 bench.py --gpus 2 --steps 4 --warmup 3 --scenario default --no-roofline > gpurun_out/r02_nvls_amax_default_n2.json 2> gpurun_out/r02_nvls_amax_default_n2.err
+echo "bench default nvls amax+reduce exit $?"; tail -c 400 gpurun_out/r02_nvls_amax_default_n2.json; tail -3 gpurun_out/r02_nvls_amax_default_n2.err
 for mode in 0 1; do
   LLMFP8_NVLS_REDUCE=$mode LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 \
       --master-port 29521 bench.py --gpus 2 --steps 4 --warmup 3 --scenario mxfp8 --no-roofline > gpurun_out/r02_nvls${mode}_n2.json 2> gpurun_out/r02_nvls${mode}_n2.err
