@@ -242,9 +242,6 @@ def main():
     H = model.H
     M = a.batch * a.seq
     flops_step = model.linear_flops(M)                 # per rank
-    if os.environ.get("LLMFP8_WEIGHT_PREFETCH", "0") == "1":     # opt-in, unmeasured: layer i+1's weight casts on a side stream under layer i
-        from llm_fp8_b200.prefetch import WeightPrefetcher
-        WeightPrefetcher(model.layers)
     # LLMFP8_NVLS_REDUCE=1 (opt-in, unmeasured): weight gradients written by the wgrad GEMMs into a symmetric arena and summed in the
     # NVSwitch fabric by our own kernel (csrc/nvls_reduce.cu) instead of NCCL
     arena = dp.NvlsGradArena(dp.gemm_weight_buffers(model)) if world > 1 and os.environ.get("LLMFP8_NVLS_REDUCE", "0") == "1" else None
@@ -451,7 +448,7 @@ def main():
                                          else "fused: GEMM epilogue / RMSNorm backward") if model.layers[0].fuse_residual else "separate elementwise passes"), "l2": "inputs larger than L2 (per-step working set: weights + activations of the stack >> 126 MB)",
                        "frac_of_nominal_fp8_peak": value / world / FP8_NOMINAL_TFLOPS,
                        "experiments": {k: os.environ[k] for k in ("LLMFP8_GEMM_DEBUG", "LLMFP8_MX_EPILOGUE_RESIDUAL", "LLMFP8_MX_FUSED_ACT",
-                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB", "LLMFP8_GRAPH_DP", "LLMFP8_WEIGHT_PREFETCH", "LLMFP8_NVLS_AMAX") if k in os.environ}},
+                                                                  "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB", "LLMFP8_GRAPH_DP", "LLMFP8_NVLS_AMAX") if k in os.environ}},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
             "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
             "cpu_baseline": cpu,

@@ -166,7 +166,7 @@ int llmfp8_nccl_destroy(void* comm);
  *                      so one pad serves every launch of a stream.  All ranks must issue the same launches in the same order.
  *   timeout_ms       : a rank whose peers do not arrive gives up after this long (0 = 10 s, < 0 = never) and counts it;
  *                      llmfp8_nvls_timeouts (synchronises the device) returns the count — non-zero means results are invalid.
- * NOT yet run on hardware (round 1 ended without GPU time): opt-in through dp.GradAllReducer(nvls=...) / LLMFP8_NVLS_REDUCE=1. */
+ * Opt-in through dp.GradAllReducer(nvls=...) / LLMFP8_NVLS_REDUCE=1. */
 int llmfp8_nvls_allreduce_sum_bf16(void* multicast_ptr, int64_t numel, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world,
                                    int max_ctas, int timeout_ms, void* stream);
 int llmfp8_nvls_grid(int64_t numel, int world, int max_ctas);
@@ -179,6 +179,11 @@ int llmfp8_nvls_amax_scale_update(float* amax_history, const void* row0_multicas
                                   int num_tensors, int margin, void* const* signal_pads, int64_t signal_pad_bytes, int rank, int world, int timeout_ms,
                                   void* stream);
 int llmfp8_nvls_timeouts(unsigned int* count);
+/* A timed-out meeting is sticky: every later llmfp8_nvls_* launch on the device returns at once (and counts itself) until the host has
+ * re-zeroed the signal pads and called llmfp8_nvls_reset.  llmfp8_nvls_timeouts_async copies the counter into PINNED host memory on
+ * `stream` without synchronising — the once-per-step poll dp.GradAllReducer.finish() and fp8.ScalePool.flush() use. */
+int llmfp8_nvls_timeouts_async(unsigned int* pinned_host_count, void* stream);
+int llmfp8_nvls_reset(void);
 
 #ifdef __cplusplus
 }

@@ -56,6 +56,8 @@ _PROTOTYPES = {
     "llmfp8_nvls_grid": [i64, i32, i32],
     "llmfp8_nvls_amax_scale_update": [vp, vp, vp, vp, vp, i32, i32, i32, vp, i64, i32, i32, i32, vp],
     "llmfp8_nvls_timeouts": [vp],
+    "llmfp8_nvls_timeouts_async": [vp, vp],
+    "llmfp8_nvls_reset": [],
     "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }
 _RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}

@@ -118,6 +118,8 @@ int launch_nvls_allreduce_sum_bf16(void*, int64_t, void* const*, int64_t, int, i
 int nvls_grid(int64_t, int, int);
 int launch_nvls_amax_scale_update(float*, const void*, float*, float*, const float*, int, int, int, void* const*, int64_t, int, int, int, cudaStream_t);
 int nvls_timeouts(unsigned int*);
+int nvls_timeouts_async(unsigned int*, cudaStream_t);
+int nvls_reset();
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
@@ -245,5 +247,7 @@ int llmfp8_nvls_amax_scale_update(float* amax_history, const void* row0_multicas
                                          signal_pad_bytes, rank, world, timeout_ms, S(stream));
 }
 int llmfp8_nvls_timeouts(unsigned int* count) { return nvls_timeouts(count); }
+int llmfp8_nvls_timeouts_async(unsigned int* pinned_host_count, void* stream) { return nvls_timeouts_async(pinned_host_count, S(stream)); }
+int llmfp8_nvls_reset(void) { return nvls_reset(); }
 
 }  // extern "C"

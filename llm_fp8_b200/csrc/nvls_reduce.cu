@@ -11,7 +11,10 @@
 //   entry (relaxed): every rank's wgrad GEMM for this gradient has completed (its reduce kernel is stream-ordered after it);
 //   exit  (release / acquire): every rank's multimem.st has landed before any rank's next kernel reads or overwrites the gradient.
 // A rank that waits longer than `timeout_ns` (%globaltimer) gives up, counts it in g_nvls_timeouts (llmfp8_nvls_timeouts) and leaves — the
-// result is then wrong and the host must raise, but the GPU is never left spinning.
+// result is then wrong and the host must raise, but the GPU is never left spinning.  The failure is STICKY: a rank that gave up may have
+// left a 1 on a peer's slot, so the signal pads can no longer be trusted; every later launch on this device sees the non-zero counter on
+// entry and returns at once (its peers then time out too and poison themselves) until the host has re-zeroed the pads and called
+// llmfp8_nvls_reset.  The host polls the counter once per step without synchronising (llmfp8_nvls_timeouts_async).
 //
 // The same file holds the other exchange of the path (exchange 1): the delayed-scaling amax MAX all-reduce fused with the scale update it
 // feeds (K4) — nvls_amax_scale_update_kernel: meet, one multimem.ld_reduce.max.u32 per fp8 tensor slot (non-negative floats order like
@@ -56,6 +59,8 @@ __device__ __forceinline__ long long now_ns() {
 }
 
 // thread t < world of each CTA pairs with CTA blockIdx.x of rank t.  Returns false on timeout.
+__device__ __forceinline__ bool poisoned() { return *reinterpret_cast<volatile unsigned int*>(&g_nvls_timeouts) != 0u; }
+
 template <bool ORDER>
 __device__ __forceinline__ bool meet_ranks(uint32_t* const* pads, int rank, int world, long long timeout_ns) {
     bool ok = true;
@@ -90,6 +95,10 @@ __global__ void __launch_bounds__(kThreads) nvls_allreduce_sum_bf16_kernel(uint4
                                                                            long long timeout_ns) {
     pdl_wait();
     pdl_launch_dependents();
+    if (poisoned()) {                       // an earlier meeting on this device timed out: refuse (uniform over the grid's lifetime or not, no thread meets)
+        if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(&g_nvls_timeouts, 1u);
+        return;
+    }
     // CTA-wide verdict without shared memory (the kernel's footprint beside a GEMM CTA is registers and the 1 KB the system reserves)
     const int alive = __syncthreads_and(meet_ranks<false>(pads, rank, world, timeout_ns) ? 1 : 0);
     if (alive) {
@@ -127,6 +136,10 @@ __global__ void __launch_bounds__(kThreads) nvls_amax_scale_update_kernel(float*
                                                                           long long timeout_ns) {
     pdl_wait();
     pdl_launch_dependents();
+    if (poisoned()) {
+        if (threadIdx.x == 0 && blockIdx.x == 0) atomicAdd(&g_nvls_timeouts, 1u);
+        return;
+    }
     const int t = blockIdx.x * blockDim.x + threadIdx.x;
     int alive = __syncthreads_and(meet_ranks<false>(pads, rank, world, timeout_ns) ? 1 : 0);
     uint32_t m = 0;
@@ -210,6 +223,26 @@ int nvls_timeouts(unsigned int* count) {
     cudaError_t e = cudaMemcpyFromSymbol(count, g_nvls_timeouts, sizeof(unsigned int));     // synchronises: diagnostics only
     if (e != cudaSuccess) {
         set_error("nvls_timeouts: %s", cudaGetErrorString(e));
+        return static_cast<int>(e);
+    }
+    return 0;
+}
+
+int nvls_timeouts_async(unsigned int* pinned_host, cudaStream_t stream) {
+    LLMFP8_REQUIRE(pinned_host != nullptr, "nvls_timeouts_async: null output");
+    cudaError_t e = cudaMemcpyFromSymbolAsync(pinned_host, g_nvls_timeouts, sizeof(unsigned int), 0, cudaMemcpyDeviceToHost, stream);
+    if (e != cudaSuccess) {
+        set_error("nvls_timeouts_async: %s", cudaGetErrorString(e));
+        return static_cast<int>(e);
+    }
+    return 0;
+}
+
+int nvls_reset() {
+    const unsigned int zero = 0;
+    cudaError_t e = cudaMemcpyToSymbol(g_nvls_timeouts, &zero, sizeof(unsigned int));      // synchronises; the caller has re-zeroed the signal pads
+    if (e != cudaSuccess) {
+        set_error("nvls_reset: %s", cudaGetErrorString(e));
         return static_cast<int>(e);
     }
     return 0;

@@ -12,7 +12,9 @@ tensor is the all-reduce buffer.
 from __future__ import annotations
 
 import bisect
+import contextlib
 import os
+import weakref
 from typing import Iterable, List, Optional, Sequence, Tuple
 
 import torch
@@ -55,7 +57,13 @@ class GradAllReducer:
     Large gradients (>= `direct_numel` elements) are all-reduced in place, individually, as soon as their
     post-accumulate hook fires (asynchronously, on NCCL's stream); small ones (norm weights, biases) are packed into one
     flat buffer and reduced together in `finish()`.  Call `finish()` after `backward()`; it makes the current stream wait
-    for every outstanding reduction."""
+    for every outstanding reduction.
+
+    Gradient accumulation (more than one backward() per optimizer step; DDP.no_sync in the reference, train_multi_gpu.py:714-725):
+    run every micro-batch but the last inside `no_sync()` — the hooks then leave the locally accumulated gradient alone — and the
+    last one outside it, so the SUM over micro-batches is reduced exactly once.  A hook that fires for a gradient tensor which was
+    already reduced (or whose reduce is still in flight) raises instead of summing the reduced value a second time; after
+    `optimizer.zero_grad(set_to_none=False)` (same tensor, zeroed in place) call `new_step()` to say so."""
 
     def __init__(self, params: Iterable[torch.nn.Parameter], group=None, direct_numel: int = 1 << 20, average: bool = True,
                  prescaled: Optional[bool] = None, bucket_bytes: Optional[int] = None, nvls: Optional["NvlsGradArena"] = None):
@@ -92,6 +100,8 @@ class GradAllReducer:
         self.nvls_launches = 0
         self._nvls_stream = None
         self._nvls_busy = False
+        self.sync = True                # False inside no_sync(): hooks do nothing
+        self._reduced = {}              # id(grad tensor) -> weakref: reduced (or being reduced) since it was created
         if self.nvls is not None and not self.prescaled:
             raise RuntimeError("the in-switch gradient reduce is a plain SUM: it needs prescaled=True (loss scaled by 1/world)")
         if self.world > 1:
@@ -103,10 +113,34 @@ class GradAllReducer:
         # gloo has no AVG: sum, then scale in finish()
         return dist.ReduceOp.AVG if (self.average and dist.get_backend(self.group) == "nccl") else dist.ReduceOp.SUM
 
+    @contextlib.contextmanager
+    def no_sync(self):
+        """Micro-batches whose gradients only accumulate locally (every one but the last of an optimizer step)."""
+        prev, self.sync = self.sync, False
+        try:
+            yield
+        finally:
+            self.sync = prev
+
+    def new_step(self):
+        """Forget which gradient tensors were reduced (needed only when gradients are zeroed in place instead of dropped)."""
+        self._reduced = {}
+
+    def _claim(self, g: torch.Tensor):
+        ref = self._reduced.get(id(g))
+        if ref is not None and ref() is g:
+            raise RuntimeError("GradAllReducer: this gradient tensor was already all-reduced (or its reduce is still in flight) and backward "
+                               "accumulated into it again — wrap all micro-batches but the last in reducer.no_sync(), and drop the gradients "
+                               "(zero_grad(set_to_none=True)) or call reducer.new_step() between optimizer steps")
+        if len(self._reduced) > 4096:
+            self._reduced = {k: r for k, r in self._reduced.items() if r() is not None}
+        self._reduced[id(g)] = weakref.ref(g)
+
     def _hook(self, p: torch.nn.Parameter):
         g = p.grad
-        if g is None:
+        if g is None or not self.sync:
             return
+        self._claim(g)
         if self.nvls is not None and g.is_contiguous():
             where = self.nvls.locate(g)
             if where is not None:
@@ -149,6 +183,7 @@ class GradAllReducer:
         if self._nvls_busy:
             self.nvls.current_stream().wait_stream(self._nvls_stream)
             self._nvls_busy = False
+            self.nvls.poll()     # raises (at the latest one step on) if a rank meeting gave up
         self._flush_pending()
         if self._small:
             grads = [p.grad for p in self._small]
@@ -178,6 +213,51 @@ class GradAllReducer:
 
 
 # ------------------------------------------------------------------------------------------ in-switch gradient reduce (NVLS)
+class NvlsWatch:
+    """Once-per-step poll of the library's timed-out-meeting counter without synchronising: each poll() first looks at the value the
+    PREVIOUS poll copied (its event has long completed), raises if it is non-zero, then queues the next copy on `stream`.  A failure
+    therefore surfaces one step late at worst — and it is sticky in the kernels (csrc/nvls_reduce.cu), so nothing computed after it
+    is trusted either.  One watch per device."""
+    _by_device = {}
+
+    @classmethod
+    def get(cls, device: torch.device) -> "NvlsWatch":
+        idx = device.index if device.index is not None else torch.cuda.current_device()
+        w = cls._by_device.get(idx)
+        if w is None:
+            w = cls._by_device[idx] = cls(idx)
+        return w
+
+    def __init__(self, idx: int):
+        from . import _lib
+        self._lib, self._check = _lib.load(), _lib.check
+        self.idx = idx
+        self._host = torch.zeros(1, dtype=torch.int32).pin_memory()
+        self._event = None
+
+    def poll(self, stream=None):
+        if self._event is not None and self._event.query():
+            self._raise_if(int(self._host[0]) & 0xFFFFFFFF)
+        stream = stream or torch.cuda.current_stream(self.idx)
+        with torch.cuda.device(self.idx):
+            self._check(self._lib.llmfp8_nvls_timeouts_async(self._host.data_ptr(), stream.cuda_stream), "nvls_timeouts_async")
+            self._event = torch.cuda.Event()
+            self._event.record(stream)
+
+    def check_now(self):
+        import ctypes as C
+        n = C.c_uint(0)
+        with torch.cuda.device(self.idx):
+            self._check(self._lib.llmfp8_nvls_timeouts(C.byref(n)), "nvls_timeouts")
+        self._raise_if(n.value)
+
+    @staticmethod
+    def _raise_if(n: int):
+        if n:
+            raise RuntimeError(f"in-switch (NVLS) exchange: {n} rank meetings timed out or were refused after a time-out — the gradients / scales "
+                               "since then are invalid; re-zero the signal pads and call llmfp8_nvls_reset, or fall back to NCCL")
+
+
 def gemm_weight_buffers(module: torch.nn.Module) -> List[Tuple[torch.Tensor, List[torch.nn.Parameter]]]:
     """Every [out, in] buffer that a wgrad GEMM of the path writes a gradient for, with the Parameters living in it: Linear.weight,
     LayerNormLinear.weight (or the joined buffer of its split query / key / value weights: te_llama.py:198-211), LayerNormMLP's
@@ -301,16 +381,13 @@ class NvlsGradArena:
                                                       stream.cuda_stream)
         _lib.check(rc, "nvls_allreduce_sum_bf16")
 
+    def poll(self) -> None:
+        """Non-blocking, once per step (GradAllReducer.finish): raises if a rank meeting was seen to have timed out."""
+        NvlsWatch.get(self.device).poll(self.current_stream())
+
     def check(self) -> None:
         """Raises if any reduce launch gave up waiting for its peers (synchronises the device)."""
-        import ctypes as C
-
-        from . import _lib
-        n = C.c_uint(0)
-        with torch.cuda.device(self.device):
-            _lib.check(self._lib.llmfp8_nvls_timeouts(C.byref(n)), "nvls_timeouts")
-        if n.value:
-            raise RuntimeError(f"in-switch gradient reduce: {n.value} rank meetings timed out — gradients of this step are invalid")
+        NvlsWatch.get(self.device).check_now()
 
     def release(self) -> None:
         from . import functional as fn

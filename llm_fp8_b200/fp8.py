@@ -47,6 +47,7 @@ class ScalePool:
         self.pending = False          # amaxes recorded and their region closed, update not yet applied
         self.epoch = 0                # number of flushes
         self.group = None
+        self._free = {}               # width -> released slot ranges
         self._nvls = None             # (multicast address of row 0, device array of signal-pad pointers, pad bytes, rank, world, handle, flat tensor)
         if NVLS_AMAX and device.type == "cuda" and recipe.reduce_amax and torch.distributed.is_available() \
                 and torch.distributed.is_initialized() and torch.distributed.get_world_size() > 1:
@@ -73,11 +74,32 @@ class ScalePool:
                       hdl, flat)
 
     def claim(self, n: int) -> int:
+        free = self._free.get(n)
+        if free:
+            off = free.pop()
+            self.amax_history[:, off:off + n].zero_()          # a recycled range starts like a fresh one: scale 1, empty history
+            self.scale[off:off + n].fill_(1.0)
+            self.scale_inv[off:off + n].fill_(1.0)
+            return off
         if self.used + n > _POOL_CAP:
             raise RuntimeError(f"fp8 scale pool exhausted ({_POOL_CAP} slots)")
         off = self.used
         self.used += n
         return off
+
+    def release(self, off: int, n: int):
+        """A module that claimed [off, off + n) is gone (Fp8Meta.__del__): the range is handed to the next claim of the same width."""
+        self._free.setdefault(n, []).append(off)
+
+    def bind_group(self, group):
+        """The fp8_group of the enclosing fp8_autocast: the amax MAX exchange of this pool runs over it.  One group per pool."""
+        if group is None or group is self.group:
+            return
+        if self.group is not None:
+            raise RuntimeError("fp8_autocast: two different fp8_group values for modules sharing one delayed-scaling recipe pool")
+        if self._nvls is not None:
+            raise RuntimeError("LLMFP8_NVLS_AMAX=1 exchanges amaxes over the default group only; fp8_group is not supported with it")
+        self.group = group
 
     # device pointers of a slot
     def scale_ptr(self, slot: int) -> int:
@@ -95,6 +117,11 @@ class ScalePool:
             self.pending = False
             return
         T = self.used
+        # scale_inv is VERSIONED: every update writes a fresh tensor (K4 writes all CAP entries and reads none), so a forward that
+        # captured `pool.scale_inv` keeps de-scaling its saved fp8 bytes with the factors they were cast with however many updates
+        # happen before its backward runs (fwd, fwd, bwd, bwd; an eval forward in between; recompute) — what TE gets from cloning
+        # scale_inv in forward, without a copy kernel.  The old version dies with the last graph that holds it.
+        self.scale_inv = torch.empty_like(self.scale_inv)
         if self._nvls is not None and self.group in (None, torch.distributed.group.WORLD):
             mc, pads, pad_bytes, rank, world, _, _ = self._nvls
             L, cap = self.amax_history.shape
@@ -102,6 +129,8 @@ class ScalePool:
             rc = _lib.load().llmfp8_nvls_amax_scale_update(self.amax_history.data_ptr(), mc, self.scale.data_ptr(), self.scale_inv.data_ptr(),
                                                            self.fmax.data_ptr(), L, cap, self.recipe.margin, pads, pad_bytes, rank, world, 0, stream)
             _lib.check(rc, "nvls_amax_scale_update")
+            from .dp import NvlsWatch
+            NvlsWatch.get(self.device).poll()          # a timed-out meeting leaves the scales un-updated: raise (one flush later at worst)
             self.pending = False
             self.epoch += 1
             return
@@ -188,6 +217,9 @@ def fp8_autocast(enabled: bool = True, calibrating: bool = False, fp8_recipe: Op
     (the reference nests its per-block autocasts inside accelerate's outer one: train_fp8.py:184-188)."""
     if enabled and not torch.cuda.is_available():
         raise RuntimeError("fp8_autocast(enabled=True) needs a CUDA device: llm_fp8_b200 has no CPU path")
+    if calibrating:
+        raise NotImplementedError("fp8_autocast(calibrating=True) (amax collection during a higher-precision run) is not on the reference's path "
+                                  "(te_llama.py:76,79 never passes it) and is not implemented")
     _state.stack.append((enabled, fp8_recipe, fp8_group))
     try:
         yield

@@ -15,7 +15,7 @@ from typing import Optional
 import torch
 
 from . import ops
-from .fp8 import ScalePool, get_pool, note_forward_pool
+from .fp8 import ScalePool, get_fp8_group, get_pool, note_forward_pool
 from .recipe import DelayedScaling, MXFP8BlockScaling, Recipe, bwd_fmt, fwd_fmt
 
 
@@ -34,9 +34,21 @@ class Fp8Meta:
             s = self._slots[key] = {"pf": pf, "pb": pb, "f0": pf.claim(self.n_fwd), "b0": pb.claim(self.n_bwd), "ef": -1, "eb": -1}
         return s
 
+    def __del__(self):
+        try:
+            for s in self._slots.values():
+                s["pf"].release(s["f0"], self.n_fwd)
+                s["pb"].release(s["b0"], self.n_bwd)
+        except Exception:          # interpreter shutdown
+            pass
+
     @staticmethod
     def begin_fwd(s, training: bool):
         pf: ScalePool = s["pf"]
+        group = get_fp8_group()
+        if group is not None:
+            pf.bind_group(group)
+            s["pb"].bind_group(group)
         if pf.pending and s["ef"] == pf.epoch:
             pf.flush()
         if training:
@@ -75,7 +87,7 @@ def _weight_pt(wcache, first, key, weight, ff, pf: ScalePool, slot) -> "ops.QTen
         return wcache[key]
     wq = ops.quantize(weight, ff, pf, slot)
     if wcache is not None and first is not None:
-        wq = ops.QTensor(wq.data, wq.fmt, pf.scale_inv[slot:slot + 1].clone(), 0)
+        wq = ops.QTensor(wq.data, wq.fmt, pf.scale_inv, slot)        # this version of scale_inv is never rewritten (ScalePool.flush)
         wcache[key] = wq
     return wq
 
@@ -193,6 +205,7 @@ class LinearFn(torch.autograd.Function):
             ctx.needs = (x.requires_grad, weight.requires_grad)
             ctx.has_residual = residual is not None
             ctx.w_si = (wq.scale_inv, wq.scale_inv_off)
+            ctx.si = pf.scale_inv             # the version the saved fp8 bytes were cast under (ScalePool.flush replaces, never rewrites, it)
         ctx.set_materialize_grads(False)
         y = y.reshape(*x.shape[:-1], N)
         return (y, x.view_as(x)) if passthrough else y
@@ -207,7 +220,7 @@ class LinearFn(torch.autograd.Function):
         Fp8Meta.begin_bwd(s)
         pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
         ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
-        xq = ops.QTensor(xq_d, ff, pf.scale_inv, f0 + 0)
+        xq = ops.QTensor(xq_d, ff, ctx.si, f0 + 0)
         wq = ops.QTensor(wq_d, ff, *ctx.w_si)
         dy2 = _2d(dy).contiguous()
         dbias = None
@@ -253,6 +266,7 @@ class LayerNormMLPFn(torch.autograd.Function):
             ctx.recipe, ctx.slots = recipe, s
             ctx.residual = residual
             ctx.w1_si, ctx.w2_si = (w1q.scale_inv, w1q.scale_inv_off), (w2q.scale_inv, w2q.scale_inv_off)
+            ctx.si = pf.scale_inv
             ctx.has_bias = b1 is not None
             ctx.shape = x.shape
             ctx.dims = (M, H, I)
@@ -268,9 +282,9 @@ class LayerNormMLPFn(torch.autograd.Function):
         Fp8Meta.begin_bwd(s)
         pf, pb, f0, b0 = s["pf"], s["pb"], s["f0"], s["b0"]
         ff, bf = fwd_fmt(recipe.fp8_format), bwd_fmt(recipe.fp8_format)
-        lnq = ops.QTensor(lnq_d, ff, pf.scale_inv, f0 + 0)
+        lnq = ops.QTensor(lnq_d, ff, ctx.si, f0 + 0)
         w1q = ops.QTensor(w1q_d, ff, *ctx.w1_si)
-        aq = ops.QTensor(aq_d, ff, pf.scale_inv, f0 + 3)
+        aq = ops.QTensor(aq_d, ff, ctx.si, f0 + 3)
         w2q = ops.QTensor(w2q_d, ff, *ctx.w2_si)
         dy2 = _2d(dy).contiguous()
         db2 = db1 = None

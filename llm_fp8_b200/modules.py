@@ -17,7 +17,7 @@ import torch.nn.functional as F
 
 from . import functional as fn
 from .fp8 import get_fp8_recipe, is_fp8_enabled
-from .recipe import DelayedScaling, MXFP8BlockScaling, fwd_fmt
+from .recipe import DelayedScaling, MXFP8BlockScaling
 
 
 def _init_weight(shape, dtype, device, std=0.023):
@@ -44,54 +44,35 @@ class _Fp8Module(nn.Module):
 
     def _apply(self, fn_, *args, **kwargs):
         self._wcache.clear()                 # .cuda() / .to() replace the parameters the copies were cast from
-        self._prefetched = False
         return super()._apply(fn_, *args, **kwargs)
 
-    # ---- weight copies quantised ahead of the forward that uses them (prefetch.WeightPrefetcher; opt-in, unmeasured)
-    _prefetched = False          # the copies for the coming forward already sit in _wcache
-    _last_recipe = None          # recipe of the latest forward: what a prefetch for the next step casts with
-
-    def _prefetch_targets(self):
-        """-> [(cache name, weight [out, in], forward slot of the weight)] as the autograd Functions of this module key them"""
-        raise NotImplementedError
-
-    def prefetch_weights(self, recipe, device, need_col: bool = True) -> None:
-        """Casts this module's weights exactly as its forward would (same kernels, same cache keys, same amax / scale slots) and keeps
-        the copies; the next forward(is_first_microbatch=None) picks them up instead of casting."""
-        with torch.no_grad():
-            for name, w, slot in self._prefetch_targets():
-                if isinstance(recipe, MXFP8BlockScaling):
-                    fn._weight_mx(self._wcache, True, (name, "mx"), w, need_col)
-                else:
-                    s = self._meta.get(recipe, device)
-                    fn._weight_pt(self._wcache, True, (name, recipe.key()), w, fwd_fmt(recipe.fp8_format), s["pf"], s["f0"] + slot)
-
-    def _wcache_tensors(self):
-        for v in self._wcache.values():
-            for t in (getattr(v, a, None) for a in ("data", "scale_inv", "row", "sf_row", "col", "sf_col")):
-                if isinstance(t, torch.Tensor):
-                    yield t
-
-    def _take_prefetched(self, is_first_microbatch, recipe):
-        """-> (is_first_microbatch to run with, drop the copies afterwards)"""
-        self._last_recipe = recipe
-        if self._prefetched:
-            self._prefetched = False
-            if is_first_microbatch is None:
-                return False, True           # reuse the kept copies (the TE contract's `False`), then let them go
-        return is_first_microbatch, False
-
     def get_extra_state(self):
+        """This module's delayed-scaling slots, exactly as they stand — including amaxes recorded but not yet folded into the scales
+        (`pending`), so a restore resumes mid-window without a collective (state_dict() is often called on one rank only)."""
         out = {}
         for (rkey, dev), s in self._meta._slots.items():
             pf, pb = s["pf"], s["pb"]
             out[str((rkey, "fwd"))] = {k: v[..., s["f0"]:s["f0"] + self._N_FWD].detach().cpu() for k, v in
                                        (("amax_history", pf.amax_history), ("scale", pf.scale), ("scale_inv", pf.scale_inv))}
+            out[str((rkey, "fwd"))]["pending"] = bool(pf.pending)
             out[str((rkey, "bwd"))] = {k: v[..., s["b0"]:s["b0"] + self._N_BWD].detach().cpu() for k, v in
                                        (("amax_history", pb.amax_history), ("scale", pb.scale), ("scale_inv", pb.scale_inv))}
+            out[str((rkey, "bwd"))]["pending"] = bool(pb.pending)
         return out
 
     def set_extra_state(self, state):
+        """Only this package's own dict format is understood.  A checkpoint written with Transformer Engine modules carries a pickled
+        uint8 tensor / BytesIO here: it is ignored with a warning (the delayed-scaling windows restart empty; weights load normally)."""
+        if state is None or (isinstance(state, dict) and not state):
+            self._pending_extra_state = None
+            return
+        if not isinstance(state, dict):
+            if not (isinstance(state, torch.Tensor) and state.numel() == 0):
+                import warnings
+                warnings.warn(f"{type(self).__name__}: ignoring an _extra_state of type {type(state).__name__} (not written by llm_fp8_b200); "
+                              "delayed-scaling state starts fresh")
+            self._pending_extra_state = None
+            return
         self._pending_extra_state = state      # applied when the slots are claimed for that recipe
 
     def _apply_extra_state(self, recipe, device):
@@ -106,6 +87,7 @@ class _Fp8Module(nn.Module):
             pool.amax_history[:, off:off + n].copy_(blob["amax_history"])
             pool.scale[off:off + n].copy_(blob["scale"])
             pool.scale_inv[off:off + n].copy_(blob["scale_inv"])
+            pool.pending = pool.pending or bool(blob.get("pending", False))
         self._pending_extra_state = None
 
 
@@ -128,19 +110,13 @@ class Linear(_Fp8Module):
         _check_active("Linear")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
-        first, drop = self._take_prefetched(is_first_microbatch, recipe)
+        first = is_first_microbatch
         if isinstance(recipe, MXFP8BlockScaling):
             out = fn.MXLinearFn.apply(inp, self.weight, self.bias, None, 0.0, g, residual, False, self._wcache, first)
         else:
             self._apply_extra_state(recipe, inp.device)
             out = fn.LinearFn.apply(inp, self.weight, self.bias, self._meta, recipe, None, 0.0, g, residual, False, self._wcache, first)
-        if drop:
-            self._wcache.clear()
         return out
-
-    def _prefetch_targets(self):
-        return [("w", self.weight, 1)]
-
 
 _JOIN_SPLIT_WEIGHTS = os.environ.get("LLMFP8_JOIN_SPLIT_WEIGHTS", "1") != "0"
 
@@ -243,25 +219,13 @@ class LayerNormLinear(_Fp8Module):
         recipe = get_fp8_recipe()
         w, b = self._weight_bias()
         g = torch.is_grad_enabled()
-        first, drop = self._take_prefetched(is_first_microbatch, recipe)
+        first = is_first_microbatch
         if isinstance(recipe, MXFP8BlockScaling):
             out = fn.MXLinearFn.apply(inp, w, b, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, first)
         else:
             self._apply_extra_state(recipe, inp.device)
             out = fn.LinearFn.apply(inp, w, b, self._meta, recipe, self.layer_norm_weight, self.eps, g, None, return_input, self._wcache, first)
-        if drop:
-            self._wcache.clear()
         return out
-
-    def _prefetch_targets(self):
-        if self._split is None:
-            return [("w", self.weight, 1)]
-        ws = [getattr(self, n + "weight") for n in self._split]
-        if _JOIN_SPLIT_WEIGHTS:
-            self._joined = _joined_rows(ws, getattr(self, "_joined", None))
-            return [("w", self._joined, 1)]
-        return [("w", torch.cat([w.detach() for w in ws], dim=0), 1)]
-
 
 class LayerNormMLP(_Fp8Module):
     """RMSNorm -> fc1 (+bias) -> SwiGLU -> fc2 (+bias).  Parameters: layer_norm_weight [H], fc1_weight [2I, H] (gate rows first:
@@ -295,7 +259,7 @@ class LayerNormMLP(_Fp8Module):
         _check_active("LayerNormMLP")
         recipe = get_fp8_recipe()
         g = torch.is_grad_enabled()
-        first, drop = self._take_prefetched(is_first_microbatch, recipe)
+        first = is_first_microbatch
         if isinstance(recipe, MXFP8BlockScaling):
             out = fn.MXLayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self.eps, g,
                                             add_residual, self._wcache, first)
@@ -303,13 +267,7 @@ class LayerNormMLP(_Fp8Module):
             self._apply_extra_state(recipe, inp.device)
             out = fn.LayerNormMLPFn.apply(inp, self.layer_norm_weight, self.fc1_weight, self.fc1_bias, self.fc2_weight, self.fc2_bias, self._meta,
                                           recipe, self.eps, g, add_residual, self._wcache, first)
-        if drop:
-            self._wcache.clear()
         return out
-
-    def _prefetch_targets(self):
-        return [("w1", self.fc1_weight, 1), ("w2", self.fc2_weight, 4)]
-
 
 # ------------------------------------------------------------------------------------------ attention shell
 class RotaryPositionEmbedding(nn.Module):

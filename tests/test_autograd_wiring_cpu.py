@@ -231,131 +231,10 @@ def test_weight_copies_are_kept_between_microbatches(fake_ops):
     assert run(False)[4] == base[4] - 1                 # mlp casts again (and keeps), lin still reuses
 
 
-def test_weight_prefetcher_feeds_the_next_layer_and_changes_nothing(fake_ops):
-    """prefetch.WeightPrefetcher: from the second step on (recipes known), layers 2.. find their weight copies already cast when they
-    start (issued one layer ahead), layers 0 and 1 cast inline; outputs, gradients and the number of quantiser launches are those of
-    the plain run, and no copy outlives the forward that used it."""
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-
-    def stack():
-        layers = torch.nn.ModuleList(_layer(True) for _ in range(5))
-        with torch.no_grad():
-            for i, layer in enumerate(layers):           # _layer() seeds identically: make the layers differ
-                for p in layer.parameters():
-                    p.mul_(1.0 + 0.01 * i)
-        return layers
-
-    def run(prefetch):
-        layers = stack()
-        pf = WeightPrefetcher(layers) if prefetch else None
-        x = torch.randn(2, 5, H, generator=torch.Generator().manual_seed(11)).bfloat16()
-        outs, counts, order = [], [], []
-        for step in range(3):
-            fake_ops.calls.clear()
-            for p in layers.parameters():
-                p.grad = None
-            h = x.clone().requires_grad_(True)
-            y = h
-            for layer in layers:
-                y = layer(y)
-            y.float().square().mean().backward()
-            outs.append((y.detach().clone(), h.grad.clone(), [p.grad.clone() for p in layers.parameters()]))
-            counts.append(sum(c.startswith("mxq") for c in fake_ops.calls))
-            if pf is not None:
-                order.append((pf.issued, pf.consumed))
-                assert all(not m._wcache and not m._prefetched for mods in pf._mods for m in mods)
-                assert not pf._ready
-        return outs, counts, order
-
-    plain, n_plain, _ = run(False)
-    pre, n_pre, order = run(True)
-    assert n_plain == n_pre
-    assert order == [(0, 0), (3, 3), (6, 6)]             # step 1: recipes unknown; then layers 2, 3, 4 of each step
-    for (y0, g0, p0), (y1, g1, p1) in zip(plain, pre):
-        assert torch.equal(y0, y1) and torch.equal(g0, g1)
-        assert all(torch.equal(a, b) for a, b in zip(p0, p1))
 
 
-def test_prefetched_copies_are_cast_before_the_previous_layer_runs(fake_ops):
-    """the point of the exercise: when layer i's first GEMM is issued, layer i+1's four weight casts are already in the queue"""
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-    layers = torch.nn.ModuleList(_layer(True) for _ in range(4))
-    pf = WeightPrefetcher(layers)
-    x = torch.randn(1, 4, H, generator=torch.Generator().manual_seed(2)).bfloat16()
-    for step in range(2):
-        fake_ops.calls.clear()
-        marks = []
-        hooks = [layer.register_forward_pre_hook(lambda m, a, i=i: marks.append((i, len(fake_ops.calls)))) for i, layer in enumerate(layers)]
-        y = x
-        with torch.no_grad():
-            for layer in layers:
-                y = layer(y)
-        for h in hooks:
-            h.remove()
-        if step == 1:
-            # hooks registered after the prefetcher's run after it: at layer 1's and 2's start, the casts for layers 2 and 3 (3 weights
-            # each: joined qkv, proj, and fc1 + fc2 = 4 launches) have just been recorded
-            start = dict(marks)
-            assert fake_ops.calls[start[1] - 4:start[1]] == ["mxq"] * 4
-            assert fake_ops.calls[start[2] - 4:start[2]] == ["mxq"] * 4
-    assert (pf.issued, pf.consumed) == (2, 2)
-    pf.remove()
 
 
-def test_prefetched_copies_never_cross_a_weight_update_or_a_pass(fake_ops):
-    """a copy cast before the weights changed (optimizer step: in-place update) or left over from another pass over the layers
-    (a layer re-run out of order, as activation recomputation does) is never used: it is either replaced by the fresh prefetch of the
-    next pass or dropped, and the layer casts inline"""
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-    layers = torch.nn.ModuleList(_layer(True) for _ in range(4))
-    pf = WeightPrefetcher(layers)
-    x = torch.randn(1, 4, H, generator=torch.Generator().manual_seed(2)).bfloat16()
-
-    def forward(mods):
-        y = x
-        with torch.no_grad():
-            for layer in mods:
-                y = layer(y)
-        return y
-
-    def plain_result(scale):
-        plain = torch.nn.ModuleList(_layer(True) for _ in range(4))
-        with torch.no_grad():
-            for p in plain.parameters():
-                p.mul_(scale)
-        return forward(plain)
-
-    forward(layers)                                     # pass 1: recipes become known
-    y_ref = forward(layers)                             # pass 2: layers 2, 3 prefetched and consumed
-    assert (pf.issued, pf.consumed, pf.rejected) == (2, 2, 0)
-    # a re-run of layer 2 alone leaves a prefetch for layer 3 that nobody takes in this pass ...
-    forward([layers[2]])
-    assert 3 in pf._ready
-    with torch.no_grad():                               # ... then the weights move
-        for p in layers.parameters():
-            p.mul_(1.5)
-    y_new = forward(layers)                             # pass 3: the left-over is replaced by a fresh cast before layer 3 runs
-    assert torch.equal(y_new, plain_result(1.5)) and not torch.equal(y_new, y_ref)
-    # a left-over from an earlier pass that is NOT re-issued (layer 3 entered without its predecessor): dropped
-    forward([layers[2]])                                # issues layer 3's casts in pass 3
-    forward([layers[0]])                                # a new pass begins
-    before = pf.rejected
-    h = forward(layers[:3])[0:1]                        # (this pass re-issues and layer 3 is not run: entry of pass 5 stays)
-    forward([layers[0]])                                # pass 6
-    with torch.no_grad():
-        y3 = layers[3](h)
-    assert pf.rejected == before + 1
-    # same pass, but a weight updated between issue and use (version counter moved): dropped as well
-    with torch.no_grad():
-        h = forward(layers[:3])                         # layer 2's pre-hook issued layer 3's casts
-        layers[3].proj.weight.mul_(2.0)
-        before = pf.rejected
-        y_upd = layers[3](h)
-    assert pf.rejected == before + 1
-    with torch.no_grad():
-        y_inline = layers[3](h)                         # no prefetch pending: inline casts of the updated weights
-    assert torch.equal(y_upd, y_inline)
-    assert all(not m._wcache and not m._prefetched for mods in pf._mods for m in mods)
 
 
 @pytest.mark.parametrize("ffn", [128, 96])

@@ -2,8 +2,7 @@
 functional.LinearFn / LayerNormMLPFn: the C-ABI wrappers are replaced by exact torch stand-ins (no quantisation: the "fp8" copies
 are the bf16 values, every scale is 1), K4 by the oracle's update, CUDA's stream objects by the happens-before model of
 tests/_streams.py.  Under test: which tensors the Functions save, gradient positions, the slot bookkeeping they pass on, the
-wgrad-output homes (functional.wgrad_out), the fused residual path against the reference-shaped one, and — with the stream model —
-that the weight prefetcher's casts under delayed scaling are ordered AFTER the step's scale update and before their use.
+wgrad-output homes (functional.wgrad_out) and the fused residual path against the reference-shaped one.
 Reference structure: TELlamaDecoderLayer.forward with the two DelayedScaling recipes of te_llama.py:39-40, 68-82."""
 import pytest
 import torch
@@ -206,69 +205,3 @@ def test_per_tensor_wgrads_land_in_their_homes(pt_ops):
     finally:
         fn._WGRAD_OUT.clear()
 
-
-def test_prefetched_casts_under_delayed_scaling_follow_the_scale_update(pt_ops):
-    """prefetch.WeightPrefetcher with the reference's two DelayedScaling recipes: every weight cast issued on the side stream reads the
-    pool's scale AFTER this step's update (K4 on the main stream) and its amax lands before the next one; results and the scaling
-    state are those of the inline run."""
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-    tracker, k4 = pt_ops
-
-    def run(prefetch):
-        fp8.reset_fp8_state()
-        layers = torch.nn.ModuleList(_layer(True, seed=3 + i) for i in range(4))
-        pf = WeightPrefetcher(layers) if prefetch else None
-        x = torch.randn(2, 6, H, generator=torch.Generator().manual_seed(9)).bfloat16()
-        outs = []
-        for step in range(3):
-            for p in layers.parameters():
-                p.grad = None
-            h = x.clone().requires_grad_(True)
-            y = h
-            for layer in layers:
-                y = layer(y)
-            tracker.assert_joined()
-            y.float().square().mean().backward()
-            tracker.assert_joined()
-            outs.append((y.detach().clone(), [p.grad.clone() for p in layers.parameters()]))
-            with torch.no_grad():
-                for p in layers.parameters():
-                    p.mul_(1.01)
-            tracker.op("optimizer", [], list(layers.parameters()) + [m._joined for m in layers.modules() if hasattr(m, "_joined")])
-        state = [(p.scale[:p.used].clone(), p.amax_history[:, :p.used].clone()) for p in fp8.all_pools()]
-        return outs, state, pf
-
-    base, st0, _ = run(False)
-    pre, st1, pf = run(True)
-    assert (pf.issued, pf.consumed, pf.rejected) == (4, 4, 0)        # steps 2 and 3, layers 2 and 3
-    for (y0, g0), (y1, g1) in zip(base, pre):
-        assert torch.equal(y0, y1) and all(torch.equal(a, b) for a, b in zip(g0, g1))
-    for (s0, h0), (s1, h1) in zip(st0, st1):
-        assert torch.equal(s0, s1) and torch.equal(h0, h1)
-    assert tracker.check() > 300 and len(tracker.streams_used()) == 2
-
-
-def test_a_cast_issued_before_the_scale_update_is_caught(pt_ops):
-    """negative control for the rule "layers 0 and 1 cast inline": a prefetcher that already issues layer 1's casts when layer 0 starts
-    reads scales the step's update (inside layer 0) is about to rewrite — the stream model must object"""
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-    tracker, _ = pt_ops
-
-    class Eager(WeightPrefetcher):
-        def _pre(self, idx, module, args):
-            super()._pre(idx, module, args)
-            if idx == 0:
-                self._issue(1)
-
-    layers = torch.nn.ModuleList(_layer(True, seed=3 + i) for i in range(3))
-    Eager(layers)
-    x = torch.randn(2, 6, H, generator=torch.Generator().manual_seed(9)).bfloat16()
-    for step in range(3):
-        for p in layers.parameters():
-            p.grad = None
-        y = x.clone().requires_grad_(True)
-        for layer in layers:
-            y = layer(y)
-        y.float().square().mean().backward()
-    with pytest.raises(AssertionError, match="amax_scale_update (reads|overwrites) a buffer that quantize .* may still be"):
-        tracker.check()

@@ -148,3 +148,66 @@ def test_two_rank_allreduce_of_joined_split_weights(tmp_path):
     want = [model.lnl.query_weight.grad, model.lnl.key_weight.grad, model.lnl.value_weight.grad]
     for g, w in zip(got, want):
         assert torch.allclose(g, w, rtol=1e-5, atol=1e-7)
+
+
+# ------------------------------------------------------------------------------------------------ gradient accumulation (DDP.no_sync)
+def _accum_worker(rank, world, port, out, misuse):
+    os.environ.update(RANK=str(rank), WORLD_SIZE=str(world), LOCAL_RANK=str(rank), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port))
+    dp.init_from_env(backend="gloo")
+    model = _model()
+    reducer = dp.GradAllReducer(model.parameters(), direct_numel=64 * 128, prescaled=True)
+    x = _batch()
+    micro = [x[:4], x[4:]]                                  # two micro-batches of one optimizer step, each sharded over the ranks
+    err = None
+    try:
+        for i, xb in enumerate(micro):
+            mine = dp.shard_tokens(xb.shape[0], rank, world)
+            loss = model(xb[mine.start:mine.stop]).square().sum() * reducer.loss_scale
+            if misuse or i == len(micro) - 1:
+                loss.backward()
+                reducer.finish()
+            else:
+                with reducer.no_sync():
+                    loss.backward()
+    except RuntimeError as e:
+        err = str(e)
+    grads = [p.grad.clone() for p in model.parameters()]
+    # second optimizer step after dropping the gradients: the guard must not fire
+    if not misuse:
+        model.zero_grad(set_to_none=True)
+        (model(x[dp.shard_tokens(6, rank, world).start:dp.shard_tokens(6, rank, world).stop]).square().sum() * reducer.loss_scale).backward()
+        reducer.finish()
+        # zeroed in place: same tensors -> new_step() declares the new accumulation window
+        model.zero_grad(set_to_none=False)
+        reducer.new_step()
+        (model(x[dp.shard_tokens(6, rank, world).start:dp.shard_tokens(6, rank, world).stop]).square().sum() * reducer.loss_scale).backward()
+        reducer.finish()
+    if rank == 0:
+        torch.save({"grads": grads, "err": err, "collectives": reducer.collectives}, out)
+    if err is None:
+        dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_two_rank_gradient_accumulation_with_no_sync(tmp_path):
+    """Two micro-batches per optimizer step: the first under no_sync() (hooks idle), the second reduces the accumulated gradient once ->
+    world-mean of the summed micro-batch gradients == single-process gradient (prescaled SUM: loss * 1/world on every micro-batch)."""
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_accum_worker, args=(2, _free_port(), out, False), nprocs=2, join=True)
+    got = torch.load(out)
+    assert got["err"] is None
+    model = _model()
+    x = _batch()
+    # every rank's loss is a SUM over its shard, scaled by 1/world: the reduced gradient is the global sum / world
+    ((model(x[:4]).square().sum() + model(x[4:]).square().sum()) / 2).backward()
+    for g, p in zip(got["grads"], model.parameters()):
+        assert torch.allclose(g, p.grad, rtol=1e-5, atol=1e-6)
+
+
+def test_accumulating_into_a_reduced_gradient_raises(tmp_path):
+    """Without no_sync() the second backward would add its local gradient onto the already reduced one and reduce the sum again
+    (world * G1 + G2): the reducer refuses."""
+    out = str(tmp_path / "r0.pt")
+    mp.spawn(_accum_worker, args=(2, _free_port(), out, True), nprocs=2, join=True)
+    got = torch.load(out)
+    assert got["err"] is not None and "no_sync" in got["err"]

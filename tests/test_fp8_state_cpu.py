@@ -237,37 +237,110 @@ def test_flush_exchanges_amax_so_every_rank_derives_the_same_scales(tmp_path):
     assert r0["calls"] == r1["calls"] == [3, 3]
 
 
-# ------------------------------------------------------------------------------------------------ weight prefetch, delayed scaling
-def test_prefetch_casts_with_the_slots_and_keys_the_forward_uses(host_only, monkeypatch):
-    """modules.prefetch_weights (prefetch.WeightPrefetcher) under DelayedScaling: the weight of a Linear / LayerNormLinear sits in
-    forward slot 1 of its module, fc1 / fc2 of a LayerNormMLP in slots 1 and 4 (functional.LinearFn / LayerNormMLPFn), cached under
-    (name, recipe key) with a snapshot of the scale_inv they were cast with — what `is_first_microbatch=False` then reuses."""
-    from llm_fp8_b200 import ops
-    seen = []
 
-    def fake_quantize(x, fmt, pool, slot):
-        seen.append((tuple(x.shape), fmt, pool, slot))
-        return ops.QTensor(torch.zeros(x.shape, dtype=torch.uint8), fmt, pool.scale_inv, slot)
 
-    monkeypatch.setattr(ops, "quantize", fake_quantize)
+# ------------------------------------------------------------------------------------------------ saved fp8 copies keep THEIR scale_inv
+class _ScaledOps:
+    """Scale-aware stand-ins for the per-tensor C-ABI wrappers: the "fp8" copy is x * scale (fp32, no rounding), the amax lands in the
+    pool's history row 0, the GEMM de-scales with whatever scale_inv tensor its operands carry.  With the right scale_inv every
+    result is exact up to fp32 rounding; a stale or too-new one is off by the ratio of two scales."""
+
+    @staticmethod
+    def quantize(x, fmt, pool, slot):
+        pool.amax_history[0, slot] = torch.maximum(pool.amax_history[0, slot], x.float().abs().max())
+        return te.ops.QTensor(x.float() * pool.scale[slot], fmt, pool.scale_inv, slot)
+
+    @staticmethod
+    def quantize_bgrad(x, fmt, pool, slot):
+        return _ScaledOps.quantize(x, fmt, pool, slot), x.float().sum(0).to(x.dtype)
+
+    @staticmethod
+    def fp8_gemm(a, a_mn, b, b_mn, M, N, K, bias=None, out=None, accumulate=False, out_dtype=torch.float32, max_ctas=0, residual=None):
+        A = a.data.t() if a_mn else a.data
+        B = b.data.t() if b_mn else b.data
+        d = (A @ B.t()) * (a.scale_inv[a.scale_inv_off] * b.scale_inv[b.scale_inv_off])
+        if bias is not None:
+            d = d + bias.float()
+        return d.to(torch.float32)
+
+
+def test_backward_descales_saved_copies_with_the_scale_they_were_cast_with(host_only, monkeypatch):
+    """fwd(x1), fwd(x2), bwd(2), bwd(1) on one Linear: the second forward applies the pending scale update, so the pool's scale_inv
+    differs from the one x1 / W were cast under; backward 1 must still use the old one (TE clones scale_inv in forward for this;
+    here every update writes a new scale_inv tensor and the graph keeps the version it saw)."""
+    for name in ("quantize", "quantize_bgrad", "fp8_gemm"):
+        monkeypatch.setattr(te.ops, name, getattr(_ScaledOps, name))
+    monkeypatch.setattr(te.ops, "rows_ok", lambda t: True)
+    monkeypatch.setattr(torch.cuda, "current_device", lambda: 0)
     r = DelayedScaling(fp8_format=Format.HYBRID, amax_history_len=4)
-    lin = te.Linear(16, 24, bias=False, params_dtype=torch.bfloat16, device="cpu")
-    qkv = te.LayerNormLinear(16, 32, eps=1e-5, bias=False, normalization="RMSNorm", parameters_split={"query": 16, "key": 8, "value": 8},
-                             params_dtype=torch.bfloat16, device="cpu")
-    mlp = te.LayerNormMLP(16, 32, normalization="RMSNorm", activation="swiglu", params_dtype=torch.bfloat16, device="cpu")
-    for m in (lin, qkv, mlp):
-        m.prefetch_weights(r, CPU)
-    pf = fp8.get_pool(r, True, CPU)
-    s_lin, s_qkv, s_mlp = lin._meta.get(r, CPU), qkv._meta.get(r, CPU), mlp._meta.get(r, CPU)
-    assert [(s, f, p is pf, sl) for s, f, p, sl in seen] == [((24, 16), 0, True, s_lin["f0"] + 1), ((32, 16), 0, True, s_qkv["f0"] + 1),
-                                                             ((64, 16), 0, True, s_mlp["f0"] + 1), ((16, 32), 0, True, s_mlp["f0"] + 4)]
-    assert set(lin._wcache) == {("w", r.key())} and set(qkv._wcache) == {("w", r.key())} and set(mlp._wcache) == {("w1", r.key()), ("w2", r.key())}
-    kept = mlp._wcache[("w2", r.key())]
-    assert kept.scale_inv.numel() == 1 and kept.scale_inv.data_ptr() != pf.scale_inv.data_ptr()      # a snapshot, not the live slot
-    assert qkv.query_weight.data_ptr() == qkv._joined.data_ptr()                                     # cast from the joined buffer, in place
-    # the consuming side: a prefetched module runs its forward with `first=False` once, then lets the copies go
-    mlp._prefetched = True
-    assert mlp._take_prefetched(None, r) == (False, True) and not mlp._prefetched
-    assert mlp._take_prefetched(None, r) == (None, False)
-    mlp._prefetched = True
-    assert mlp._take_prefetched(True, r) == (True, False)          # a caller that manages micro-batches itself keeps control
+    g = torch.Generator().manual_seed(0)
+    lin = te.Linear(32, 48, bias=True, params_dtype=torch.float32)
+    x0 = torch.randn(8, 32, generator=g) * 3
+    with te.fp8_autocast(enabled=True, fp8_recipe=r):        # step 0: records amaxes (scales still 1)
+        lin(x0).sum().backward()
+    lin.zero_grad()
+    x1 = (torch.randn(8, 32, generator=g) * 10).requires_grad_(True)
+    x2 = (torch.randn(8, 32, generator=g) * 100).requires_grad_(True)
+    with te.fp8_autocast(enabled=True, fp8_recipe=r):
+        y1 = lin(x1)                                       # applies step 0's update: scale = 448 / amax(x0)
+    si_1 = fp8.all_pools()[0].scale_inv
+    with te.fp8_autocast(enabled=True, fp8_recipe=r):
+        y2 = lin(x2)                                       # applies y1's amaxes: a different scale, a NEW scale_inv tensor
+    pf = next(p for p in fp8.all_pools() if p.forward)
+    assert pf.scale_inv is not si_1 and not torch.equal(pf.scale_inv[:3], si_1[:3])
+    dy1, dy2 = torch.randn(8, 48, generator=g), torch.randn(8, 48, generator=g)
+    y2.backward(dy2)
+    dw2 = lin.weight.grad.clone()
+    lin.zero_grad()
+    y1.backward(dy1)
+    assert torch.allclose(lin.weight.grad, dy1.t() @ x1.detach(), rtol=1e-4, atol=1e-4)
+    assert torch.allclose(x1.grad, dy1 @ lin.weight.detach(), rtol=1e-4, atol=1e-4)
+    assert torch.allclose(dw2, dy2.t() @ x2.detach(), rtol=1e-4, atol=1e-3)
+    assert torch.allclose(x2.grad, dy2 @ lin.weight.detach(), rtol=1e-4, atol=1e-4)
+
+
+def test_released_slots_are_recycled_and_start_fresh(host_only):
+    """building and dropping models in one process does not exhaust the 4096-slot pools (Fp8Meta.__del__ -> ScalePool.release)"""
+    r = DelayedScaling(fp8_format=Format.E4M3, amax_history_len=4)
+    m = fn.Fp8Meta(3, 2)
+    s = m.get(r, CPU)
+    pf, f0 = s["pf"], s["f0"]
+    pf.scale[f0:f0 + 3] = 7.0
+    pf.amax_history[:, f0:f0 + 3] = 5.0
+    used = pf.used
+    del m, s
+    import gc
+    gc.collect()
+    m2 = fn.Fp8Meta(3, 2)
+    s2 = m2.get(r, CPU)
+    assert s2["f0"] == f0 and pf.used == used
+    assert torch.all(pf.scale[f0:f0 + 3] == 1) and torch.all(pf.amax_history[:, f0:f0 + 3] == 0)
+    m3 = fn.Fp8Meta(6, 4)                      # another width: a fresh range
+    assert m3.get(r, CPU)["f0"] == used
+
+
+def test_fp8_group_binds_the_pool_and_conflicts_raise(host_only):
+    r = DelayedScaling(fp8_format=Format.E4M3, amax_history_len=4)
+    m = fn.Fp8Meta(3, 2)
+    ga, gb = object(), object()
+    with te.fp8_autocast(enabled=True, fp8_recipe=r, fp8_group=ga):
+        s = m.get(r, CPU)
+        fn.Fp8Meta.begin_fwd(s, True)
+    assert s["pf"].group is ga and s["pb"].group is ga
+    with te.fp8_autocast(enabled=True, fp8_recipe=r, fp8_group=gb):
+        with pytest.raises(RuntimeError, match="two different fp8_group"):
+            fn.Fp8Meta.begin_fwd(s, True)
+    with pytest.raises(NotImplementedError):
+        with te.fp8_autocast(enabled=True, fp8_recipe=r, calibrating=True):
+            pass
+
+
+def test_foreign_extra_state_is_ignored_with_a_warning():
+    lin = te.Linear(16, 16, params_dtype=torch.float32)
+    with pytest.warns(UserWarning, match="ignoring an _extra_state"):
+        lin.set_extra_state(torch.arange(10, dtype=torch.uint8))       # what a TE-written checkpoint carries
+    assert lin._pending_extra_state is None
+    lin.set_extra_state(torch.empty(0, dtype=torch.uint8))
+    lin.set_extra_state(None)
+    lin.set_extra_state({"x": 1})
+    assert lin._pending_extra_state == {"x": 1}

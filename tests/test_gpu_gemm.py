@@ -365,3 +365,33 @@ def test_fused_residual_contract_errors():
         ops.fp8_gemm(A, False, B, False, M, N, K, residual=r, out_dtype=torch.float32)
     with pytest.raises(RuntimeError):
         ops.fp8_gemm(A, False, qt(ops, b.t().contiguous(), E4M3, 1.0), True, M, N, K, residual=r)     # dgrad layout: not built
+
+
+# ------------------------------------------------------------------------------------------------ MXFP8 dgrad / wgrad at Llama-3.1-8B shapes
+@pytest.mark.parametrize("name,T,N,K", [("qkv", 6144, 6144, 4096), ("fc2", 6144, 4096, 14336)])
+def test_mxfp8_dgrad_wgrad_at_8b_shapes_vs_oracle_sample(name, T, N, K):
+    """BASELINE.json configs[3] sizes (M = 12 x 512 tokens): operands block-quantised by the ORACLE (oracle_c.c), the block-scaled GEMM in
+    its dgrad (A rowwise K-major, B colwise MN-major) and wgrad (both colwise, MN-major) forms against dequantise -> fp64 matmul on a
+    sample of output rows that touches the first / last tile, a tile boundary and the CTA-pair halves."""
+    from oracle import c_oracle as co
+    ops = _ops()
+    x, w, dy = mx_operands(T, K, 51), mx_operands(N, K, 52), mx_operands(T, N, 53)
+    xo = co.mx_quantize_f32(x.float(), rowwise=False, colwise=True)
+    wo = co.mx_quantize_f32(w.float(), rowwise=False, colwise=True)
+    dyo = co.mx_quantize_f32(dy.float(), rowwise=True, colwise=True)
+
+    def deq_row(o, R, C):
+        return fo.mx_dequantize_rowwise(o["q_row"].view(E4M3), fo.unswizzle_sf(o["sf_row"], R, C // 32))
+
+    def deq_col(o, R, C):
+        return fo.mx_dequantize_colwise(o["q_col"].view(E4M3), fo.unswizzle_sf(o["sf_col"], C, R // 32))
+
+    c = lambda t: t.cuda()      # noqa: E731
+    rows = torch.tensor([0, 1, 127, 128, 255, 256, 3071, 3072, T - 129, T - 1])
+    dx = ops.mxfp8_gemm(c(dyo["q_row"]), c(dyo["sf_row"]), False, c(wo["q_col"]), c(wo["sf_col"]), True, T, K, N, out_dtype=torch.float32)
+    check(dx[rows.cuda()], ref_matmul(deq_row(dyo, T, N)[rows], deq_col(wo, N, K).t()), tol=1e-5)
+    nrows = torch.tensor([0, 1, 127, 128, 255, 256, N // 2 - 1, N // 2, N - 129, N - 1])
+    dw = ops.mxfp8_gemm(c(dyo["q_col"]), c(dyo["sf_col"]), True, c(xo["q_col"]), c(xo["sf_col"]), True, N, K, T, out_dtype=torch.float32)
+    check(dw[nrows.cuda()], ref_matmul(deq_col(dyo, T, N).t()[nrows], deq_col(xo, T, K).t()), tol=1e-5)
+    dwb = ops.mxfp8_gemm(c(dyo["q_col"]), c(dyo["sf_col"]), True, c(xo["q_col"]), c(xo["sf_col"]), True, N, K, T)      # bf16, as the modules ask
+    check(dwb[nrows.cuda()], ref_matmul(deq_col(dyo, T, N).t()[nrows], deq_col(xo, T, K).t()))

@@ -336,45 +336,50 @@ def test_wgrad_side_stream_matches_main_stream():
             assert torch.equal(ta, tb)
 
 
-@pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
-                    reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
-@pytest.mark.parametrize("scenario", ["mxfp8", "default"])
-def test_weight_prefetch_matches_inline_casts(scenario):
-    """prefetch.WeightPrefetcher: layer i+1's weight casts issued on a side stream when layer i starts.  Same kernels, same scale and
-    amax slots -> outputs, input gradients and weight gradients must be bit-identical to the inline run over several steps, with the
-    weights changing between steps (a missing stream dependency would show up as a stale copy); the delayed-scaling state must end
-    up identical too."""
+
+
+def test_two_forwards_per_step_follow_the_oracle_state_machine():
+    """Gradient accumulation WITHOUT is_first_microbatch (the paper's accum-4 runs, paper/conference_101719.tex:222; the reference never
+    passes the argument): two forwards, then the two backwards in reverse order, per optimizer step.  TE updates the scales at every
+    outermost autocast exit / after every module backward; here the update is deferred to the next use of the slots — which is the
+    second forward / second backward of the same step, so the sequence of scales must equal fo.DelayedScalingState driven once per
+    forward and once per backward.  Each backward de-scales the fp8 copies saved by ITS forward with the scale_inv of that forward."""
     import llm_fp8_b200 as te
-    from llm_fp8_b200 import fp8
-    from llm_fp8_b200.layer import LinearPathStack
-    from llm_fp8_b200.prefetch import WeightPrefetcher
-
-    def run(prefetch):
-        te.reset_fp8_state()
-        model = LinearPathStack("llama-3.2-1b", scenario, 5, device="cuda")
-        pf = WeightPrefetcher(model.layers) if prefetch else None
-        out = []
-        for step in range(4):
-            x = rnd((2, 256, model.H), 80 + step).cuda().requires_grad_(True)
-            for p in model.parameters():
-                p.grad = None
-            y = model(x)
-            y.float().pow(2).mean().backward()
-            out.append([y.detach().clone(), x.grad.clone()] + [p.grad.clone() for p in model.parameters()])
-            with torch.no_grad():                     # an optimizer step's worth of change, on the main stream
-                for p in model.parameters():
-                    p.add_(p.grad, alpha=-1e-3)
-        torch.cuda.synchronize()
-        state = [(p.scale[:p.used].clone(), p.amax_history[:, :p.used].clone()) for p in fp8.all_pools()]
-        if pf is not None:
-            assert (pf.issued, pf.consumed) == (9, 9)     # steps 2-4, layers 2-4
-        return out, state
-
-    base, st0 = run(False)
-    pre, st1 = run(True)
-    for a, b in zip(base, pre):
-        for ta, tb in zip(a, b):
-            assert torch.equal(ta, tb)
-    assert len(st0) == len(st1)
-    for (s0, h0), (s1, h1) in zip(st0, st1):
-        assert torch.equal(s0, s1) and torch.equal(h0, h1)
+    te.reset_fp8_state()
+    recipe = te.DelayedScaling(fp8_format=te.Format.HYBRID, amax_history_len=16, amax_compute_algo="max")
+    torch.manual_seed(0)
+    K, N, T = 512, 768, 256
+    lin = te.Linear(K, N, bias=False, params_dtype=torch.bfloat16, device="cuda")
+    w = lin.weight.detach().cpu()
+    fw, bw = DelayedEmu(3, [448.0] * 3), DelayedEmu(2, [57344.0] * 2)
+    for step in range(4):
+        xs = [rnd((T, K), 100 + 2 * step + i, (1.0 + step) * (1 + 3 * i)).cuda().requires_grad_(True) for i in range(2)]
+        dys = [rnd((T, N), 200 + 2 * step + i, 1e-2 * (1 + step) * (1 + 2 * i)).cuda() for i in range(2)]
+        ys, emu = [], []
+        for x in xs:
+            with te.fp8_autocast(enabled=True, fp8_recipe=recipe):
+                ys.append(lin(x))
+            fw.begin()
+            xd, wd = fw.q(x.detach().cpu(), 0, E4M3), fw.q(w, 1, E4M3)
+            fw.dirty = True
+            emu.append((xd, wd))
+        lin.weight.grad = None
+        want_dw = 0
+        for i in (1, 0):
+            ys[i].backward(dys[i])
+            bw.begin()
+            dyd = bw.q(dys[i].cpu(), 0, E5M2)
+            bw.dirty = True
+            xd, wd = emu[i]
+            close(ys[i], xd @ wd.t(), what=f"y[{i}] step {step}")
+            close(xs[i].grad, dyd @ wd, what=f"dx[{i}] step {step}")
+            want_dw = want_dw + dyd.t() @ xd
+        close(lin.weight.grad, want_dw, what=f"accumulated dw step {step}")
+    te.flush_all()
+    fw.begin()
+    bw.begin()
+    s = lin._meta.get(recipe, torch.device("cuda", torch.cuda.current_device()))
+    assert torch.equal(s["pf"].scale[s["f0"]:s["f0"] + 2].cpu(), fw.st.scale[:2])
+    assert torch.equal(s["pf"].amax_history[:, s["f0"]:s["f0"] + 2].cpu(), fw.st.amax_history[:, :2])
+    assert torch.equal(s["pb"].scale[s["b0"]:s["b0"] + 1].cpu(), bw.st.scale[:1])
+    assert torch.equal(s["pb"].amax_history[:, s["b0"]:s["b0"] + 1].cpu(), bw.st.amax_history[:, :1])

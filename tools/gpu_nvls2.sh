@@ -4,6 +4,9 @@
 # after 20 s / 10 s by itself and the process group after 60 / 90 s), so a protocol bug cannot hang the box:
 #   /usr/local/graft/bin/gpurun --gpus 2 --timeout 900 -- 'bash tools/gpu_nvls2.sh'
 mkdir -p gpurun_out
+# data-parallel correctness of the FP8 path (tests/test_gpu_dp2.py): scales identical across ranks, gradients == single GPU on the concatenated batch
+timeout 500 python -m pytest tests/test_gpu_dp2.py tests/test_gpu_comm.py -q -s -m gpu -p no:cacheprovider > gpurun_out/r02_test_dp2.log 2>&1
+echo "test_dp2 exit $?"; grep -E "^\[dp2\]|passed|failed" gpurun_out/r02_test_dp2.log
 LLMFP8_EXPERIMENTAL=1 timeout 280 python -m pytest tests/test_gpu_comm.py -x -q -m gpu -p no:cacheprovider -k nvls > gpurun_out/r02_test_nvls2.log 2>&1
 rc=$?; echo "test_nvls exit $rc"; tail -25 gpurun_out/r02_test_nvls2.log
 [ $rc -ne 0 ] && exit $rc
