@@ -128,7 +128,7 @@ void llmfp8_gemm_force_bn(int bn);
 void llmfp8_gemm_force_cg(int cg);
 /* experiments only: bit 0 skips the MX scale smem->TMEM copies, bit 1 the scale loads (results become wrong); bit 3 = static
  * persistent grid instead of cluster launch control, bit 4 = single TMEM accumulator for MXFP8 at 256-column tiles (results unchanged),
- * bit 5 = overlapped accumulators also under the fused-residual MXFP8 epilogue (not yet run on hardware) */
+ * bit 5 = single accumulator under the fused-residual MXFP8 epilogue (default: overlapped accumulators there too) */
 void llmfp8_gemm_debug(int flags);
 
 /* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */

@@ -63,7 +63,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = OVL also for the fused-residual MX kernel (unverified on hardware)
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
@@ -449,16 +449,17 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                 *reinterpret_cast<uint4*>(sbuf + ((g ^ sw) << 4)) = o;
                             }
                         }
-                        if constexpr (RES) {
-                            // rv is free again: next chunk's segment, under the store below
-                            if (OVL ? (n + 1 < nmine) : (c + 2 < nchunks)) load_residual(c + (walk_down ? -2 : 2));
-                        }
                         ptx::fence_proxy_async();
                         __syncwarp();
                         if (lane == 0) {
                             ptx::tma_store_2d(&map_d, stg, col, row0);
                             ptx::tma_store_commit();
                         }
+                    }
+                    if constexpr (RES) {
+                        // rv is free again: next chunk's segment, under the store above.  Outside the `col < N` guard: the downward walk of
+                        // the OVL kernel meets the chunks past the matrix edge FIRST, and the in-range ones after them still need their segment.
+                        if (OVL ? (n + 1 < nmine) : (c + 2 < nchunks)) load_residual(c + (walk_down ? -2 : 2));
                     }
                 }
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
@@ -686,8 +687,8 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
     // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
-    // (with a fused residual only under debug bit 5: that combination has not run on a GPU yet)
-    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || (g_debug & 32))) ? 1 : 0;
+    // (debug bit 5 keeps the fused-residual kernel on a single accumulator)
+    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || !(g_debug & 32))) ? 1 : 0;
     p.acc_stages = (mx && BN > 192 && !p.acc_overlap) ? 1 : 2;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;

@@ -109,7 +109,7 @@ def _weight_mx(wcache, first, key, weight, need_col: bool) -> "ops.MXTensor":
 # GEMM's last, partial wave leaves idle (an [M, 4096] output at 8B shapes is 5.2 waves of 256 x 256 tiles: 14 % of that launch) and
 # run under the RMSNorm backward / dSwiGLU that follow on the main stream.  The main stream rejoins before backward returns, so
 # autograd (and the gradient all-reduce hooks) see the weight gradient in stream order as before.
-WGRAD_SIDE_STREAM = os.environ.get("LLMFP8_WGRAD_STREAM", "0") == "1"
+WGRAD_SIDE_STREAM = os.environ.get("LLMFP8_WGRAD_STREAM", "1") == "1"
 _side_streams = {}
 
 
@@ -309,12 +309,12 @@ class LayerNormMLPFn(torch.autograd.Function):
 # critical path and the residual loads lengthen it: measured at Llama-3.1-8B shapes, +15 us (proj) / +35 us (fc2) against ~20 us for a
 # separate add (profiles/r01_microbench_llama8b_v4_gemm.jsonl).  The MXFP8 functions therefore add the residual with a plain in-place
 # add after the GEMM unless LLMFP8_MX_EPILOGUE_RESIDUAL=1; the per-tensor GEMM (two accumulators, epilogue hidden) fuses it (+7..10 us).
-MX_EPILOGUE_RESIDUAL = os.environ.get("LLMFP8_MX_EPILOGUE_RESIDUAL", "0") == "1"
+MX_EPILOGUE_RESIDUAL = os.environ.get("LLMFP8_MX_EPILOGUE_RESIDUAL", "1") == "1"
 
 
 # SwiGLU / dSwiGLU fused with the block quantiser (csrc/mx_act_quantize.cu): bit-identical by construction to the two-kernel sequences
 # below, minus the bf16 intermediate's round trip through HBM.  Not yet run on hardware -> off unless LLMFP8_MX_FUSED_ACT=1.
-MX_FUSED_ACT = os.environ.get("LLMFP8_MX_FUSED_ACT", "0") == "1"
+MX_FUSED_ACT = os.environ.get("LLMFP8_MX_FUSED_ACT", "1") == "1"
 
 
 def _mx_gemm_residual(a, sfa, b, sfb, M, N, K, bias, residual):

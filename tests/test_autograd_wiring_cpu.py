@@ -90,6 +90,8 @@ def fake_ops(monkeypatch):
     for name in ("rows_ok", "rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu_bf16", "dswiglu_bf16", "quantize_bgrad_raw"):
         monkeypatch.setattr(ops, name, getattr(_FakeOps, name))
     monkeypatch.setattr(torch.cuda, "is_available", lambda: True)      # fp8_autocast's guard; nothing below touches a device
+    monkeypatch.setattr(fn, "MX_FUSED_ACT", False)          # the two-kernel activation sequence unless a test turns the fused one on
+    monkeypatch.setattr(fn, "MX_EPILOGUE_RESIDUAL", False)
     return _FakeOps
 
 

@@ -310,10 +310,6 @@ def test_rmsnorm_bwd_with_residual_gradient():
 # ------------------------------------------------------------------------------------------------ activation + MX quantiser in one pass
 import os  # noqa: E402
 
-EXPERIMENTAL = pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
-                                  reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
-
-
 def _assert_mx_equal(got, want):
     for name in ("row", "sf_row", "col", "sf_col"):
         g, w = getattr(got, name), getattr(want, name)
@@ -322,7 +318,6 @@ def _assert_mx_equal(got, want):
             assert torch.equal(g, w), f"{name}: {int((g != w).sum())} of {g.numel()} bytes differ"
 
 
-@EXPERIMENTAL
 @pytest.mark.parametrize("M,I", [(128, 128), (256, 512), (1000 // 32 * 32, 1056), (96, 160), (6144, 14336)])
 @pytest.mark.parametrize("kind", ["normal", "heavy", "outlier"])
 def test_mx_swiglu_quantize_matches_two_kernel_sequence(M, I, kind):
@@ -341,7 +336,6 @@ def test_mx_swiglu_quantize_matches_two_kernel_sequence(M, I, kind):
     assert row_only.col is None and torch.equal(row_only.row, want.row) and torch.equal(row_only.sf_row, want.sf_row)
 
 
-@EXPERIMENTAL
 @pytest.mark.parametrize("M,I", [(128, 128), (256, 512), (992, 1152), (96, 384), (6144, 14336)])
 @pytest.mark.parametrize("kind", ["normal", "heavy"])
 def test_mx_dswiglu_quantize_matches_two_kernel_sequence(M, I, kind):
@@ -365,7 +359,6 @@ def test_mx_dswiglu_quantize_matches_two_kernel_sequence(M, I, kind):
     _assert_mx_equal(got2, want)
 
 
-@EXPERIMENTAL
 def test_mx_act_quantize_contract_errors():
     ops = _ops()
     fc1 = torch.zeros(64, 2 * 48, dtype=torch.bfloat16, device="cuda")

@@ -21,6 +21,8 @@ TRACKED = ("rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu
 def tracked_ops(monkeypatch):
     tracker = fake_cuda(monkeypatch)
     monkeypatch.setattr(ops, "rows_ok", _FakeOps.rows_ok)
+    monkeypatch.setattr(fn, "MX_FUSED_ACT", False)          # the stand-ins cover the two-kernel activation sequence
+    monkeypatch.setattr(fn, "MX_EPILOGUE_RESIDUAL", False)
     for name in TRACKED:
         real = getattr(_FakeOps, name)
 
