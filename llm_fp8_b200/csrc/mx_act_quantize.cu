@@ -7,10 +7,10 @@
 // intermediate is kept; what disappears is its round trip through HBM (fwd: 4·M·I of 10.06·M·I bytes, bwd: 8·M·I of 18.1·M·I).
 // Replaces TE's swiglu / dswiglu + mxfp8 cast inside LayerNormMLP(activation="swiglu") under te_llama_mxfp8.py:93.
 //
-// One CTA walks 128 x 128 tiles of the [M, I] index space.  Per tile: TMA loads of the gate, up (and da) tiles -> the activation is
-// computed in place (bf16, into the gate / up buffers) -> the 1x32 and 32x1 block passes of mx_quantize.cu run over those buffers ->
-// e4m3 tiles staged in shared memory -> TMA store; scale tiles (512 B, pre-swizzled for tcgen05.cp) written with 16 B stores.
-// STATUS: written after the round-1 GPU budget was spent — not run on hardware yet.  Opt-in (LLMFP8_MX_FUSED_ACT=1), gated tests.
+// Persistent, warp-specialised CTAs (one per SM): a producer warp streams input tiles through a TMA ring, 16 consumer warps compute the
+// activation in place (bf16, into the gate / up buffers), run the 1x32 and 32x1 block passes of mx_quantize.cu over those buffers, stage
+// the e4m3 tiles in shared memory and TMA-store them; scale tiles (512 B, pre-swizzled for tcgen05.cp) leave with vector stores.
+// Default path of functional.MXLayerNormMLPFn (LLMFP8_MX_FUSED_ACT=0 restores the two-kernel sequence).
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
@@ -21,9 +21,162 @@ constexpr int AT = 128;                     // tile edge
 constexpr int AT_IN_BYTES = AT * AT * 2;    // 32 KB bf16 tile
 constexpr int AT_OUT_BYTES = AT * AT;       // 16 KB e4m3 tile
 
-// Rowwise pass over one bf16 tile in shared memory (row pitch 256 B): thread `t` of 256 owns whole 1x32 blocks.
-// Same arithmetic and shared-memory access order as mx_quantize_kernel<0> (mx_quantize.cu), which stays untouched.
-__device__ __forceinline__ void act_row_pass(const uint8_t* in, uint8_t* out_row, uint8_t* sf_row, int t) {
+// ------------------------------------------------------------------------------------------------ forward: SwiGLU + quantise
+// Warp-specialised like the backward kernel below: a producer warp keeps a 2-deep ring of (gate | up) 128 x 128 bf16 tile pairs in flight
+// with TMA; 16 consumer warps compute a = bf16(silu(gate) * up) in place (into the gate buffer), then threads 0..255 run the colwise and
+// threads 256..511 the rowwise block pass over it.
+constexpr int AF_CONS = 512;
+constexpr int AF_THREADS = AF_CONS + 32;
+constexpr int AF_STAGES = 2;
+struct ActFwdStage {
+    alignas(128) uint8_t g[AT_IN_BYTES];        // gate tile; overwritten in place by a = bf16(silu(gate) * up)
+    uint8_t u[AT_IN_BYTES];                     // up tile
+};
+struct ActFwdSmem {
+    ActFwdStage st[AF_STAGES];
+    alignas(128) uint8_t out_row[AT_OUT_BYTES];
+    alignas(128) uint8_t out_col[AT_OUT_BYTES];
+    alignas(16) uint8_t sf_row[512];
+    alignas(16) uint8_t sf_col[512];
+    alignas(8) uint64_t full[AF_STAGES], empty[AF_STAGES];
+};
+
+template <class Put>
+__device__ __forceinline__ void act_row_pass_f(const uint8_t* in, uint8_t* out_row, int t, Put&& put);
+template <class Put>
+__device__ __forceinline__ void act_col_pass_f(const uint8_t* in, uint8_t* out_col, int t, Put&& put);
+
+__global__ void __launch_bounds__(AF_THREADS, 1) mx_swiglu_quantize_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_u,
+                                                                           const __grid_constant__ CUtensorMap map_row, const __grid_constant__ CUtensorMap map_col,
+                                                                           uint8_t* __restrict__ sf_row, uint8_t* __restrict__ sf_col, int M, int I, int do_row,
+                                                                           int do_col) {
+    extern __shared__ uint8_t smem_raw[];
+    ActFwdSmem& s = *reinterpret_cast<ActFwdSmem*>(smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u));
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tiles_c = (I + AT - 1) / AT, tiles_r = (M + AT - 1) / AT;
+    const int64_t ntiles = static_cast<int64_t>(tiles_c) * tiles_r;
+    const int t0 = static_cast<int>(ntiles * blockIdx.x / gridDim.x), t1 = static_cast<int>(ntiles * (blockIdx.x + 1) / gridDim.x);
+
+    if (tid == 0) {
+        ptx::prefetch_tensormap(&map_g);
+        ptx::prefetch_tensormap(&map_u);
+        for (int i = 0; i < AF_STAGES; i++) {
+            ptx::mbar_init(&s.full[i], 1);
+            ptx::mbar_init(&s.empty[i], 1);
+        }
+        ptx::fence_barrier_init();
+    }
+    __syncthreads();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
+    pdl_launch_dependents();
+
+    if (warp == AF_CONS / 32) {
+        if (lane == 0) {
+            int stage = 0, phase = 0;
+            for (int t = t0; t < t1; t++) {
+                const int c = (t % tiles_c) * AT, r = (t / tiles_c) * AT;
+                ptx::mbar_wait(&s.empty[stage], phase ^ 1);
+                ptx::mbar_arrive_expect_tx(&s.full[stage], 2 * AT_IN_BYTES);
+                ptx::tma_load_2d(&map_g, &s.full[stage], s.st[stage].g, c, r);
+                ptx::tma_load_2d(&map_u, &s.full[stage], s.st[stage].u, c, r);
+                if (++stage == AF_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
+    }
+
+    int stage = 0, phase = 0;
+    for (int t = t0; t < t1; t++) {
+        const int tr = t / tiles_c, tc = t % tiles_c;
+        const int row0 = tr * AT, col0 = tc * AT;
+        if (tid == 0) ptx::tma_store_wait_read<0>();   // the previous tile's stores no longer read out_row / out_col
+        ptx::mbar_wait(&s.full[stage], phase);
+        ActFwdStage& S = s.st[stage];
+
+        // activation pass, in place: 2048 16-byte vectors, 4 per thread, consecutive threads on consecutive vectors.
+        // Arithmetic = swiglu_quant_kernel<FMT_BF16> (swiglu.cu): a = (g * sigmoid(g)) * up, each product rounded, then RNE to bf16.
+#pragma unroll 2
+        for (int i = 0; i < (AT * AT / 8) / AF_CONS; i++) {
+            const int idx = i * AF_CONS + tid;
+            const uint4 vg = reinterpret_cast<const uint4*>(S.g)[idx];
+            const uint4 vu = reinterpret_cast<const uint4*>(S.u)[idx];
+            float g[8], up[8];
+            unpack8(vg, g);
+            unpack8(vu, up);
+            uint32_t o[4];
+#pragma unroll
+            for (int j = 0; j < 4; j++) {
+                const f32x2 sig = sigmoid2_pinned(g[2 * j], g[2 * j + 1]);
+                float lo, hi;
+                upk2(mul2(mul2(pk2(g[2 * j], g[2 * j + 1]), sig), pk2(up[2 * j], up[2 * j + 1])), lo, hi);
+                o[j] = pack_bf16x2(lo, hi);
+            }
+            reinterpret_cast<uint4*>(S.g)[idx] = make_uint4(o[0], o[1], o[2], o[3]);
+        }
+        asm volatile("bar.sync 1, %0;" ::"n"(AF_CONS) : "memory");      // S1: activation tile complete, out buffers and scale staging free
+        if (tid < 256) {
+            if (do_col) act_col_pass_f(S.g, s.out_col, tid, [&](int c, int rb, uint32_t e) { s.sf_col[(c & 31) * 16 + (c >> 5) * 4 + rb] = static_cast<uint8_t>(e); });
+        } else {
+            if (do_row) act_row_pass_f(S.g, s.out_row, tid - 256, [&](int r, int blk, uint32_t e) { s.sf_row[(r & 31) * 16 + (r >> 5) * 4 + blk] = static_cast<uint8_t>(e); });
+        }
+        ptx::fence_proxy_async();                      // generic writes (out tiles) before the async-proxy reads of the stores
+        asm volatile("bar.sync 1, %0;" ::"n"(AF_CONS) : "memory");      // S2
+        if (tid == 0) {
+            if (do_row) ptx::tma_store_2d(&map_row, s.out_row, col0, row0);
+            if (do_col) ptx::tma_store_2d(&map_col, s.out_col, col0, row0);
+            ptx::tma_store_commit();
+            ptx::mbar_arrive(&s.empty[stage]);
+        }
+        if (do_row && tid >= 32 && tid < 64) {
+            const int64_t off = (static_cast<int64_t>(tr) * tiles_c + tc) * 512;
+            reinterpret_cast<uint4*>(sf_row + off)[tid - 32] = reinterpret_cast<const uint4*>(s.sf_row)[tid - 32];
+        }
+        if (do_col && tid >= 64 && tid < 96) {
+            const int64_t off = (static_cast<int64_t>(tc) * tiles_r + tr) * 512;
+            reinterpret_cast<uint4*>(sf_col + off)[tid - 64] = reinterpret_cast<const uint4*>(s.sf_col)[tid - 64];
+        }
+        if (++stage == AF_STAGES) { stage = 0; phase ^= 1; }
+    }
+    if (tid == 0) ptx::tma_store_wait<0>();
+}
+
+// ------------------------------------------------------------------------------------------------ backward: dSwiGLU + quantise (+ dbias)
+// Warp-specialised: one producer warp keeps a 3-deep ring of input tiles (da, gate, up: 64 x 128 bf16 each) in flight with TMA while 16
+// consumer warps work — so the loads of tiles n+1, n+2 run under the arithmetic of tile n (the first version of this kernel was single
+// buffered: per tile 4.3 us of transfer + 4 us of issue-bound arithmetic back to back = 0.48 of HBM bandwidth).
+//   consumers, per tile:  activation pass in place (gate -> dgate, up -> dup, bf16; gate | up are adjacent, so together they form one
+//   virtual 128 x 128 tile V: rows 0..63 dgate, rows 64..127 dup) -> barrier -> threads 0..255 run the 32x1 (colwise) block pass over V,
+//   threads 256..511 the 1x32 (rowwise) one -> barrier -> four TMA stores (dgate half at column col0, dup half at I + col0), the ring
+//   slot goes back to the producer, scale bytes go out from their staging area.
+// Each CTA walks a contiguous range of tiles in COLUMN-major order, so the dbias column sums stay in registers from tile to tile and are
+// folded / atomically added only when the tile column changes (2-3 times per CTA) instead of once per tile.
+constexpr int ABR = 64;                          // tile rows of the [M, I] index space
+constexpr int AB_CONS = 512;                     // consumer threads
+constexpr int AB_THREADS = AB_CONS + 32;         // + the producer warp
+constexpr int AB_STAGES = 3;
+constexpr int AB_IN = ABR * AT * 2;              // 16 KB: one 64 x 128 bf16 tile
+struct ActBwdStage {
+    alignas(128) uint8_t g[AB_IN];               // gate -> dgate  \ contiguous: V
+    uint8_t u[AB_IN];                            // up   -> dup    /
+    uint8_t da[AB_IN];
+};
+struct ActBwdSmem {
+    ActBwdStage st[AB_STAGES];
+    alignas(128) uint8_t out_row[AT_OUT_BYTES];  // V as e4m3, rowwise blocks
+    alignas(128) uint8_t out_col[AT_OUT_BYTES];  // V as e4m3, colwise blocks
+    alignas(16) uint8_t sf_row[2][32][8];        // [half][row & 31][(row >> 5) * 4 + k-block]: 8 consecutive bytes of the swizzled scale tile
+    alignas(16) uint8_t sf_col[2][AT][2];        // [half][column][row block]: 2 consecutive bytes of the swizzled scale tile
+    float part[AB_CONS / 32][2 * AT];            // per-warp column sums of the fp32 dgate (0..127) and dup (128..255) values
+    alignas(8) uint64_t full[AB_STAGES], empty[AB_STAGES];
+};
+static_assert(offsetof(ActBwdStage, u) == AB_IN && offsetof(ActBwdStage, da) == 2 * AB_IN, "gate | up must be adjacent");
+
+__device__ __forceinline__ void bar_consumers() { asm volatile("bar.sync 1, %0;" ::"n"(AB_CONS) : "memory"); }
+
+// rowwise / colwise block passes over a 128 x 128 bf16 tile (row pitch 256 B) with the scale byte handed to `put`; arithmetic and
+// shared-memory access order are act_row_pass / act_col_pass's (and mx_quantize_kernel<0>'s)
+template <class Put>
+__device__ __forceinline__ void act_row_pass_f(const uint8_t* in, uint8_t* out_row, int t, Put&& put) {
 #pragma unroll 1
     for (int i = 0; i < (AT * AT / 32) / 256; i++) {
         const int idx = i * 256 + t;
@@ -59,17 +212,15 @@ __device__ __forceinline__ void act_row_pass(const uint8_t* in, uint8_t* out_row
             }
             *reinterpret_cast<uint2*>(out_row + r * AT + blk * 32 + seg * 8) = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
         }
-        sf_row[(r & 31) * 16 + (r >> 5) * 4 + blk] = static_cast<uint8_t>(e);
+        put(r, blk, e);
     }
 }
-
-// Colwise pass: thread `t` of 256 owns 2 adjacent columns x 32 rows = two 32x1 blocks.
-__device__ __forceinline__ void act_col_pass(const uint8_t* in, uint8_t* out_col, uint8_t* sf_col, int t) {
+template <class Put>
+__device__ __forceinline__ void act_col_pass_f(const uint8_t* in, uint8_t* out_col, int t, Put&& put) {
     const int cp = t & 63, rb = t >> 6;
     uint32_t pk[32];
 #pragma unroll
     for (int r = 0; r < 32; r++) pk[r] = *reinterpret_cast<const uint32_t*>(in + (rb * 32 + r) * (AT * 2) + cp * 4);
-    // |x| of both columns at once as u16x2 integers (non-negative bf16 values order like their bit patterns)
     uint32_t mx = 0;
 #pragma unroll
     for (int r = 0; r < 32; r++) {
@@ -77,9 +228,8 @@ __device__ __forceinline__ void act_col_pass(const uint8_t* in, uint8_t* out_col
         asm("max.u16x2 %0, %1, %2;" : "=r"(m) : "r"(mx), "r"(pk[r] & 0x7fff7fffu));
         mx = m;
     }
-    // NaN patterns (> 0x7f80) must not win: fmaxf in the oracle drops NaN.  Rare: redo both columns the slow way.
     float am0 = bf16lo(mx), am1 = bf16hi(mx);
-    if (((mx & 0xffffu) > 0x7f80u) || ((mx >> 16) > 0x7f80u)) {
+    if (((mx & 0xffffu) > 0x7f80u) || ((mx >> 16) > 0x7f80u)) {      // NaN patterns must not win (fmaxf in the oracle drops NaN): rare slow path
         am0 = am1 = 0.f;
 #pragma unroll
         for (int r = 0; r < 32; r++) {
@@ -95,129 +245,13 @@ __device__ __forceinline__ void act_col_pass(const uint8_t* in, uint8_t* out_col
         upk2(mul2(pk2(bf16lo(pk[r]), bf16hi(pk[r])), inv2), lo, hi);
         *reinterpret_cast<uint16_t*>(out_col + (rb * 32 + r) * AT + cp * 2) = static_cast<uint16_t>(cvt_fp8x2<FMT_E4M3>(lo, hi));
     }
-    const int c0 = cp * 2, c1 = cp * 2 + 1;
-    sf_col[(c0 & 31) * 16 + (c0 >> 5) * 4 + rb] = static_cast<uint8_t>(e0);
-    sf_col[(c1 & 31) * 16 + (c1 >> 5) * 4 + rb] = static_cast<uint8_t>(e1);
+    put(cp * 2, rb, e0);
+    put(cp * 2 + 1, rb, e1);
 }
-
-// ------------------------------------------------------------------------------------------------ forward: SwiGLU + quantise
-struct ActFwdSmem {
-    alignas(128) uint8_t g[AT_IN_BYTES];        // gate tile; overwritten in place by a = bf16(silu(gate) * up)
-    alignas(128) uint8_t u[AT_IN_BYTES];        // up tile
-    alignas(128) uint8_t out_row[AT_OUT_BYTES];
-    alignas(128) uint8_t out_col[AT_OUT_BYTES];
-    alignas(16) uint8_t sf_row[512];
-    alignas(16) uint8_t sf_col[512];
-    alignas(8) uint64_t full_g, full_u;
-};
-
-// 97 KB of shared memory per CTA: two CTAs per SM, each single-buffered — the two CTAs overlap each other's load and compute phases,
-// and within a CTA the up tile of the next tile is requested as soon as the activation pass is done with it, the gate tile once the
-// block passes have read the activation.
-__global__ void __launch_bounds__(256, 2) mx_swiglu_quantize_kernel(const __grid_constant__ CUtensorMap map_g, const __grid_constant__ CUtensorMap map_u,
-                                                                    const __grid_constant__ CUtensorMap map_row, const __grid_constant__ CUtensorMap map_col,
-                                                                    uint8_t* __restrict__ sf_row, uint8_t* __restrict__ sf_col, int M, int I, int do_row,
-                                                                    int do_col) {
-    extern __shared__ uint8_t smem_raw[];
-    ActFwdSmem& s = *reinterpret_cast<ActFwdSmem*>(smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u));
-    const int tid = threadIdx.x;
-    const int tiles_c = (I + AT - 1) / AT, tiles_r = (M + AT - 1) / AT;
-    const int ntiles = tiles_c * tiles_r;
-
-    if (tid == 0) {
-        ptx::prefetch_tensormap(&map_g);
-        ptx::prefetch_tensormap(&map_u);
-        ptx::mbar_init(&s.full_g, 1);
-        ptx::mbar_init(&s.full_u, 1);
-        ptx::fence_barrier_init();
-    }
-    __syncthreads();
-    pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
-    pdl_launch_dependents();
-    if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
-        const int t = blockIdx.x;
-        ptx::mbar_arrive_expect_tx(&s.full_g, AT_IN_BYTES);
-        ptx::tma_load_2d(&map_g, &s.full_g, s.g, (t % tiles_c) * AT, (t / tiles_c) * AT);
-        ptx::mbar_arrive_expect_tx(&s.full_u, AT_IN_BYTES);
-        ptx::tma_load_2d(&map_u, &s.full_u, s.u, (t % tiles_c) * AT, (t / tiles_c) * AT);
-    }
-
-    int it = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-        const uint32_t phase = it & 1;
-        const int tr = t / tiles_c, tc = t % tiles_c;
-        const int row0 = tr * AT, col0 = tc * AT;
-        const int tn = t + gridDim.x;
-        if (tid == 0) ptx::tma_store_wait_read<0>();   // the previous tile's stores no longer read out_row / out_col
-        ptx::mbar_wait(&s.full_g, phase);
-        ptx::mbar_wait(&s.full_u, phase);
-
-        // activation pass, in place: 2048 16-byte vectors, 8 per thread, consecutive threads on consecutive vectors.
-        // Arithmetic = swiglu_quant_kernel<FMT_BF16> (swiglu.cu): a = (g * sigmoid(g)) * up, each product rounded, then RNE to bf16.
-#pragma unroll 2
-        for (int i = 0; i < (AT * AT / 8) / 256; i++) {
-            const int idx = i * 256 + tid;
-            const uint4 vg = reinterpret_cast<const uint4*>(s.g)[idx];
-            const uint4 vu = reinterpret_cast<const uint4*>(s.u)[idx];
-            float g[8], up[8];
-            unpack8(vg, g);
-            unpack8(vu, up);
-            uint32_t o[4];
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                const f32x2 sig = sigmoid2_pinned(g[2 * j], g[2 * j + 1]);
-                float lo, hi;
-                upk2(mul2(mul2(pk2(g[2 * j], g[2 * j + 1]), sig), pk2(up[2 * j], up[2 * j + 1])), lo, hi);
-                o[j] = pack_bf16x2(lo, hi);
-            }
-            reinterpret_cast<uint4*>(s.g)[idx] = make_uint4(o[0], o[1], o[2], o[3]);
-        }
-        __syncthreads();                               // S1: activation tile complete, up buffer dead, out buffers free
-        if (tid == 0 && tn < ntiles) {
-            ptx::mbar_arrive_expect_tx(&s.full_u, AT_IN_BYTES);
-            ptx::tma_load_2d(&map_u, &s.full_u, s.u, (tn % tiles_c) * AT, (tn / tiles_c) * AT);
-        }
-        if (do_row) act_row_pass(s.g, s.out_row, s.sf_row, tid);
-        if (do_col) act_col_pass(s.g, s.out_col, s.sf_col, tid);
-        ptx::fence_proxy_async();                      // generic writes (out tiles, the in-place activation) before async-proxy reads / writes
-        __syncthreads();                               // S2
-        if (tid == 0) {
-            if (do_row) ptx::tma_store_2d(&map_row, s.out_row, col0, row0);
-            if (do_col) ptx::tma_store_2d(&map_col, s.out_col, col0, row0);
-            ptx::tma_store_commit();
-            if (tn < ntiles) {
-                ptx::mbar_arrive_expect_tx(&s.full_g, AT_IN_BYTES);
-                ptx::tma_load_2d(&map_g, &s.full_g, s.g, (tn % tiles_c) * AT, (tn / tiles_c) * AT);
-            }
-        }
-        if (do_row && tid >= 32 && tid < 64) {
-            const int64_t off = (static_cast<int64_t>(tr) * tiles_c + tc) * 512;
-            reinterpret_cast<uint4*>(sf_row + off)[tid - 32] = reinterpret_cast<const uint4*>(s.sf_row)[tid - 32];
-        }
-        if (do_col && tid >= 64 && tid < 96) {
-            const int64_t off = (static_cast<int64_t>(tc) * tiles_r + tr) * 512;
-            reinterpret_cast<uint4*>(sf_col + off)[tid - 64] = reinterpret_cast<const uint4*>(s.sf_col)[tid - 64];
-        }
-    }
-    if (tid == 0) ptx::tma_store_wait<0>();
-}
-
-// ------------------------------------------------------------------------------------------------ backward: dSwiGLU + quantise (+ dbias)
-constexpr int AB_THREADS = 512;             // warps 0-7 quantise the dgate tile, warps 8-15 the dup tile, all 16 run the activation pass
-struct ActBwdSmem {
-    alignas(128) uint8_t da[AT_IN_BYTES];
-    alignas(128) uint8_t g[AT_IN_BYTES];         // gate tile -> dgate (bf16), in place
-    alignas(128) uint8_t u[AT_IN_BYTES];         // up tile   -> dup   (bf16), in place
-    alignas(128) uint8_t out_row[2][AT_OUT_BYTES];
-    alignas(128) uint8_t out_col[2][AT_OUT_BYTES];
-    alignas(16) uint8_t sf_row[2][512];
-    alignas(16) uint8_t sf_col[2][512];
-    float part[AB_THREADS / 32][2 * AT];         // per-warp column sums of the fp32 dgate (0..127) and dup (128..255) values
-    alignas(8) uint64_t full_da, full_gu;
-};
 
 // Output matrix dfc1 is [M, 2I] = (dgate | dup): the dgate tile of (tr, tc) lands at columns col0, the dup tile at I + col0 (I % 128 == 0,
-// so both start on a scale-tile boundary).  ~179 KB of shared memory: one CTA per SM, 16 warps.
+// so both start on a scale-tile boundary).  Row tiles are 64 rows: two of them fill one 128-row scale tile, and the row-tile count is
+// rounded up to even so that every scale tile is written whole (rows past M come zero-filled from TMA and leave clipped).
 __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(const __grid_constant__ CUtensorMap map_da, const __grid_constant__ CUtensorMap map_g,
                                                                             const __grid_constant__ CUtensorMap map_u, const __grid_constant__ CUtensorMap map_row,
                                                                             const __grid_constant__ CUtensorMap map_col, uint8_t* __restrict__ sf_row,
@@ -226,52 +260,96 @@ __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(cons
     extern __shared__ uint8_t smem_raw[];
     ActBwdSmem& s = *reinterpret_cast<ActBwdSmem*>(smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u));
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int tiles_c = I / AT, tiles_r = (M + AT - 1) / AT;      // tiles of the [M, I] index space; the output has 2 * tiles_c tile columns
-    const int ntiles = tiles_c * tiles_r;
+    const int tiles_c = I / AT, tiles_r128 = (M + AT - 1) / AT, tiles_r = 2 * tiles_r128;
+    const int64_t ntiles = static_cast<int64_t>(tiles_c) * tiles_r;
+    const int t0 = static_cast<int>(ntiles * blockIdx.x / gridDim.x), t1 = static_cast<int>(ntiles * (blockIdx.x + 1) / gridDim.x);
 
     if (tid == 0) {
         ptx::prefetch_tensormap(&map_da);
         ptx::prefetch_tensormap(&map_g);
         ptx::prefetch_tensormap(&map_u);
-        ptx::mbar_init(&s.full_da, 1);
-        ptx::mbar_init(&s.full_gu, 1);
+        for (int i = 0; i < AB_STAGES; i++) {
+            ptx::mbar_init(&s.full[i], 1);
+            ptx::mbar_init(&s.empty[i], 1);
+        }
         ptx::fence_barrier_init();
     }
     __syncthreads();
     pdl_wait();                // LLMFP8_PDL build only (common.cuh): the prologue above ran under the previous kernel's tail
     pdl_launch_dependents();
-    if (tid == 0 && static_cast<int>(blockIdx.x) < ntiles) {
-        const int t = blockIdx.x;
-        const int c = (t % tiles_c) * AT, r = (t / tiles_c) * AT;
-        ptx::mbar_arrive_expect_tx(&s.full_da, AT_IN_BYTES);
-        ptx::tma_load_2d(&map_da, &s.full_da, s.da, c, r);
-        ptx::mbar_arrive_expect_tx(&s.full_gu, 2 * AT_IN_BYTES);
-        ptx::tma_load_2d(&map_g, &s.full_gu, s.g, c, r);
-        ptx::tma_load_2d(&map_u, &s.full_gu, s.u, c, r);
+
+    if (warp == AB_CONS / 32) {
+        // ================================ producer: one lane keeps the ring full
+        if (lane == 0) {
+            int stage = 0, phase = 0;
+            for (int t = t0; t < t1; t++) {
+                const int c = (t / tiles_r) * AT, r = (t % tiles_r) * ABR;
+                ptx::mbar_wait(&s.empty[stage], phase ^ 1);
+                ptx::mbar_arrive_expect_tx(&s.full[stage], 3 * AB_IN);
+                ptx::tma_load_2d(&map_g, &s.full[stage], s.st[stage].g, c, r);
+                ptx::tma_load_2d(&map_u, &s.full[stage], s.st[stage].u, c, r);
+                ptx::tma_load_2d(&map_da, &s.full[stage], s.st[stage].da, c, r);
+                if (++stage == AB_STAGES) { stage = 0; phase ^= 1; }
+            }
+        }
+        return;
     }
 
-    const f32x2 one2 = pk2(1.0f, 1.0f);
-    int it = 0;
-    for (int t = blockIdx.x; t < ntiles; t += gridDim.x, it++) {
-        const uint32_t phase = it & 1;
-        const int tr = t / tiles_c, tc = t % tiles_c;
-        const int row0 = tr * AT, col0 = tc * AT;
-        const int tn = t + gridDim.x;
-        if (tid == 0) ptx::tma_store_wait_read<0>();   // the previous tile's stores no longer read the out buffers
-        ptx::mbar_wait(&s.full_da, phase);
-        ptx::mbar_wait(&s.full_gu, phase);
-
-        // activation pass, in place: 2048 16-byte vectors, 4 per thread; thread -> fixed 8-column segment (tid & 15), rows i*32 + tid/16.
-        // Arithmetic = dswiglu_quant_kernel<FMT_BF16> (swiglu.cu); the column sums take the fp32 values before the bf16 rounding.
-        f32x2 sg[4], su[4];
+    // ==================================== consumers
+    const f32x2 one2 = pk2(1.0f, 1.0f), zero2 = pk2(0.f, 0.f);
+    f32x2 sg[4], su[4];
 #pragma unroll
-        for (int j = 0; j < 4; j++) sg[j] = su[j] = pk2(0.f, 0.f);
-#pragma unroll 1
-        for (int i = 0; i < (AT * AT / 8) / AB_THREADS; i++) {
-            const int idx = i * AB_THREADS + tid;
-            const uint4 vd = reinterpret_cast<const uint4*>(s.da)[idx];
-            const uint4 vg = reinterpret_cast<const uint4*>(s.g)[idx];
-            const uint4 vu = reinterpret_cast<const uint4*>(s.u)[idx];
+    for (int j = 0; j < 4; j++) sg[j] = su[j] = zero2;
+    auto flush_dbias = [&](int tcf) {
+        // lanes l and l ^ 16 hold the same 8-column segment (rows differ): fold them, one row of `part` per warp, then 256 threads add up
+#pragma unroll
+        for (int j = 0; j < 4; j++) {
+            float glo, ghi, ulo, uhi;
+            upk2(sg[j], glo, ghi);
+            upk2(su[j], ulo, uhi);
+            glo += __shfl_xor_sync(0xffffffffu, glo, 16);
+            ghi += __shfl_xor_sync(0xffffffffu, ghi, 16);
+            ulo += __shfl_xor_sync(0xffffffffu, ulo, 16);
+            uhi += __shfl_xor_sync(0xffffffffu, uhi, 16);
+            if (lane < 16) {
+                s.part[warp][lane * 8 + 2 * j] = glo;
+                s.part[warp][lane * 8 + 2 * j + 1] = ghi;
+                s.part[warp][AT + lane * 8 + 2 * j] = ulo;
+                s.part[warp][AT + lane * 8 + 2 * j + 1] = uhi;
+            }
+            sg[j] = su[j] = zero2;
+        }
+        bar_consumers();
+        if (tid < 2 * AT) {
+            float acc = 0.f;
+#pragma unroll
+            for (int w = 0; w < AB_CONS / 32; w++) acc += s.part[w][tid];
+            const int col = tid < AT ? tcf * AT + tid : I + tcf * AT + (tid - AT);
+            atomicAdd(dbias_ws + col, acc);
+        }
+        bar_consumers();
+    };
+
+    int stage = 0, phase = 0, cur_tc = -1;
+    for (int t = t0; t < t1; t++) {
+        const int tc = t / tiles_r, tr = t % tiles_r;
+        const int row0 = tr * ABR, col0 = tc * AT;
+        if (dbias_ws && tc != cur_tc) {
+            if (cur_tc >= 0) flush_dbias(cur_tc);
+            cur_tc = tc;
+        }
+        if (tid == 0) ptx::tma_store_wait_read<0>();   // the previous tile's stores no longer read the out buffers
+        ptx::mbar_wait(&s.full[stage], phase);
+        ActBwdStage& S = s.st[stage];
+
+        // activation pass, in place: 1024 16-byte vectors, 2 per thread; thread -> fixed 8-column segment (tid & 15), rows tid / 16 and + 32.
+        // Arithmetic = dswiglu_quant_kernel<FMT_BF16> (swiglu.cu); the column sums take the fp32 values before the bf16 rounding.
+#pragma unroll
+        for (int i = 0; i < (ABR * AT / 8) / AB_CONS; i++) {
+            const int idx = i * AB_CONS + tid;
+            const uint4 vd = reinterpret_cast<const uint4*>(S.da)[idx];
+            const uint4 vg = reinterpret_cast<const uint4*>(S.g)[idx];
+            const uint4 vu = reinterpret_cast<const uint4*>(S.u)[idx];
             float dy[8], g[8], up[8];
             unpack8(vd, dy);
             unpack8(vg, g);
@@ -293,77 +371,46 @@ __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(cons
                 upk2(du, lo, hi);
                 ou[j] = pack_bf16x2(lo, hi);
             }
-            reinterpret_cast<uint4*>(s.g)[idx] = make_uint4(og[0], og[1], og[2], og[3]);
-            reinterpret_cast<uint4*>(s.u)[idx] = make_uint4(ou[0], ou[1], ou[2], ou[3]);
+            reinterpret_cast<uint4*>(S.g)[idx] = make_uint4(og[0], og[1], og[2], og[3]);
+            reinterpret_cast<uint4*>(S.u)[idx] = make_uint4(ou[0], ou[1], ou[2], ou[3]);
         }
-        if (dbias_ws) {
-            // lanes l and l ^ 16 hold the same column segment (rows differ): fold them, then one row of `part` per warp
-#pragma unroll
-            for (int j = 0; j < 4; j++) {
-                float glo, ghi, ulo, uhi;
-                upk2(sg[j], glo, ghi);
-                upk2(su[j], ulo, uhi);
-                glo += __shfl_xor_sync(0xffffffffu, glo, 16);
-                ghi += __shfl_xor_sync(0xffffffffu, ghi, 16);
-                ulo += __shfl_xor_sync(0xffffffffu, ulo, 16);
-                uhi += __shfl_xor_sync(0xffffffffu, uhi, 16);
-                if (lane < 16) {
-                    s.part[warp][lane * 8 + 2 * j] = glo;
-                    s.part[warp][lane * 8 + 2 * j + 1] = ghi;
-                    s.part[warp][AT + lane * 8 + 2 * j] = ulo;
-                    s.part[warp][AT + lane * 8 + 2 * j + 1] = uhi;
-                }
-            }
+        bar_consumers();                               // S1: V complete, out buffers and scale staging free
+        if (tid < 256) {
+            if (do_col) act_col_pass_f(S.g, s.out_col, tid, [&](int c, int rb, uint32_t e) { s.sf_col[rb >> 1][c][rb & 1] = static_cast<uint8_t>(e); });
+        } else {
+            if (do_row) act_row_pass_f(S.g, s.out_row, tid - 256, [&](int r, int blk, uint32_t e) {
+                s.sf_row[r >> 6][r & 31][((r >> 5) & 1) * 4 + blk] = static_cast<uint8_t>(e);
+            });
         }
-        __syncthreads();                               // S1: dgate / dup tiles complete, da buffer dead, out buffers free, part[] complete
-        if (tid == 0 && tn < ntiles) {
-            ptx::mbar_arrive_expect_tx(&s.full_da, AT_IN_BYTES);
-            ptx::tma_load_2d(&map_da, &s.full_da, s.da, (tn % tiles_c) * AT, (tn / tiles_c) * AT);
-        }
-        if (dbias_ws && tid < 2 * AT) {
-            float acc = 0.f;
-#pragma unroll
-            for (int w = 0; w < AB_THREADS / 32; w++) acc += s.part[w][tid];
-            const int col = tid < AT ? col0 + tid : I + col0 + (tid - AT);
-            atomicAdd(dbias_ws + col, acc);
-        }
-        {
-            const int grp = tid >> 8, lt = tid & 255;          // grp 0: dgate, grp 1: dup
-            const uint8_t* src = grp ? s.u : s.g;
-            if (do_row) act_row_pass(src, s.out_row[grp], s.sf_row[grp], lt);
-            if (do_col) act_col_pass(src, s.out_col[grp], s.sf_col[grp], lt);
-        }
-        ptx::fence_proxy_async();
-        __syncthreads();                               // S2
+        ptx::fence_proxy_async();                      // generic writes (out tiles) before the async-proxy reads of the stores
+        bar_consumers();                               // S2: out tiles and scale staging complete, the ring slot is dead
         if (tid == 0) {
             if (do_row) {
-                ptx::tma_store_2d(&map_row, s.out_row[0], col0, row0);
-                ptx::tma_store_2d(&map_row, s.out_row[1], I + col0, row0);
+                ptx::tma_store_2d(&map_row, s.out_row, col0, row0);
+                ptx::tma_store_2d(&map_row, s.out_row + ABR * AT, I + col0, row0);
             }
             if (do_col) {
-                ptx::tma_store_2d(&map_col, s.out_col[0], col0, row0);
-                ptx::tma_store_2d(&map_col, s.out_col[1], I + col0, row0);
+                ptx::tma_store_2d(&map_col, s.out_col, col0, row0);
+                ptx::tma_store_2d(&map_col, s.out_col + ABR * AT, I + col0, row0);
             }
             ptx::tma_store_commit();
-            if (tn < ntiles) {
-                const int c = (tn % tiles_c) * AT, r = (tn / tiles_c) * AT;
-                ptx::mbar_arrive_expect_tx(&s.full_gu, 2 * AT_IN_BYTES);
-                ptx::tma_load_2d(&map_g, &s.full_gu, s.g, c, r);
-                ptx::tma_load_2d(&map_u, &s.full_gu, s.u, c, r);
-            }
+            ptx::mbar_arrive(&s.empty[stage]);
         }
-        // scale tiles: warps 1, 2 -> rowwise (dgate, dup), warps 3, 4 -> colwise (dgate, dup); one 16 B vector per lane
-        if (do_row && warp >= 1 && warp <= 2) {
-            const int h = warp - 1;
-            const int64_t off = (static_cast<int64_t>(tr) * (2 * tiles_c) + h * tiles_c + tc) * 512;
-            reinterpret_cast<uint4*>(sf_row + off)[lane] = reinterpret_cast<const uint4*>(s.sf_row[h])[lane];
+        // scale bytes: this 64-row tile fills half of a 128-row scale tile (row groups 0-1 or 2-3 of the swizzled layout)
+        const int upper = (row0 & 64) ? 1 : 0;
+        if (do_row && tid >= 32 && tid < 96) {
+            const int j = tid - 32, h = j >> 5, q = j & 31;
+            const int64_t off = (static_cast<int64_t>(row0 >> 7) * (2 * tiles_c) + h * tiles_c + tc) * 512 + q * 16 + upper * 8;
+            *reinterpret_cast<uint2*>(sf_row + off) = *reinterpret_cast<const uint2*>(s.sf_row[h][q]);
         }
-        if (do_col && warp >= 3 && warp <= 4) {
-            const int h = warp - 3;
-            const int64_t off = (static_cast<int64_t>(h * tiles_c + tc) * tiles_r + tr) * 512;
-            reinterpret_cast<uint4*>(sf_col + off)[lane] = reinterpret_cast<const uint4*>(s.sf_col[h])[lane];
+        if (do_col && tid >= 256) {
+            const int j = tid - 256, h = j >> 7, c = j & 127;
+            const int64_t off = (static_cast<int64_t>(h * tiles_c + tc) * tiles_r128 + (row0 >> 7)) * 512 + (c & 31) * 16 + (c >> 5) * 4 + upper * 2;
+            *reinterpret_cast<uint16_t*>(sf_col + off) = *reinterpret_cast<const uint16_t*>(s.sf_col[h][c]);
         }
+        if (++stage == AB_STAGES) { stage = 0; phase ^= 1; }
     }
+    if (dbias_ws && cur_tc >= 0) flush_dbias(cur_tc);
     if (tid == 0) ptx::tma_store_wait<0>();
 }
 
@@ -402,11 +449,11 @@ int launch_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q
     if (rc) return rc;
     const int ntiles = static_cast<int>(((M + AT - 1) / AT) * ((I + AT - 1) / AT));
     const int smem = sizeof(ActFwdSmem) + 128;
-    const int cap = sm_count() * 2;
+    const int cap = sm_count();
     const int grid = ntiles < cap ? ntiles : cap;
     cudaError_t e = cudaFuncSetAttribute(mx_swiglu_quantize_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
     if (e != cudaSuccess) { set_error("mx_swiglu_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-    LLMFP8_LAUNCH((mx_swiglu_quantize_kernel), grid, 256, smem, stream, m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, (int)M, (int)I, do_row, do_col);
+    LLMFP8_LAUNCH((mx_swiglu_quantize_kernel), grid, AF_THREADS, smem, stream, m_g, m_u, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, (int)M, (int)I, do_row, do_col);
     LLMFP8_LAUNCH_CHECK("mx_swiglu_quantize");
     return 0;
 }
@@ -427,17 +474,18 @@ int launch_mx_dswiglu_quantize(const void* da, const void* fc1_out, int64_t M, i
     }
     const uint16_t* base = static_cast<const uint16_t*>(fc1_out);
     CUtensorMap m_da, m_g, m_u, m_row, m_col;
-    int rc = make_tensor_map_2d(&m_da, da, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, I * 2, AT, AT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    int rc = make_tensor_map_2d(&m_da, da, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, I * 2, AT, ABR, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&m_g, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, 2 * I * 2, AT, AT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    rc = make_tensor_map_2d(&m_g, base, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, 2 * I * 2, AT, ABR, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&m_u, base + I, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, 2 * I * 2, AT, AT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    rc = make_tensor_map_2d(&m_u, base + I, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, I, M, 2 * I * 2, AT, ABR, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&m_row, do_row ? q_row : q_col, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, 2 * I, M, 2 * I, AT, AT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    rc = make_tensor_map_2d(&m_row, do_row ? q_row : q_col, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, 2 * I, M, 2 * I, AT, ABR, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    rc = make_tensor_map_2d(&m_col, do_col ? q_col : q_row, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, 2 * I, M, 2 * I, AT, AT, CU_TENSOR_MAP_SWIZZLE_NONE);
+    rc = make_tensor_map_2d(&m_col, do_col ? q_col : q_row, CU_TENSOR_MAP_DATA_TYPE_UINT8, 1, 2 * I, M, 2 * I, AT, ABR, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
-    const int ntiles = static_cast<int>(((M + AT - 1) / AT) * (I / AT));
+    const int64_t ntiles64 = 2 * ((M + AT - 1) / AT) * (I / AT);
+    const int ntiles = ntiles64 > (1 << 30) ? (1 << 30) : static_cast<int>(ntiles64);
     const int smem = sizeof(ActBwdSmem) + 128;
     const int cap = sm_count();
     const int grid = ntiles < cap ? ntiles : cap;
