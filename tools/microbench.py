@@ -34,6 +34,58 @@ def peaks():
     return 6650.0, 1590.0, "fallback"
 
 
+class NvmlClocks:
+    """SM clock / power / throttle reasons sampled every 5 ms by a thread through NVML while one kernel is being timed, so that every
+    line this tool emits carries its own clock record (bench.ClockSampler's nvidia-smi loop is too coarse for a 10-launch timing)."""
+
+    def __init__(self, index=0):
+        self.ok = False
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = float(pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM))
+            self.ok = True
+        except Exception as e:  # noqa: BLE001
+            self.err = str(e)[:100]
+
+    def __enter__(self):
+        import threading
+        self.sm, self.pw, self.reasons, self._stop = [], [], 0, False
+        if self.ok:
+            def loop():
+                import time
+                while not self._stop:
+                    try:
+                        self.sm.append(float(self.nv.nvmlDeviceGetClockInfo(self.h, self.nv.NVML_CLOCK_SM)))
+                        self.pw.append(self.nv.nvmlDeviceGetPowerUsage(self.h) / 1000.0)
+                        self.reasons |= int(self.nv.nvmlDeviceGetCurrentClocksEventReasons(self.h))
+                    except Exception:  # noqa: BLE001
+                        pass
+                    time.sleep(0.005)
+            self._t = threading.Thread(target=loop, daemon=True)
+            self._t.start()
+        return self
+
+    def __exit__(self, *a):
+        self._stop = True
+        if self.ok:
+            self._t.join()
+
+    def record(self):
+        if not self.ok or not self.sm:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvml unavailable"]}
+        nv = self.nv
+        names = [("hw_slowdown", nv.nvmlClocksEventReasonHwSlowdown), ("hw_thermal_slowdown", nv.nvmlClocksEventReasonHwThermalSlowdown),
+                 ("sw_thermal_slowdown", nv.nvmlClocksEventReasonSwThermalSlowdown), ("sw_power_cap", nv.nvmlClocksEventReasonSwPowerCap)]
+        s = sorted(self.sm)
+        return {"sm_mhz": s[len(s) // 2], "sm_mhz_min": s[0], "sm_max_mhz": self.max_mhz, "power_w_max": max(self.pw) if self.pw else None,
+                "samples": len(s), "reasons": [n for n, bit in names if self.reasons & bit]}
+
+
+_clocks = None
+_last_clocks = None
 _flush = None
 
 
@@ -45,19 +97,24 @@ def flush_l2():
 
 
 def timeit(fn, iters=10, warm=3, flush=True):
+    global _clocks, _last_clocks
+    if _clocks is None:
+        _clocks = NvmlClocks(torch.cuda.current_device())
     for _ in range(warm):
         fn()
     torch.cuda.synchronize()
     ts = []
-    for _ in range(iters):
-        if flush:
-            flush_l2()
-        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        a.record()
-        fn()
-        b.record()
-        torch.cuda.synchronize()
-        ts.append(a.elapsed_time(b))
+    with _clocks:
+        for _ in range(iters):
+            if flush:
+                flush_l2()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            fn()
+            b.record()
+            torch.cuda.synchronize()
+            ts.append(a.elapsed_time(b))
+    _last_clocks = _clocks.record()
     ts.sort()
     return ts[len(ts) // 2], ts[0]
 
@@ -91,6 +148,7 @@ def main():
         rec["bn"] = args.bn
         rec["cg"] = args.cg
         rec["debug"] = args.debug
+        rec["clocks"] = _last_clocks          # sampled while THIS kernel was being timed
         if args.tag:
             rec["tag"] = args.tag
         print(json.dumps(rec), flush=True)
@@ -143,10 +201,9 @@ def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
             int(10.0625 * M * I))
         mem("K3mb dswiglu_bf16 + mx_quantize row+col [M,2I] (two kernels)", lambda: ops.mx_quantize(ops.dswiglu_bf16(da, fc1)[0], True, True),
             int(18.125 * M * I))
-        if args.experimental:
-            mem("K3m mx_swiglu_quantize row+col [M,I] (one pass)", lambda: ops.mx_swiglu_quantize(fc1, True, True), int(6.0625 * M * I))
-            if I % 128 == 0:
-                mem("K3mb mx_dswiglu_quantize row+col [M,2I] (one pass)", lambda: ops.mx_dswiglu_quantize(da, fc1, True, True), int(10.125 * M * I))
+        mem("K3m mx_swiglu_quantize row+col [M,I] (one pass)", lambda: ops.mx_swiglu_quantize(fc1, True, True), int(6.0625 * M * I))
+        if I % 128 == 0:
+            mem("K3mb mx_dswiglu_quantize row+col [M,2I] (one pass)", lambda: ops.mx_dswiglu_quantize(da, fc1, True, True), int(10.125 * M * I))
         mem("copy bf16 [M,2I] (torch, reference point)", lambda: fc1.clone(), 4 * M * 2 * I)
         mem("copy bf16 [M,H] (torch, reference point for the short kernels)", lambda: x.clone(), 4 * M * H)
         del x, w1, fc1, da
