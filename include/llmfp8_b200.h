@@ -90,6 +90,11 @@ int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, v
 /* same with an explicit row pitch of x (elements; >= cols, % 8 == 0): quantises a column slice of a wider matrix in place */
 int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
                           const float* rsigma, const void* gamma, void* stream);
+/* llmfp8_mx_quantize_ld of a gradient dY [rows, cols] (plain mode, colwise copy required) that also emits the bias gradient: bgrad_ws
+ * fp32 [cols] workspace, bgrad_bf16 [cols] = column sums of dY — taken from the tiles while they are in shared memory instead of a second
+ * pass over dY.  [tex.bgrad_quantize with an MXFP8 quantizer] */
+int llmfp8_mx_quantize_bgrad(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                             float* bgrad_ws, void* bgrad_bf16, void* stream);
 int llmfp8_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, float eps, void* stream);
 /* K3m: SwiGLU + MXFP8 quantiser in one pass.  fc1_out bf16 [M, 2I] (gate | up) -> a = bf16(silu(gate) * up) [M, I], never written to
  * memory -> rowwise and/or colwise MXFP8 copies of a (layouts as llmfp8_mx_quantize).  Bit-identical to llmfp8_swiglu_quant_fwd(fmt = bf16)

@@ -37,6 +37,7 @@ _PROTOTYPES = {
     "llmfp8_amax_scale_update": [vp, vp, vp, vp, i32, i32, i32, vp],
     "llmfp8_mx_quantize": [vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_mx_quantize_ld": [vp, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp],
+    "llmfp8_mx_quantize_bgrad": [vp, i64, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_mx_swiglu_quantize": [vp, i64, i64, vp, vp, vp, vp, vp],
     "llmfp8_mx_dswiglu_quantize": [vp, vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_rsigma": [vp, vp, i64, i64, f32, vp],
@@ -127,6 +128,9 @@ def _work(name: str, a):
     if name == "llmfp8_mx_dswiglu_quantize":      # read da + gate | up (6 B per [M, I] element), write the copies + scales of [M, 2I]
         mi = float(a[2]) * a[3]
         return "byte", 6.0 * mi + 2.0 * (mi + mi / 32) * ((a[4] is not None) + (a[6] is not None))
+    if name == "llmfp8_mx_quantize_bgrad":
+        rc = float(a[2]) * a[3]
+        return "byte", 2.0 * rc + (rc + rc / 32) * ((a[4] is not None) + (a[6] is not None))
     if name == "llmfp8_mx_quantize_ld":
         rc = float(a[2]) * a[3]
         return "byte", 2.0 * rc + (rc + rc / 32) * ((a[4] is not None) + (a[6] is not None))

@@ -104,7 +104,7 @@ int launch_rmsnorm_bwd(const void*, const void*, const void*, const float*, cons
 int rmsnorm_bwd_grid(int64_t);
 int launch_swiglu_quant_fwd(const void*, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
 int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
-int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, cudaStream_t);
+int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, float*, void*, cudaStream_t);
 int launch_mx_swiglu_quantize(const void*, int64_t, int64_t, void*, void*, void*, void*, cudaStream_t);
 int launch_mx_dswiglu_quantize(const void*, const void*, int64_t, int64_t, void*, void*, void*, void*, float*, void*, cudaStream_t);
 int launch_fp8_gemm(const void*, int64_t, int, int, const void*, int64_t, int, int, void*, int64_t, int, int, int, int, const float*, const float*,
@@ -172,11 +172,16 @@ int llmfp8_amax_scale_update(float* amax_history, float* scale, float* scale_inv
 }
 int llmfp8_mx_quantize(const void* x, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
                        const void* gamma, void* stream) {
-    return launch_mx_quantize(x, cols, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+    return launch_mx_quantize(x, cols, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, nullptr, nullptr, S(stream));
 }
 int llmfp8_mx_quantize_ld(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
                           const float* rsigma, const void* gamma, void* stream) {
-    return launch_mx_quantize(x, ldx, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, S(stream));
+    return launch_mx_quantize(x, ldx, rows, cols, q_row, sf_row, q_col, sf_col, rsigma, gamma, nullptr, nullptr, S(stream));
+}
+int llmfp8_mx_quantize_bgrad(const void* x, int64_t ldx, int64_t rows, int64_t cols, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                             float* bgrad_ws, void* bgrad_bf16, void* stream) {
+    if (!bgrad_ws || !bgrad_bf16) { set_error("mx_quantize_bgrad: bgrad workspace and output are required"); return -1; }
+    return launch_mx_quantize(x, ldx, rows, cols, q_row, sf_row, q_col, sf_col, nullptr, nullptr, bgrad_ws, bgrad_bf16, S(stream));
 }
 int llmfp8_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col, void* stream) {
     return launch_mx_swiglu_quantize(fc1_out, M, I, q_row, sf_row, q_col, sf_col, S(stream));

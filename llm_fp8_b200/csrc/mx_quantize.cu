@@ -25,14 +25,18 @@ struct MxSmem {
     alignas(16) uint8_t sf_row[512];
     alignas(16) uint8_t sf_col[512];
     float rs[MXT];
+    float colsum[4][MXT];                   // BG: per row-group column sums of the tile
     alignas(8) uint64_t full[2];
 };
 
-template <int MODE /*0 plain, 1 rmsnorm*/>
+// BG (plain mode, colwise copy requested): also accumulates the column sums of x into bgrad_ws (fp32 [C], zeroed by the host) — the bias
+// gradient of a Linear whose dY is being quantised, taken from the tile while it is in shared memory instead of a second pass over dY.
+template <int MODE /*0 plain, 1 rmsnorm*/, bool BG = false>
 __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant__ CUtensorMap map_in, const __grid_constant__ CUtensorMap map_row,
                                                           const __grid_constant__ CUtensorMap map_col, uint8_t* __restrict__ sf_row,
                                                           uint8_t* __restrict__ sf_col, const float* __restrict__ rsigma,
-                                                          const uint16_t* __restrict__ gamma, int R, int C, int do_row, int do_col) {
+                                                          const uint16_t* __restrict__ gamma, int R, int C, int do_row, int do_col,
+                                                          float* __restrict__ bgrad_ws) {
     extern __shared__ uint8_t smem_raw[];
     // pointer arithmetic (not an integer round trip) so the compiler keeps the shared address space: LDS / STS, not generic LD / ST
     MxSmem& s = *reinterpret_cast<MxSmem*>(smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u));
@@ -180,6 +184,16 @@ __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant_
                         am1 = fmaxf(am1, fabsf(bf16hi(pk[r])));
                     }
                 }
+                if constexpr (BG) {
+                    float s0 = 0.f, s1 = 0.f;           // rows past R come zero-filled from TMA
+#pragma unroll
+                    for (int r = 0; r < 32; r++) {
+                        s0 += bf16lo(pk[r]);
+                        s1 += bf16hi(pk[r]);
+                    }
+                    s.colsum[rb][cp * 2] = s0;
+                    s.colsum[rb][cp * 2 + 1] = s1;
+                }
                 const uint32_t e0 = e8m0_from_amax(am0), e1 = e8m0_from_amax(am1);
                 const f32x2 inv2 = pk2(e8m0_inv_scale(e0), e8m0_inv_scale(e1));
 #pragma unroll
@@ -208,14 +222,24 @@ __global__ void __launch_bounds__(256) mx_quantize_kernel(const __grid_constant_
             const int64_t off = (static_cast<int64_t>(tc) * tiles_r + tr) * 512;
             reinterpret_cast<uint4*>(sf_col + off)[tid - 64] = reinterpret_cast<const uint4*>(s.sf_col)[tid - 64];
         }
+        if constexpr (BG) {
+            if (tid >= 128 && col0 + (tid - 128) < C) {
+                const int c = tid - 128;
+                atomicAdd(bgrad_ws + col0 + c, (s.colsum[0][c] + s.colsum[1][c]) + (s.colsum[2][c] + s.colsum[3][c]));
+            }
+        }
     }
     if (tid == 0) ptx::tma_store_wait<0>();
 }
 
 // sf_row: u8 [ceil(R/128)*128 * ceil(C/128)*4]; sf_col: u8 [ceil(C/128)*128 * ceil(R/128)*4]
 // ldx: row pitch of x in elements (>= C, multiple of 8): a column slice of a wider matrix is quantised in place, without a copy
+int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t stream);
+
+// bgrad_ws (fp32 [C]) / bgrad_bf16 ([C]) together or both null: column sums of x (the bias gradient when x is a Linear's dY); needs the
+// colwise copy (the sums ride in its pass) and the plain mode.
 int launch_mx_quantize(const void* x, int64_t ldx, int64_t R, int64_t C, void* q_row, void* sf_row, void* q_col, void* sf_col, const float* rsigma,
-                       const void* gamma, cudaStream_t stream) {
+                       const void* gamma, float* bgrad_ws, void* bgrad_bf16, cudaStream_t stream) {
     const int do_row = q_row != nullptr, do_col = q_col != nullptr;
     LLMFP8_REQUIRE(do_row || do_col, "mx_quantize: nothing to produce");
     LLMFP8_REQUIRE(!do_row || (C % 32 == 0 && sf_row), "mx_quantize: rowwise needs cols %% 32 == 0 (got %lld) and a scale buffer", (long long)C);
@@ -224,7 +248,13 @@ int launch_mx_quantize(const void* x, int64_t ldx, int64_t R, int64_t C, void* q
     LLMFP8_REQUIRE(ldx >= C && ldx % 8 == 0 && reinterpret_cast<uintptr_t>(x) % 16 == 0, "mx_quantize: row pitch %lld must be >= cols, a multiple of 8, x 16 B aligned", (long long)ldx);
     LLMFP8_REQUIRE((rsigma == nullptr) == (gamma == nullptr), "mx_quantize: rsigma and gamma go together");
     LLMFP8_REQUIRE(R < (1ll << 31) && C < (1ll << 31), "mx_quantize: dims too large");
+    LLMFP8_REQUIRE((bgrad_ws == nullptr) == (bgrad_bf16 == nullptr), "mx_quantize: bgrad workspace and output go together");
+    LLMFP8_REQUIRE(!bgrad_ws || (do_col && !rsigma), "mx_quantize: the bias gradient rides in the colwise pass of the plain mode");
     if (R == 0 || C == 0) return 0;
+    if (bgrad_ws) {
+        cudaError_t e0 = cudaMemsetAsync(bgrad_ws, 0, sizeof(float) * C, stream);
+        if (e0 != cudaSuccess) { set_error("mx_quantize: memset: %s", cudaGetErrorString(e0)); return (int)e0; }
+    }
     CUtensorMap m_in, m_row, m_col;
     int rc = make_tensor_map_2d(&m_in, x, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, C, R, ldx * 2, MXT, MXT, CU_TENSOR_MAP_SWIZZLE_NONE);
     if (rc) return rc;
@@ -241,12 +271,19 @@ int launch_mx_quantize(const void* x, int64_t ldx, int64_t R, int64_t C, void* q
         e = cudaFuncSetAttribute(mx_quantize_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) { set_error("mx_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
         LLMFP8_LAUNCH((mx_quantize_kernel<1>), grid, 256, smem, stream, m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, rsigma, (const uint16_t*)gamma,
-                                                           (int)R, (int)C, do_row, do_col);
+                                                           (int)R, (int)C, do_row, do_col, nullptr);
+    } else if (bgrad_ws) {
+        e = cudaFuncSetAttribute(mx_quantize_kernel<0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+        if (e != cudaSuccess) { set_error("mx_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
+        LLMFP8_LAUNCH((mx_quantize_kernel<0, true>), grid, 256, smem, stream, m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, nullptr, nullptr, (int)R, (int)C,
+                                                                 do_row, do_col, bgrad_ws);
+        LLMFP8_LAUNCH_CHECK("mx_quantize");
+        return launch_f32_to_bf16(bgrad_ws, bgrad_bf16, C, stream);
     } else {
         e = cudaFuncSetAttribute(mx_quantize_kernel<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
         if (e != cudaSuccess) { set_error("mx_quantize: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
         LLMFP8_LAUNCH((mx_quantize_kernel<0>), grid, 256, smem, stream, m_in, m_row, m_col, (uint8_t*)sf_row, (uint8_t*)sf_col, nullptr, nullptr, (int)R, (int)C,
-                                                           do_row, do_col);
+                                                           do_row, do_col, nullptr);
     }
     LLMFP8_LAUNCH_CHECK("mx_quantize");
     return 0;

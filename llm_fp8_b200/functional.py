@@ -325,10 +325,11 @@ def _mx_gemm_residual(a, sfa, b, sfb, M, N, K, bias, residual):
     return y.add_(residual)
 
 
-def _mx_bgrad(dy2: torch.Tensor) -> torch.Tensor:
-    """bias gradient for the MXFP8 path: the per-tensor K2b kernel's column sums, its fp8 output discarded."""
-    _, bgrad = ops.quantize_bgrad_raw(dy2, 0, None, None)
-    return bgrad
+def _mx_quantize_dy(dy2: torch.Tensor, want_bgrad: bool):
+    """row + col MXFP8 copies of dY and (for a biased Linear) the bias gradient from the same pass over dY"""
+    if want_bgrad:
+        return ops.mx_quantize_bgrad(dy2)
+    return ops.mx_quantize(dy2, True, True), None
 
 
 class MXLinearFn(torch.autograd.Function):
@@ -363,8 +364,7 @@ class MXLinearFn(torch.autograd.Function):
         x_col, x_sfc, w_col, w_sfc, x2, ln_weight, rsigma = ctx.saved_tensors
         M, N, K = ctx.dims
         dy2 = _2d(dy).contiguous()
-        dbias = _mx_bgrad(dy2) if ctx.has_bias else None
-        dyq = ops.mx_quantize(dy2, True, True)
+        dyq, dbias = _mx_quantize_dy(dy2, ctx.has_bias)
         # dgrad: dX[M,K] = dY[M,N] W[N,K]: dY rowwise (blocks along N), W colwise (blocks along N), W read MN-major
         wg = _SideWgrad(dy2.device)
         dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N)
@@ -414,8 +414,7 @@ class MXLayerNormMLPFn(torch.autograd.Function):
         x2, ln_weight, rsigma, ln_col, ln_sfc, w1_col, w1_sfc, fc1, a_col, a_sfc, w2_col, w2_sfc = ctx.saved_tensors
         M, H, I = ctx.dims
         dy2 = _2d(dy).contiguous()
-        db2 = _mx_bgrad(dy2) if ctx.has_bias else None
-        dyq = ops.mx_quantize(dy2, True, True)
+        dyq, db2 = _mx_quantize_dy(dy2, ctx.has_bias)
         da = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w2_col, w2_sfc, True, M, I, H)                       # fc2 dgrad
         if MX_FUSED_ACT and I % 128 == 0:
             dfq, db1 = ops.mx_dswiglu_quantize(da, fc1, True, True, want_dbias=ctx.has_bias)

@@ -254,6 +254,19 @@ def mx_quantize(x: torch.Tensor, rowwise: bool = True, colwise: bool = True, rsi
     return out
 
 
+def mx_quantize_bgrad(x: torch.Tensor, rowwise: bool = True):
+    """mx_quantize(x, rowwise, colwise=True) of a gradient dY [R, C] plus its column sums (the bias gradient), in one pass."""
+    x = _req(x, torch.bfloat16)
+    R, C = x.shape
+    out = _mx_out(R, C, rowwise, True, x.device)
+    ws = torch.empty(C, dtype=torch.float32, device=x.device)
+    bgrad = torch.empty(C, dtype=torch.bfloat16, device=x.device)
+    rc = _lib.load().llmfp8_mx_quantize_bgrad(x.data_ptr(), C, R, C, _p(out.row), _p(out.sf_row), out.col.data_ptr(), out.sf_col.data_ptr(), ws.data_ptr(),
+                                              bgrad.data_ptr(), _stream(x))
+    _lib.check(rc, "mx_quantize_bgrad")
+    return out, bgrad
+
+
 # ------------------------------------------------------------------------------------------ GEMMs
 def fp8_gemm(a: QTensor, a_mn: bool, b: QTensor, b_mn: bool, M: int, N: int, K: int, bias: Optional[torch.Tensor] = None,
              out: Optional[torch.Tensor] = None, accumulate: bool = False, out_dtype: torch.dtype = torch.bfloat16, max_ctas: int = 0,

@@ -80,14 +80,14 @@ class _FakeOps:
         return out.bfloat16(), (out.sum(0).bfloat16() if want_dbias else None)
 
     @staticmethod
-    def quantize_bgrad_raw(x, fmt, scale, amax):
-        return None, x.float().sum(0).bfloat16()
+    def mx_quantize_bgrad(x, rowwise=True):
+        return _FakeOps.mx_quantize(x, rowwise, True), x.float().sum(0).bfloat16()
 
 
 @pytest.fixture
 def fake_ops(monkeypatch):
     _FakeOps.calls = []
-    for name in ("rows_ok", "rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu_bf16", "dswiglu_bf16", "quantize_bgrad_raw"):
+    for name in ("rows_ok", "rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu_bf16", "dswiglu_bf16", "mx_quantize_bgrad"):
         monkeypatch.setattr(ops, name, getattr(_FakeOps, name))
     monkeypatch.setattr(torch.cuda, "is_available", lambda: True)      # fp8_autocast's guard; nothing below touches a device
     monkeypatch.setattr(fn, "MX_FUSED_ACT", False)          # the two-kernel activation sequence unless a test turns the fused one on

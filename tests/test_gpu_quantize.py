@@ -240,6 +240,24 @@ def test_mx_quantize(shape):
     assert only_row.col is None and torch.equal(only_row.row.cpu(), out.row.cpu())
 
 
+@pytest.mark.parametrize("shape", [(6144, 4096), (256, 384), (96, 160), (992, 1056)])
+def test_mx_quantize_bgrad(shape):
+    """llmfp8_mx_quantize_bgrad: the block quantiser of a gradient dY with the bias gradient (column sums) taken from the tiles in shared
+    memory — bytes and scales bit-identical to the oracle (as the plain quantiser), sums against the oracle's column sum."""
+    ops = _ops()
+    R, C = shape
+    x = (gen(shape, 12, "heavy") * 1e-2).bfloat16()
+    want = co.mx_quantize_f32(x.float())
+    out, bgrad = ops.mx_quantize_bgrad(dev(x))
+    assert_fp8_equal(out.row, want["q_row"], E4M3)
+    assert torch.equal(out.sf_row.cpu(), want["sf_row"])
+    assert_fp8_equal(out.col, want["q_col"], E4M3)
+    assert torch.equal(out.sf_col.cpu(), want["sf_col"])
+    ref = co.colsum_bf16(x)
+    tol = 1e-2 * ref.abs().max().item() + 1e-6
+    assert (bgrad.float().cpu() - ref).abs().max().item() <= tol
+
+
 @pytest.mark.parametrize("shape", [(6144, 4096), (160, 2048), (64, 5120)])
 def test_mx_rmsnorm_quantize(shape):
     ops = _ops()

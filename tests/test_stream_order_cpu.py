@@ -14,7 +14,7 @@ from test_autograd_wiring_cpu import H, _FakeOps, _layer
 from llm_fp8_b200 import dp, ops
 from llm_fp8_b200 import functional as fn
 
-TRACKED = ("rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu_bf16", "dswiglu_bf16", "quantize_bgrad_raw")
+TRACKED = ("rmsnorm_rsigma", "mx_quantize", "mxfp8_gemm", "rmsnorm_bwd", "swiglu_bf16", "dswiglu_bf16", "mx_quantize_bgrad")
 
 
 @pytest.fixture
