@@ -387,6 +387,33 @@ def main():
     value = world * flops_step / (ms_step * 1e-3) / 1e12
     e2e_value = world * flops_step / (ms_e2e * 1e-3) / 1e12
 
+    # ---- where a step's time goes on the main stream: forward | backward (its GEMMs compete with the gradient all-reduces for SMs,
+    # HBM and power at N > 1) | the wait for the reductions still outstanding when backward has returned (the exposed tail).  Three
+    # untimed steps, events on the launching stream, max over ranks — the split the scaling loss is attributed with.
+    def timeline_step():
+        ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+        x = x_dev.detach().requires_grad_(True)
+        ev[0].record()
+        y = model(x)
+        loss = y.float().square().mean()
+        ev[1].record()
+        (loss * reducer.loss_scale if reducer is not None and reducer.prescaled else loss).backward()
+        ev[2].record()
+        if reducer is not None:
+            reducer.finish()
+        ev[3].record()
+        zero()
+        return ev
+    sync_all()
+    tl = [timeline_step() for _ in range(3)]
+    sync_all()
+    parts = [sum(e[i].elapsed_time(e[i + 1]) for e in tl) / len(tl) for i in range(3)]
+    if world > 1:
+        t = torch.tensor(parts, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        parts = t.tolist()
+    timeline = {"forward_ms": parts[0], "backward_ms": parts[1], "reduce_tail_ms": parts[2], "how": "CUDA events on the main stream, 3 steps, max over ranks"}
+
     # ---- roofline leg: every C-ABI launch of one more step bracketed by CUDA events on the launching stream
     roof, roof_q, shares = None, None, None
     if not a.no_roofline and rank != 0:
@@ -450,7 +477,7 @@ def main():
                        "experiments": {k: os.environ[k] for k in ("LLMFP8_GEMM_DEBUG", "LLMFP8_MX_EPILOGUE_RESIDUAL", "LLMFP8_MX_FUSED_ACT",
                                                                   "LLMFP8_WGRAD_STREAM", "LLMFP8_FUSE_RESIDUAL", "LLMFP8_JOIN_SPLIT_WEIGHTS", "LLMFP8_PDL", "LLMFP8_GEMM_FORCE_CG", "LLMFP8_GEMM_FORCE_BN", "NCCL_CGA_CLUSTER_SIZE", "NCCL_MAX_CTAS", "LLMFP8_GRAD_BUCKET_MB", "LLMFP8_NVLS_REDUCE", "LLMFP8_NVLS_CTAS", "LLMFP8_NVLS_CHUNK_MB", "LLMFP8_GRAPH_DP", "LLMFP8_NVLS_AMAX") if k in os.environ}},
             "e2e": {"value": e2e_value, "unit": UNIT, "ms_per_step": ms_e2e, "h2d_bytes_per_step": x_host.numel() * 2, "d2h_bytes_per_step": 4},
-            "gpu_launches": int(launches), "clocks": clocks, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
+            "gpu_launches": int(launches), "clocks": clocks, "timeline": timeline, "roofline": roof, "roofline_quantize": roof_q, "kernel_time_shares": shares,
             "cpu_baseline": cpu,
         }
         print(json.dumps(line), flush=True)

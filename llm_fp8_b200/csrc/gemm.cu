@@ -63,7 +63,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL)
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
@@ -694,6 +694,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;
     int stages = (SMEM_BUDGET - fixed) / stage_bytes;
     if (stages > MAX_STAGES) stages = MAX_STAGES;
+    if ((g_debug & 64) && stages > 5) stages = 5;      // experiment: the per-tensor kernel on the ring depth the MX kernel gets
     p.stages = stages;
     const int smem_bytes = fixed + stages * stage_bytes;
 

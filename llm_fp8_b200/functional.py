@@ -165,6 +165,32 @@ def wgrad_out(key: int, N: int, K: int, dtype: torch.dtype) -> Optional[torch.Te
     return home.view(N, K)          # a fresh alias: autograd keeps it as .grad without a copy (sole owner, contiguous)
 
 
+def _slice_of(x: torch.Tensor, x2: torch.Tensor):
+    """x2 ([M, K], rows spaced) is columns [off, off + K) of a contiguous [M, W] matrix that x is a view of -> (W, off), else None.
+    A plain Linear fed such a slice (the attention stand-in's query columns of the fused qkv output, layer._QuerySlice) can then hand
+    its input gradient back as the same slice of a zero-padded [M, W] buffer — written in place by the dgrad GEMM's TMA stores — and
+    the slicing op's backward returns that buffer instead of concatenating dq with zeros."""
+    b = x._base
+    if x2.is_contiguous() or b is None or not b.is_contiguous() or b.dim() < 2:
+        return None
+    W = b.shape[-1]
+    off = x.storage_offset() - b.storage_offset()
+    if x2.stride(0) != W or not (0 <= off <= W - x2.shape[1]) or off % 8 or b.numel() != x2.shape[0] * W:
+        return None
+    return W, off
+
+
+def _padded_dx(M: int, K: int, wide, dtype, device) -> torch.Tensor:
+    W, off = wide
+    buf = torch.empty((M, W), dtype=dtype, device=device)
+    if off:
+        buf[:, :off].zero_()
+    if off + K < W:
+        buf[:, off + K:].zero_()
+    buf._llmfp8_pad = (off, K)
+    return buf[:, off:off + K]
+
+
 def _wgrad(dyq, xq, N, K, T, weight):
     """dW[N,K] = dY^T X over T tokens; both operands read MN-major from the forward/backward fp8 copies."""
     return ops.fp8_gemm(dyq, True, xq, True, N, K, T, out_dtype=weight.dtype)
@@ -204,6 +230,7 @@ class LinearFn(torch.autograd.Function):
             ctx.wkey = weight.data_ptr()
             ctx.needs = (x.requires_grad, weight.requires_grad)
             ctx.has_residual = residual is not None
+            ctx.wide = _slice_of(x, x2) if ln_weight is None else None
             ctx.w_si = (wq.scale_inv, wq.scale_inv_off)
             ctx.si = pf.scale_inv             # the version the saved fp8 bytes were cast under (ScalePool.flush replaces, never rewrites, it)
         ctx.set_materialize_grads(False)
@@ -229,7 +256,8 @@ class LinearFn(torch.autograd.Function):
         else:
             dyq = ops.quantize(dy2, bf, pb, b0 + 0)
         wg = _SideWgrad(dy2.device)
-        dx = ops.fp8_gemm(dyq, False, wq, True, M, K, N)                  # dgrad: contraction over N, W read MN-major
+        dx = ops.fp8_gemm(dyq, False, wq, True, M, K, N,                   # dgrad: contraction over N, W read MN-major
+                          out=_padded_dx(M, K, ctx.wide, dy2.dtype, dy2.device) if ctx.wide is not None and dres is None else None)
         dw = wg.run(lambda: ops.fp8_gemm(dyq, True, xq, True, N, K, M, out=wgrad_out(ctx.wkey, N, K, ctx.wdtype), out_dtype=ctx.wdtype))   # wgrad: contraction over tokens
         dgamma = None
         if ln_weight is not None:
@@ -353,6 +381,7 @@ class MXLinearFn(torch.autograd.Function):
             ctx.shape, ctx.dims, ctx.wdtype = x.shape, (M, N, K), weight.dtype
             ctx.wkey = weight.data_ptr()
             ctx.has_residual = residual is not None
+            ctx.wide = _slice_of(x, x2) if ln_weight is None else None
         ctx.set_materialize_grads(False)
         y = y.reshape(*x.shape[:-1], N)
         return (y, x.view_as(x)) if passthrough else y
@@ -367,7 +396,8 @@ class MXLinearFn(torch.autograd.Function):
         dyq, dbias = _mx_quantize_dy(dy2, ctx.has_bias)
         # dgrad: dX[M,K] = dY[M,N] W[N,K]: dY rowwise (blocks along N), W colwise (blocks along N), W read MN-major
         wg = _SideWgrad(dy2.device)
-        dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N)
+        dx = ops.mxfp8_gemm(dyq.row, dyq.sf_row, False, w_col, w_sfc, True, M, K, N,
+                            out=_padded_dx(M, K, ctx.wide, dy2.dtype, dy2.device) if ctx.wide is not None and dres is None else None)
         # wgrad: dW[N,K] = dY^T X: both colwise (blocks along tokens), both MN-major
         dw = wg.run(lambda: ops.mxfp8_gemm(dyq.col, dyq.sf_col, True, x_col, x_sfc, True, N, K, M, out=wgrad_out(ctx.wkey, N, K, ctx.wdtype), out_dtype=ctx.wdtype))
         dgamma = None

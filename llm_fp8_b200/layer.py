@@ -63,6 +63,13 @@ class _QuerySlice(torch.autograd.Function):
     def backward(ctx, dq):
         if ctx.rest == 0:
             return dq, None
+        # the Linear that consumed the slice hands dq over as columns [0, q) of a zero-padded [M, q + rest] buffer its dgrad GEMM wrote
+        # in place (functional._padded_dx): that buffer IS the gradient of qkv
+        b = dq._base
+        W = dq.shape[-1] + ctx.rest
+        if b is not None and getattr(b, "_llmfp8_pad", None) == (0, dq.shape[-1]) and b.shape[-1] == W and b.is_contiguous() \
+                and b.numel() == dq.numel() // dq.shape[-1] * W:
+            return b.view(*dq.shape[:-1], W), None
         return torch.cat((dq, dq.new_zeros(*dq.shape[:-1], ctx.rest)), dim=-1), None
 
 

@@ -40,6 +40,13 @@ def _req_rows(t: torch.Tensor, dtype=None):
     return t, t.stride(0)
 
 
+def _req_out(t: torch.Tensor):
+    """GEMM output: contiguous, or a column slice of a wider row-major matrix (the TMA store descriptor carries the row pitch)."""
+    if t.dim() == 2 and t.is_cuda and not t.is_contiguous():
+        return _req_rows(t)[0]
+    return _req(t)
+
+
 def rows_ok(t: torch.Tensor) -> bool:
     """True when `t` ([R, C]) can be read in place by the strided quantisers (else the caller makes it contiguous)."""
     return (t.dim() == 2 and t.stride(1) == 1 and t.stride(0) >= t.shape[1] and t.stride(0) % 8 == 0 and t.data_ptr() % 16 == 0
@@ -278,7 +285,7 @@ def fp8_gemm(a: QTensor, a_mn: bool, b: QTensor, b_mn: bool, M: int, N: int, K: 
         if accumulate:
             raise RuntimeError("accumulate=True needs an output tensor")
         out = torch.empty((M, N), dtype=out_dtype, device=dev)
-    _req(out)
+    _req_out(out)
     if out.dtype not in (torch.bfloat16, torch.float32):
         raise RuntimeError("fp8_gemm output must be bf16 or fp32")
     lda, ldb = a.data.shape[-1], b.data.shape[-1]
@@ -306,7 +313,7 @@ def mxfp8_gemm(a: torch.Tensor, sfa: torch.Tensor, a_mn: bool, b: torch.Tensor, 
         if accumulate:
             raise RuntimeError("accumulate=True needs an output tensor")
         out = torch.empty((M, N), dtype=out_dtype, device=dev)
-    _req(out)
+    _req_out(out)
     if residual is not None:
         residual, ldr = _req_rows(residual, torch.bfloat16)
         if tuple(residual.shape) != (M, N) or out.dtype != torch.bfloat16 or accumulate:

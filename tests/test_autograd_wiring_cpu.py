@@ -50,6 +50,11 @@ class _FakeOps:
         if residual is not None:
             assert residual.shape == (M, N)
             d = d + residual.float()
+        if out is not None:
+            assert out.shape == (M, N) and out.stride(1) == 1 and not accumulate
+            _FakeOps.calls.append("gemm:out" + (":pitched" if not out.is_contiguous() else ""))
+            out.copy_(d)
+            return out
         return d.to(out_dtype)
 
     @staticmethod
@@ -279,3 +284,31 @@ def test_fused_activation_branch_is_wired_like_the_two_kernel_sequence(fake_ops,
     assert used == (["fwd", "bwd"] if ffn % 128 == 0 else ["fwd"])
     for a, b in zip(base, fused):
         assert torch.equal(a, b)
+
+
+def test_query_slice_gradient_is_handed_over_without_a_copy(fake_ops):
+    """layer._QuerySlice (the attention stand-in) + proj Linear: the dgrad GEMM writes dq straight into columns [0, q) of a zero-padded
+    [M, q + 2kv] buffer (functional._padded_dx) and the slice's backward returns that buffer — no torch.cat; values equal the reference."""
+    layer = _layer(True)
+    g = torch.Generator().manual_seed(5)
+    x = torch.randn(2, 24, H, generator=g).bfloat16().requires_grad_(True)
+    out = layer(x)
+    fake_ops.calls.clear()
+    seen = {}
+    real_cat = torch.cat
+
+    def spy_cat(ts, dim=0, **kw):
+        import traceback
+        if any(f.name == "backward" and f.filename.endswith("layer.py") for f in traceback.extract_stack(limit=4)):
+            seen["cat"] = True          # called from _QuerySlice.backward (the stand-in kernels concatenate too)
+        return real_cat(ts, dim=dim, **kw)
+    torch.cat, saved = spy_cat, torch.cat
+    try:
+        out.float().square().mean().backward()
+    finally:
+        torch.cat = saved
+    assert "gemm:out:pitched" in fake_ops.calls          # proj dgrad wrote into the wide buffer
+    assert "cat" not in seen
+    ref_out, h, P = _reference(layer, x.detach())
+    ref_out.float().square().mean().backward()
+    _close(x.grad, h.grad, "dx through the slice hand-over")

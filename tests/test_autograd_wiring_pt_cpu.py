@@ -55,7 +55,8 @@ class _FakePt:
 
     @staticmethod
     def fp8_gemm(a, a_mn, b, b_mn, M, N, K, bias=None, out=None, accumulate=False, out_dtype=torch.bfloat16, max_ctas=0, residual=None):
-        _FakePt.calls.append("gemm" + (":res" if residual is not None else "") + (":home" if out is not None else ""))
+        _FakePt.calls.append("gemm" + (":res" if residual is not None else "") +
+                             ("" if out is None else (":home" if out.is_contiguous() else ":pitched")))      # pitched: dx into a zero-padded wide buffer
         A = a.data.float().t() if a_mn else a.data.float()
         B = b.data.float().t() if b_mn else b.data.float()
         assert A.shape == (M, K) and B.shape == (N, K), (A.shape, B.shape, M, N, K)
