@@ -127,13 +127,16 @@ int llmfp8_fp8_gemm_res(const void* a, int64_t lda, int a_fmt, int a_mn, const v
                         int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, const void* residual, int64_t ldr,
                         int max_ctas, void* stream);
 
-/* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  Process-wide, not thread-safe. */
+/* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  The three knobs below are process-wide, so they
+ * are INERT (non-zero values are ignored, llmfp8_last_error says so) unless the process was started with LLMFP8_ALLOW_TUNING=1 — the test
+ * suite and tools/ set it, a training process does not; values are atomics (a racing launch sees the old or the new value). */
 void llmfp8_gemm_force_bn(int bn);
 /* likewise the CTA group: 1 = single-CTA kernel, 2 = CTA pairs (cta_group::2), 0 = automatic */
 void llmfp8_gemm_force_cg(int cg);
 /* experiments only: bit 0 skips the MX scale smem->TMEM copies, bit 1 the scale loads (results become wrong); bit 3 = static
  * persistent grid instead of cluster launch control, bit 4 = single TMEM accumulator for MXFP8 at 256-column tiles (results unchanged),
- * bit 5 = single accumulator under the fused-residual MXFP8 epilogue (default: overlapped accumulators there too) */
+ * bit 5 = single accumulator under the fused-residual MXFP8 epilogue (default: overlapped accumulators there too), bit 6 = at most 5
+ * ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier */
 void llmfp8_gemm_debug(int flags);
 
 /* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */

@@ -84,6 +84,8 @@ def load():
             if lib.llmfp8_abi_version() != 1:
                 raise RuntimeError("libllmfp8_b200.so ABI version mismatch")
             dbg = os.environ.get("LLMFP8_GEMM_DEBUG")          # experiments only: the bits of llmfp8_gemm_debug (include/llmfp8_b200.h)
+            if dbg or os.environ.get("LLMFP8_GEMM_FORCE_CG") or os.environ.get("LLMFP8_GEMM_FORCE_BN"):
+                os.environ["LLMFP8_ALLOW_TUNING"] = "1"        # the knobs are inert without it; read by the library at its first setter call
             if dbg:
                 lib.llmfp8_gemm_debug(int(dbg, 0))
             for var, setter in (("LLMFP8_GEMM_FORCE_CG", lib.llmfp8_gemm_force_cg), ("LLMFP8_GEMM_FORCE_BN", lib.llmfp8_gemm_force_bn)):

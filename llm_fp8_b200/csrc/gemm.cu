@@ -20,6 +20,9 @@
 // BN (the UMMA N) is a RUNTIME parameter in {128, 192, 256}: the host picks it per problem to minimise wave quantisation
 // (tiles / 148 CTAs).  MXFP8 keeps 64 TMEM columns for scale factors: at BN <= 192 two accumulators fit beside them, at BN = 256 the two
 // accumulators overlap by 64 columns (OVL below) — either way the epilogue of tile t overlaps the mainloop of tile t+1.
+#include <atomic>
+#include <cstdlib>
+
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
@@ -63,7 +66,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
@@ -382,7 +385,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
                 };
                 if constexpr (RES) load_residual((OVL && acc == 0) ? half + 2 * (((nchunks - half + 1) >> 1) - 1) : half);   // the chunk the walk below starts with
-                ptx::mbar_wait(&tmem_full[acc], acc_phase);
+                if (p.debug & 128) ptx::mbar_wait_backoff(&tmem_full[acc], acc_phase, 128);      // experiment: sleeping instead of spinning epilogue warps
+                else ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
                 // OVL: this warp's chunks are walked so that the one lying in the shared columns [192, 256) comes first — the LAST chunk of
@@ -555,12 +559,22 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------------ host side
-static int g_bn_override = 0;     // tuning / tests only (llmfp8_gemm_force_bn / llmfp8_gemm_force_cg)
-static int g_cg_override = 0;
-static int g_debug = 0;
-void gemm_debug(int d) { g_debug = d; }
-void gemm_force_bn(int bn) { g_bn_override = bn; }
-void gemm_force_cg(int cg) { g_cg_override = cg; }
+// Tuning / test knobs (llmfp8_gemm_force_bn / _force_cg / _debug).  Process-wide by nature (they pick which kernel every thread's next
+// launch gets), so they are inert unless the process opted in with LLMFP8_ALLOW_TUNING=1 before the first call — the test suite and the
+// tools/ scripts do, a training process does not, and then no caller can perturb the launches of the autograd thread.  Atomics: a setter
+// racing a launch yields the old or the new value, never a torn one.
+static std::atomic<int> g_bn_override_a{0}, g_cg_override_a{0}, g_debug_a{0};
+static bool tuning_allowed() {
+    static const bool ok = [] { const char* e = getenv("LLMFP8_ALLOW_TUNING"); return e && e[0] == '1'; }();
+    return ok;
+}
+static void set_knob(std::atomic<int>& k, int v, const char* what) {
+    if (v != 0 && !tuning_allowed()) { set_error("%s ignored: set LLMFP8_ALLOW_TUNING=1 before loading the library (tuning / tests only)", what); return; }
+    k.store(v, std::memory_order_relaxed);
+}
+void gemm_debug(int d) { set_knob(g_debug_a, d, "llmfp8_gemm_debug"); }
+void gemm_force_bn(int bn) { set_knob(g_bn_override_a, bn, "llmfp8_gemm_force_bn"); }
+void gemm_force_cg(int cg) { set_knob(g_cg_override_a, cg, "llmfp8_gemm_force_cg"); }
 
 template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false>
 static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
@@ -625,7 +639,7 @@ static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const 
 // Tile width: minimise (waves x per-tile cost).  Narrow tiles cost more per column: their shared-memory traffic per MMA cycle is
 // higher (measured, profiles/r01_gemm_bn_sweep: 192 runs 10-25 % and 128 30-35 % below 256 in the 1-CTA kernel).
 static int pick_bn(int M, int N, bool mx, bool b_mn, int cg, int units) {
-    if (g_bn_override) return g_bn_override;
+    if (const int f = g_bn_override_a.load(std::memory_order_relaxed)) return f;
     const int cand[3] = {256, 192, 128};
     const double eff1[3] = {1.0, b_mn ? 0.76 : 0.88, 0.70};
     const double eff2[3] = {1.0, 0.90, 0.80};
@@ -667,6 +681,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     LLMFP8_REQUIRE(!mx || (reinterpret_cast<uintptr_t>(sfa) | reinterpret_cast<uintptr_t>(sfb)) % 16 == 0, "fp8_gemm: scale tensors must be 16 B aligned");
     LLMFP8_REQUIRE(!(mx && (a_mn != b_mn) && a_mn), "fp8_gemm: operand layout combination (A MN-major, B K-major) is not built");
 
+    const int g_debug = g_debug_a.load(std::memory_order_relaxed), g_cg_override = g_cg_override_a.load(std::memory_order_relaxed);   // one snapshot per launch
     int grid = sm_count();
     if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
     // CTA pairs for anything with at least one full wave of 256-row tiles; the single-CTA kernel for small problems

@@ -3,6 +3,8 @@ import sys
 
 import pytest
 
+os.environ.setdefault("LLMFP8_ALLOW_TUNING", "1")      # the suite drives the GEMM tile / debug knobs; a training process leaves them inert
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)

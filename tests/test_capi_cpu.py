@@ -116,3 +116,18 @@ def test_parameter_names_and_aliasing():
     assert (attn.layernorm_qkv.query_weight == 3).all()
     missing, unexpected = attn.load_state_dict({k: v for k, v in sd.items() if not k.endswith("_extra_state")}, strict=False)
     assert not unexpected
+
+
+def test_gemm_tuning_knobs_are_inert_without_opt_in():
+    """llmfp8_gemm_debug / _force_bn / _force_cg change which kernel every thread's next launch gets: a process that did not set
+    LLMFP8_ALLOW_TUNING=1 cannot be perturbed by them (checked in a fresh interpreter; this suite's conftest opts in)."""
+    import subprocess
+    import sys
+    code = ("import os; os.environ.pop('LLMFP8_ALLOW_TUNING', None)\n"
+            "from llm_fp8_b200 import _lib\n"
+            "lib = _lib.load(); lib.llmfp8_gemm_debug(16)\n"
+            "print(lib.llmfp8_last_error().decode())")
+    env = {k: v for k, v in os.environ.items() if not k.startswith("LLMFP8_")}
+    out = subprocess.run([sys.executable, "-c", code], cwd=ROOT, env=env, capture_output=True, text=True, timeout=120)
+    assert out.returncode == 0, out.stderr
+    assert "LLMFP8_ALLOW_TUNING" in out.stdout

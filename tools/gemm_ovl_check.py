@@ -8,6 +8,8 @@ import sys
 
 import torch
 
+os.environ.setdefault("LLMFP8_ALLOW_TUNING", "1")      # this tool drives the GEMM tuning knobs
+
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from llm_fp8_b200 import _lib, ops  # noqa: E402

@@ -8,7 +8,7 @@ S=gpurun_out/r02_scale_summary.txt
 : > $S
 # Every line costs ~2 min x 8 GPUs = 16 GPU-minutes of the round's 180: run a SHORT list.  LINES="tag tag ..." selects (default below);
 # LINES=all runs everything (only with budget to spare).
-LINES=${LINES:-"base nvls32 wgradstream bucket256"}
+LINES=${LINES:-"base nvls32 nvls96 bucket256"}
 run() {  # tag, env assignments...
   tag=$1; shift
   case " $LINES " in *" all "*|*" $tag "*) ;; *) return 0;; esac
@@ -19,23 +19,29 @@ run() {  # tag, env assignments...
 import json
 try:
     d = json.loads(open("gpurun_out/r02_scale_${tag}_n$N.json").read().strip().splitlines()[-1])
-    print("   ${tag}", round(d["value"]), "TF total", round(d["ms_per_step"], 1), "ms/step  e2e", round(d["e2e"]["value"]), d["clocks"])
+    tl = d.get("timeline") or {}
+    print("   ${tag}", round(d["value"]), "TF total", round(d["ms_per_step"], 1), "ms/step  e2e", round(d["e2e"]["value"]),
+          "fwd/bwd/tail ms", [round(tl.get(k, 0), 1) for k in ("forward_ms", "backward_ms", "reduce_tail_ms")], d["clocks"])
 except Exception as e:
     print("   ${tag}: parse failed", e)
 PY
 }
 # single-GPU reference on the same box (ratio denominators must come from the same box)
 timeout 200 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-roofline > gpurun_out/r02_scale_base_n1.json 2> gpurun_out/r02_scale_base_n1.err; echo "base n=1 exit $?" >> $S
+python - >> $S <<PY
+import json
+d = json.loads(open("gpurun_out/r02_scale_base_n1.json").read().strip().splitlines()[-1])
+tl = d.get("timeline") or {}
+print("   n=1", round(d["value"]), "TF", round(d["ms_per_step"], 1), "ms/step  fwd/bwd/tail ms", [round(tl.get(k, 0), 1) for k in ("forward_ms", "backward_ms", "reduce_tail_ms")], d["clocks"])
+PY
 run base LLMFP8_NOOP=1
 run pdl LLMFP8_PDL=1                                   # launch gaps matter more when NCCL kernels interleave
-run wgradstream LLMFP8_WGRAD_STREAM=1
+run nowgradstream LLMFP8_WGRAD_STREAM=0
 run cga2 NCCL_CGA_CLUSTER_SIZE=2                       # NCCL CTAs in pairs: fewer TPCs half-occupied (our GEMM needs both SMs of a TPC)
 run cga1 NCCL_CGA_CLUSTER_SIZE=1
 run cg1 LLMFP8_GEMM_FORCE_CG=1                         # single-CTA GEMM tiles: do they coexist better with the all-reduce kernels?
 run bucket256 LLMFP8_GRAD_BUCKET_MB=256                # coalesced gradient groups: ~2 NCCL launches per decoder layer instead of 6
 run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
-run fusedact LLMFP8_MX_FUSED_ACT=1
-run wprefetch LLMFP8_WEIGHT_PREFETCH=1
 # in-switch gradient reduce (own multimem kernel, csrc/nvls_reduce.cu) — only after tools/gpu_nvls2.sh passed on two GPUs
 run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
