@@ -1,8 +1,8 @@
 """Index model of csrc/mx_act_quantize.cu, checked on CPU against the oracle's layouts.
 
-The fused SwiGLU / dSwiGLU + MXFP8 kernels were written without a GPU at hand; their arithmetic is shared, line for line, with
-kernels that ARE pinned on hardware (swiglu.cu, mx_quantize.cu).  What is new is index logic — which tile lands where, which
-512 B scale tile it owns, which thread sums which bias column — and that part can be replayed here in numpy-style torch:
+The arithmetic of the fused SwiGLU / dSwiGLU + MXFP8 kernels is shared, line for line, with kernels pinned on hardware (swiglu.cu,
+mx_quantize.cu); what is their own is index logic — which tile lands where, which bytes of which 512 B scale tile it owns, when the bias
+sums are flushed — and that part is replayed here in numpy-style torch:
 each function below walks the tiles exactly as the CUDA code does (same formulas, cited) and must reproduce
 oracle.fp8_oracle's full-matrix results.  No product code runs here; the GPU parity tests are in tests/test_gpu_quantize.py."""
 import pytest
@@ -91,41 +91,71 @@ def _dswiglu(da, g, u):
     return dg, du
 
 
-def model_bwd(da, fc1, M, I):
-    """mx_dswiglu_quantize_kernel: tiles over [M, I]; output [M, 2I] = (dgate | dup); the dup tile of (tr, tc) is tile column
-    tiles_c + tc of the output; bias sums per tile -> column col0 + c (dgate) and I + col0 + c (dup)."""
+def model_bwd(da, fc1, M, I, grid=3):
+    """mx_dswiglu_quantize_kernel (ring version): 64-row tiles over [M, I], row-tile count rounded up to even so every 128-row scale tile is
+    written whole; each CTA owns a contiguous range of tiles in COLUMN-major order; output [M, 2I] = (dgate | dup) with the dup half at
+    tile column tiles_c + tc; a 64-row tile fills 8 consecutive bytes per (row & 31) of its rowwise scale tile and 2 per column of its
+    colwise one (the staging arrays sf_row[2][32][8] / sf_col[2][128][2]); bias sums flushed when the tile column changes."""
+    R = 64
     gate, up = fc1[:, :I], fc1[:, I:]
-    tiles_c, tiles_r = I // AT, (M + AT - 1) // AT
+    tiles_c, tiles_r128 = I // AT, (M + AT - 1) // AT
+    tiles_r = 2 * tiles_r128
+    ntiles = tiles_c * tiles_r
     q_row = torch.zeros(M, 2 * I, dtype=torch.uint8)
     q_col = torch.zeros(M, 2 * I, dtype=torch.uint8)
-    sf_row = torch.zeros(tiles_r * 2 * tiles_c * 512, dtype=torch.uint8)
-    sf_col = torch.zeros(2 * tiles_c * tiles_r * 512, dtype=torch.uint8)
+    sf_row = torch.full((tiles_r128 * 2 * tiles_c * 512,), 0xAA, dtype=torch.uint8)      # poison: every byte must be written
+    sf_col = torch.full((2 * tiles_c * tiles_r128 * 512,), 0xAA, dtype=torch.uint8)
     dbias = torch.zeros(2 * I, dtype=torch.float64)
-    for t in range(tiles_r * tiles_c):
-        tr, tc = t // tiles_c, t % tiles_c
-        row0, col0 = tr * AT, tc * AT
-        dg, du = _dswiglu(_tile(da, row0, col0), _tile(gate, row0, col0), _tile(up, row0, col0))
-        # activation pass: vector idx = i * 512 + tid -> row idx >> 4, column segment (idx & 15) * 8; lanes l and l ^ 16 fold, then
-        # part[warp][seg * 8 + j]; summed over warps by thread `c` -> here simply the column sums of the tile
-        part = torch.zeros(16, 2 * AT, dtype=torch.float64)
-        for i in range(4):
-            for tid in range(512):
-                idx = i * 512 + tid
-                r, seg, w = idx >> 4, idx & 15, tid >> 5
-                assert seg == (tid & 31) % 16                  # the fold partner (lane ^ 16) holds the same segment
-                part[w, seg * 8:seg * 8 + 8] += dg[r, seg * 8:seg * 8 + 8].double()
-                part[w, AT + seg * 8:AT + seg * 8 + 8] += du[r, seg * 8:seg * 8 + 8].double()
-        for c in range(2 * AT):
-            col = col0 + c if c < AT else I + col0 + (c - AT)
-            dbias[col] += part[:, c].sum()
-        for h, val in ((0, dg), (1, du)):
-            qr, er, qc, ec = _quantise_tile(val.bfloat16())
-            _store(q_row, qr, row0, h * I + col0)
-            _store(q_col, qc, row0, h * I + col0)
-            off = (tr * (2 * tiles_c) + h * tiles_c + tc) * 512
-            sf_row[off:off + 512] = _sf_tile_row(er)
-            off = ((h * tiles_c + tc) * tiles_r + tr) * 512
-            sf_col[off:off + 512] = _sf_tile_col(ec)
+    flushes = 0
+
+    def tile64(x, r0, c0):
+        t = torch.zeros(R, AT, dtype=x.dtype)
+        r1 = min(r0 + R, x.shape[0])
+        if r1 > r0:
+            t[: r1 - r0] = x[r0:r1, c0:c0 + AT]
+        return t
+
+    for cta in range(grid):
+        t0, t1 = ntiles * cta // grid, ntiles * (cta + 1) // grid
+        acc, cur_tc = torch.zeros(2 * AT, dtype=torch.float64), -1
+        for t in range(t0, t1):
+            tc, tr = t // tiles_r, t % tiles_r
+            row0, col0 = tr * R, tc * AT
+            if tc != cur_tc:
+                if cur_tc >= 0:
+                    dbias[cur_tc * AT:cur_tc * AT + AT] += acc[:AT]
+                    dbias[I + cur_tc * AT:I + cur_tc * AT + AT] += acc[AT:]
+                    flushes += 1
+                acc, cur_tc = torch.zeros(2 * AT, dtype=torch.float64), tc
+            dg, du = _dswiglu(tile64(da, row0, col0), tile64(gate, row0, col0), tile64(up, row0, col0))
+            acc[:AT] += dg.double().sum(0)
+            acc[AT:] += du.double().sum(0)
+            V = torch.cat((dg, du), 0).bfloat16()                       # the virtual 128 x 128 tile: rows 0..63 dgate, 64..127 dup
+            qr, er, qc, ec = _quantise_tile(V)
+            upper = 1 if (row0 & 64) else 0
+            for h in range(2):
+                r1 = min(row0 + R, M)
+                if r1 > row0:
+                    q_row[row0:r1, h * I + col0:h * I + col0 + AT] = qr[h * R:h * R + (r1 - row0)]
+                    q_col[row0:r1, h * I + col0:h * I + col0 + AT] = qc[h * R:h * R + (r1 - row0)]
+                # rowwise scale staging: s.sf_row[r >> 6][r & 31][((r >> 5) & 1) * 4 + blk], written out as 8 bytes at q * 16 + upper * 8
+                stage = torch.zeros(32, 8, dtype=torch.uint8)
+                for r in range(h * R, h * R + R):
+                    for blk in range(4):
+                        stage[r & 31, ((r >> 5) & 1) * 4 + blk] = er[r, blk]
+                base = ((row0 >> 7) * (2 * tiles_c) + h * tiles_c + tc) * 512
+                for q in range(32):
+                    sf_row[base + q * 16 + upper * 8: base + q * 16 + upper * 8 + 8] = stage[q]
+                # colwise: s.sf_col[rb >> 1][c][rb & 1], written as 2 bytes at (c & 31) * 16 + (c >> 5) * 4 + upper * 2
+                base = ((h * tiles_c + tc) * tiles_r128 + (row0 >> 7)) * 512
+                for c in range(AT):
+                    for k in range(2):
+                        sf_col[base + (c & 31) * 16 + (c >> 5) * 4 + upper * 2 + k] = ec[c, 2 * h + k]
+        if cur_tc >= 0:
+            dbias[cur_tc * AT:cur_tc * AT + AT] += acc[:AT]
+            dbias[I + cur_tc * AT:I + cur_tc * AT + AT] += acc[AT:]
+            flushes += 1
+    assert flushes <= grid + tiles_c          # a few atomics per CTA, not one set per tile
     return q_row, sf_row, q_col, sf_col, dbias
 
 
