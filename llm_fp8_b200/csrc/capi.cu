@@ -51,8 +51,20 @@ static EncodeTiledFn encode_fn() {
     return fn;
 }
 
+// cuTensorMapEncodeTiled is a DRIVER entry point: unlike the runtime calls around it, it does not bind the device's primary context to the
+// calling thread, and returns CUDA_ERROR_INVALID_CONTEXT on a thread that has none yet — e.g. autograd's backward thread when the first thing
+// a process ever runs in backward is one of our TMA-fed kernels.  One cheap runtime call per thread establishes it.
+static void ensure_context() {
+    static thread_local bool ready = false;
+    if (!ready) {
+        cudaFree(nullptr);
+        ready = true;
+    }
+}
+
 int make_tensor_map_2d(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int elem_bytes, int64_t dim0, int64_t dim1,
                        int64_t pitch_bytes, int box0, int box1, CUtensorMapSwizzle swizzle) {
+    ensure_context();
     EncodeTiledFn fn = encode_fn();
     if (!fn) {
         set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");
@@ -74,6 +86,7 @@ int make_tensor_map_2d(CUtensorMap* map, const void* base, CUtensorMapDataType d
 
 int make_tensor_map_3d(CUtensorMap* map, const void* base, CUtensorMapDataType dtype, int64_t d0, int64_t d1, int64_t d2, int64_t stride1_bytes,
                        int64_t stride2_bytes, int b0, int b1, int b2) {
+    ensure_context();
     EncodeTiledFn fn = encode_fn();
     if (!fn) {
         set_error("cuTensorMapEncodeTiled is not available from the CUDA driver");

@@ -188,3 +188,21 @@ def test_mx_decoder_path_matches_oracle_layer():
     close(y.reshape(-1, H), want, what="layer output")
     y.float().pow(2).mean().backward()
     assert all(torch.isfinite(v.grad.float()).all() for v in blk.parameters())
+
+
+def test_first_backward_of_a_process_can_be_a_tma_kernel():
+    """autograd's backward thread has no CUDA context bound until a runtime call runs on it, and cuTensorMapEncodeTiled (a driver entry
+    point) does not bind one: the very first backward of a fresh process going straight into the MX quantiser must still work."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    code = ("import torch, llm_fp8_b200 as te\n"
+            "lin = te.Linear(256, 256, bias=False, params_dtype=torch.bfloat16, device='cuda')\n"
+            "x = torch.randn(64, 256, device='cuda').bfloat16().requires_grad_(True)\n"
+            "with te.fp8_autocast(enabled=True, fp8_recipe=te.MXFP8BlockScaling(fp8_format=te.Format.E4M3)):\n"
+            "    y = lin(x)\n"
+            "y.backward(torch.ones_like(y))\n"
+            "torch.cuda.synchronize(); assert torch.isfinite(x.grad.float()).all(); print('ok')\n")
+    out = subprocess.run([sys.executable, "-c", code], cwd=root, capture_output=True, text=True, timeout=300)
+    assert out.returncode == 0 and "ok" in out.stdout, out.stderr[-2000:]
