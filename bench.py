@@ -419,9 +419,16 @@ def main():
     if not a.no_roofline and rank != 0:
         resident_step()                      # every rank runs the step (its gradient / amax all-reduces must match rank 0's)
     if not a.no_roofline and rank == 0:
-        _lib.profile_start()
-        eager_resident_step()
-        recs = _lib.profile_stop()
+        # per-launch timing needs the launches one after the other: the wgrad side stream (functional.WGRAD_SIDE_STREAM) is switched off
+        # for this ONE untimed step, otherwise a kernel's event pair also spans the time it waits for SMs held by the overlapping GEMM
+        from llm_fp8_b200 import functional as _fn
+        _side, _fn.WGRAD_SIDE_STREAM = _fn.WGRAD_SIDE_STREAM, False
+        try:
+            _lib.profile_start()
+            eager_resident_step()
+            recs = _lib.profile_stop()
+        finally:
+            _fn.WGRAD_SIDE_STREAM = _side
         tot = sum(r[3] for r in recs) or 1e-9
         by = {}
         canon = {"llmfp8_fp8_gemm_res": "llmfp8_fp8_gemm", "llmfp8_mxfp8_gemm_res": "llmfp8_mxfp8_gemm", "llmfp8_mx_quantize_ld": "llmfp8_mx_quantize",

@@ -66,7 +66,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no ordering of the epilogue warps' first TMEM loads (OVL)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
 };
@@ -399,6 +399,12 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 for (int c = walk_down ? half + 2 * (nmine - 1) : half, n = 0; OVL ? (n < nmine) : (c < nchunks); c += walk_down ? -2 : 2, n++) {
                     const int col = n0 + c * ccols;
                     uint32_t r0[32], r1[32];
+                    if constexpr (OVL) {
+                        // TMEM reads share one port per SM (measured: the 64 shared columns took as long to drain as half the accumulator while
+                        // all eight warps loaded at once): the warp that does NOT own the shared chunk holds its first load back until its
+                        // quadrant sibling has the shared columns in registers, so the hand-over to the next tile's MMAs waits for 32 KB, not 64
+                        if (n == 0 && !owns_shared && !(p.debug & 256)) asm volatile("bar.sync %0, 64;" ::"r"(2 + quad) : "memory");
+                    }
                     ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
                     if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
@@ -411,6 +417,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                 if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ctrl->ovl_free), 0));
                                 else ptx::mbar_arrive(&ctrl->ovl_free);
                             }
+                            if (!p.out_fp32 && !(p.debug & 256)) asm volatile("bar.arrive %0, 64;" ::"r"(2 + quad) : "memory");   // sibling warp may load now
                         }
                     }
                     if (OVL ? (n + 1 == nmine) : (c + 2 >= nchunks)) release_acc(acc);           // this warp's share of the accumulator is in registers

@@ -186,16 +186,19 @@ class GradAllReducer:
             self.nvls.poll()     # raises (at the latest one step on) if a rank meeting gave up
         self._flush_pending()
         if self._small:
+            # norm weights and biases (a few hundred small tensors): ONE flat buffer, filled and emptied with one fused multi-tensor copy
+            # each (torch._foreach_copy_) instead of a copy kernel per tensor — on the critical path after the last wgrad
             grads = [p.grad for p in self._small]
-            flat = torch.cat([g.reshape(-1).float() for g in grads])
+            flat = torch.empty(sum(g.numel() for g in grads), dtype=torch.float32, device=grads[0].device)
+            views, off = [], 0
+            for g in grads:
+                views.append(flat[off:off + g.numel()].view_as(g))
+                off += g.numel()
+            torch._foreach_copy_(views, grads)
             dist.all_reduce(flat, op=self._op(), group=self.group)
             if post_scale:
                 flat /= self.world
-            off = 0
-            for g in grads:
-                n = g.numel()
-                g.copy_(flat[off:off + n].view_as(g))
-                off += n
+            torch._foreach_copy_(grads, views)
             self.bytes_reduced += flat.numel() * 4
             self.collectives += 1
             self._small = []
