@@ -127,6 +127,29 @@ int llmfp8_fp8_gemm_res(const void* a, int64_t lda, int a_fmt, int a_mn, const v
                         int N, int K, const float* a_scale_inv, const float* b_scale_inv, const void* bias, const void* residual, int64_t ldr,
                         int max_ctas, void* stream);
 
+/* bf16 GEMM on the same tcgen05 pipeline (kind::f16, fp32 accumulate): D[M, N] = A B^T (+ bias[n]) (+ D).  lda / ldb: row pitches in ELEMENTS
+ * (multiples of 8) of the stored matrices — [M, K] / [N, K], or [K, M] / [K, N] when a_mn / b_mn (MN-major: dgrad and wgrad read the forward's
+ * tensors in place).  The one bf16 linear on the reference's step is the lm_head (HF nn.Linear outside TE: train_fp8.py:278). */
+int llmfp8_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* d, int64_t ldd, int out_fp32, int M, int N, int K,
+                     const void* bias, int accumulate, int max_ctas, void* stream);
+/* lm_head + cross-entropy without materialising the [M, V] logits in forward:
+ *   llmfp8_lm_head_ce_stats : logits = x[M, H] w[V, H]^T in the GEMM, rounded to bf16 as HF's lm_head output is; the epilogue keeps, per row and
+ *                             per (256-column tile, warp half), the maximum and the sum of exponentials -> partials float2 [llmfp8_lm_head_partials(V), M],
+ *                             and the label's logit -> label_logit [M] (rows whose label is outside [0, V) are left untouched);
+ *   llmfp8_ce_reduce        : lse [M], loss_and_count = {mean over rows with label != ignore_index of (lse - label_logit), number of such rows};
+ *                             block_ws: llmfp8_ce_reduce_ws_floats(M) floats; deterministic summation order;
+ *   llmfp8_lm_head_dlogits  : the GEMM again with d(logits)[M, V] = (exp(logit - lse) - [col == label]) * gscale[0] (0 for ignored rows), bf16;
+ *                             dX and dW are then llmfp8_bf16_gemm(dlogits, w MN-major) and llmfp8_bf16_gemm(dlogits MN-major, x MN-major).
+ * [HF LlamaForCausalLM: lm_head + CrossEntropyLoss on the bf16 logits upcast to fp32] */
+int llmfp8_lm_head_partials(int V);
+int llmfp8_lm_head_ce_stats(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, void* partials,
+                            float* label_logit, void* stream);
+int llmfp8_ce_reduce_ws_floats(int M);
+int llmfp8_ce_reduce(const void* partials, int n_partials, int M, const float* label_logit, const int64_t* labels, int64_t ignore_index, float* lse,
+                     float* block_ws, float* loss_and_count, void* stream);
+int llmfp8_lm_head_dlogits(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, int64_t ignore_index,
+                           const float* lse, const float* gscale, void* dlogits, int64_t ldd, void* stream);
+
 /* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  The three knobs below are process-wide, so they
  * are INERT (non-zero values are ignored, llmfp8_last_error says so) unless the process was started with LLMFP8_ALLOW_TUNING=1 — the test
  * suite and tools/ set it, a training process does not; values are atomics (a racing launch sees the old or the new value). */

@@ -42,6 +42,12 @@ _PROTOTYPES = {
     "llmfp8_mx_dswiglu_quantize": [vp, vp, i64, i64, vp, vp, vp, vp, vp, vp, vp],
     "llmfp8_rmsnorm_rsigma": [vp, vp, i64, i64, f32, vp],
     "llmfp8_mx_scale_bytes": [i64, i64],
+    "llmfp8_bf16_gemm": [vp, i64, i32, vp, i64, i32, vp, i64, i32, i32, i32, i32, vp, i32, i32, vp],
+    "llmfp8_lm_head_partials": [i32],
+    "llmfp8_lm_head_ce_stats": [vp, i64, vp, i64, i32, i32, i32, vp, vp, vp, vp],
+    "llmfp8_ce_reduce_ws_floats": [i32],
+    "llmfp8_ce_reduce": [vp, i32, i32, vp, vp, i64, vp, vp, vp, vp],
+    "llmfp8_lm_head_dlogits": [vp, i64, vp, i64, i32, i32, i32, vp, i64, vp, vp, vp, i64, vp],
     "llmfp8_gemm_force_bn": [i32],
     "llmfp8_gemm_force_cg": [i32],
     "llmfp8_gemm_debug": [i32],
@@ -130,6 +136,10 @@ def _work(name: str, a):
     if name == "llmfp8_mx_dswiglu_quantize":      # read da + gate | up (6 B per [M, I] element), write the copies + scales of [M, 2I]
         mi = float(a[2]) * a[3]
         return "byte", 6.0 * mi + 2.0 * (mi + mi / 32) * ((a[4] is not None) + (a[6] is not None))
+    if name == "llmfp8_bf16_gemm":
+        return "flop", 2.0 * a[9] * a[10] * a[11]
+    if name in ("llmfp8_lm_head_ce_stats", "llmfp8_lm_head_dlogits"):
+        return "flop", 2.0 * a[4] * a[5] * a[6]
     if name == "llmfp8_mx_quantize_bgrad":
         rc = float(a[2]) * a[3]
         return "byte", 2.0 * rc + (rc + rc / 32) * ((a[4] is not None) + (a[6] is not None))
@@ -148,7 +158,7 @@ class _Profiled:
     def __getattr__(self, name):
         fn = getattr(self._lib, name)
         if name in ("llmfp8_gemm_force_bn", "llmfp8_gemm_force_cg", "llmfp8_gemm_debug", "llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
-                    "llmfp8_rmsnorm_bwd_ws_rows") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
+                    "llmfp8_rmsnorm_bwd_ws_rows", "llmfp8_lm_head_partials", "llmfp8_ce_reduce_ws_floats") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
             return fn
         import torch
 

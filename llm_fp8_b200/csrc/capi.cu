@@ -133,6 +133,10 @@ int launch_nvls_amax_scale_update(float*, const void*, float*, float*, const flo
 int nvls_timeouts(unsigned int*);
 int nvls_timeouts_async(unsigned int*, cudaStream_t);
 int nvls_reset();
+int launch_bf16_gemm(const void*, int64_t, int, const void*, int64_t, int, void*, int64_t, int, int, int, int, const void*, int, int, int, const int64_t*,
+                     const float*, const float*, void*, float*, int64_t, cudaStream_t);
+int launch_ce_reduce(const void*, int, int, const float*, const int64_t*, int64_t, float*, float*, float*, cudaStream_t);
+int ce_reduce_ws_floats(int);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
@@ -225,6 +229,25 @@ int llmfp8_fp8_gemm_res(const void* a, int64_t lda, int a_fmt, int a_mn, const v
     }
     return launch_fp8_gemm(a, lda, a_fmt, a_mn, b, ldb, b_fmt, b_mn, d, ldd, 0, M, N, K, a_scale_inv, b_scale_inv, nullptr, nullptr, bias, residual, ldr,
                            0, max_ctas, S(stream));
+}
+int llmfp8_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* d, int64_t ldd, int out_fp32, int M, int N, int K,
+                     const void* bias, int accumulate, int max_ctas, void* stream) {
+    return launch_bf16_gemm(a, lda, a_mn, b, ldb, b_mn, d, ldd, out_fp32, M, N, K, bias, accumulate, max_ctas, 0, nullptr, nullptr, nullptr, nullptr, nullptr, 0,
+                            S(stream));
+}
+int llmfp8_lm_head_partials(int V) { return 2 * ((V + 255) / 256); }
+int llmfp8_lm_head_ce_stats(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, void* partials,
+                            float* label_logit, void* stream) {
+    return launch_bf16_gemm(x, ldx, 0, w, ldw, 0, nullptr, 0, 0, M, V, H, nullptr, 0, 0, 1, labels, nullptr, nullptr, partials, label_logit, 0, S(stream));
+}
+int llmfp8_ce_reduce_ws_floats(int M) { return ce_reduce_ws_floats(M); }
+int llmfp8_ce_reduce(const void* partials, int n_partials, int M, const float* label_logit, const int64_t* labels, int64_t ignore_index, float* lse,
+                     float* block_ws, float* loss_and_count, void* stream) {
+    return launch_ce_reduce(partials, n_partials, M, label_logit, labels, ignore_index, lse, block_ws, loss_and_count, S(stream));
+}
+int llmfp8_lm_head_dlogits(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, int64_t ignore_index,
+                           const float* lse, const float* gscale, void* dlogits, int64_t ldd, void* stream) {
+    return launch_bf16_gemm(x, ldx, 0, w, ldw, 0, dlogits, ldd, 0, M, V, H, nullptr, 0, 0, 2, labels, lse, gscale, nullptr, nullptr, ignore_index, S(stream));
 }
 void llmfp8_gemm_force_bn(int bn) { gemm_force_bn(bn); }
 void llmfp8_gemm_force_cg(int cg) { gemm_force_cg(cg); }

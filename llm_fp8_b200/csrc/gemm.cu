@@ -69,7 +69,22 @@ struct GemmParams {
                                 // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no ordering of the epilogue warps' first TMEM loads (OVL)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
+    // cross-entropy epilogues of the bf16 lm_head GEMM (EPI 1 / 2)
+    const int64_t* ce_labels;   // [M] class index per row
+    const float* ce_lse;        // EPI 2: [M] log-sum-exp of each row's logits
+    const float* ce_gscale;     // EPI 2: device scalar, upstream gradient / number of counted rows
+    float2* ce_partials;        // EPI 1: [2 * num_n, M] (maximum, sum of exp(v - maximum)) per warp half and column tile
+    float* ce_label_logit;      // EPI 1: [M]
+    int64_t ce_ignore;          // rows with this label contribute no loss and no gradient
 };
+
+__device__ __forceinline__ float bf16_round(float x) { return __uint_as_float(pack_bf16x2(x, 0.f) << 16); }
+__device__ __forceinline__ float ex2_approx(float x) {
+    float r;
+    asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+    return r;
+}
+constexpr float CE_LOG2E = 1.4426950408889634f;
 
 // Shared-memory control block of one CTA.
 struct GemmCtrl {
@@ -129,11 +144,22 @@ __device__ __forceinline__ void tma3d(const CUtensorMap* m, uint64_t* bar, uint3
 // tile drains that shared chunk first and signals `ovl_free`, after which the MMAs of the next tile may start while the rest of the
 // previous accumulator is still being read: the exposed epilogue shrinks from a whole tile's read-out to one 64-column chunk.
 constexpr int OVL_STRIDE = 192;
-template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false>
+// BF: bf16 operands (kind::f16, fp32 accumulate) through the same pipeline — a stage still holds 128 B of k per row, i.e. 64 k-elements,
+// one tcgen05.mma covers 16 of them (32 B), MN-major operands come in 64-element (128 B) swizzle atoms.  The lm_head of the reference
+// (HF nn.Linear in bf16, outside TE: train_fp8.py:278) runs on it.  EPI selects what the epilogue does with the fp32 accumulator:
+//   0  scale / bias / residual -> D (everything above)
+//   1  cross-entropy statistics of the bf16-rounded logits, no D: per (row, 64-column chunk set of this warp) the running maximum and
+//      sum of exponentials -> p.ce_partials[(n_blk * 2 + half) * M + row], and the label's logit -> p.ce_label_logit[row]
+//   2  d(logits) = (softmax - onehot) * ce_gscale[0] for rows whose label is not ce_ignore, 0 otherwise -> D (bf16), from p.ce_lse
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false, bool BF = false, int EPI = 0>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b, const __grid_constant__ CUtensorMap map_sfa,
                 const __grid_constant__ CUtensorMap map_sfb, const __grid_constant__ CUtensorMap map_d, const GemmParams p) {
     constexpr int A_BYTES = BM * BK;
+    constexpr int ELT = BF ? 2 : 1;                  // operand element size in bytes
+    constexpr int BKE = BK / ELT;                    // k elements per stage (a stage row is always 128 B)
+    constexpr int CW = 128 / ELT;                    // MN-major operands: elements per 128 B swizzle atom
+    static_assert(!(BF && MX) && !(EPI != 0 && (!BF || A_MN || B_MN || RES || OVL)), "unsupported combination");
     constexpr int TM = BM * CG;                      // output rows per tile (per CTA pair when CG == 2)
     constexpr int TMEM_COLS = 512;
     const int BN = p.bn;
@@ -156,7 +182,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;     // dynamic mode: unit = this cluster's own (first) tile
     const int num_m = (p.M + TM - 1) / TM, num_n = (p.N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
-    const int num_kb = (p.K + BK - 1) / BK;
+    const int num_kb = (p.K + BKE - 1) / BKE;
 
     if (warp == 0 && lane == 0) {
         ptx::prefetch_tensormap(&map_a);
@@ -211,7 +237,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         // ================================ TMA producer (one per CTA: own A rows, own part of B, own scale tiles)
         {
             int stage = 0, phase = 0;
-            const int b_chunks = p.b_rows_cta >> 7;     // MN-major B: 128-column chunks (the last one may over-fetch)
+            const int b_chunks = p.b_rows_cta / CW;     // MN-major B: 128-byte-wide column chunks (the last one may over-fetch)
             const int bn_cta = BN / CG;
             const bool sf_load = MX && !(p.debug & 2);
             const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? SF_STAGE_BYTES : 0));
@@ -228,13 +254,17 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     uint64_t* fb = &full_bar[stage];
                     const uint32_t fb_leader = CG == 2 ? ptx::mapa(ptx::smem_u32(fb), 0) : 0u;
                     if (rank == 0) ptx::mbar_arrive_expect_tx(fb, tx_bytes);
-                    const int k0 = kb * BK;
-                    if (!A_MN) tma2d<CG>(&map_a, fb, fb_leader, sa, k0, m0);
-                    else tma2d<CG>(&map_a, fb, fb_leader, sa, m0, k0);
+                    const int k0 = kb * BKE;
+                    if (!A_MN) {
+                        tma2d<CG>(&map_a, fb, fb_leader, sa, k0, m0);
+                    } else {
+#pragma unroll
+                        for (int j = 0; j < BM / CW; j++) tma2d<CG>(&map_a, fb, fb_leader, sa + j * (BKE * 128), m0 + j * CW, k0);
+                    }
                     if (!B_MN) {
                         tma2d<CG>(&map_b, fb, fb_leader, sb, k0, nb0);
                     } else {
-                        for (int j = 0; j < b_chunks; j++) tma2d<CG>(&map_b, fb, fb_leader, sb + j * (128 * BK), nb0 + j * 128, k0);
+                        for (int j = 0; j < b_chunks; j++) tma2d<CG>(&map_b, fb, fb_leader, sb + j * (BKE * 128), nb0 + j * CW, k0);
                     }
                     if (sf_load) {
                         uint8_t* ssf = sf_base + stage * SF_STAGE_BYTES;
@@ -253,8 +283,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         if (rank == 0) {
             int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
             int tiles_done = 0;                 // OVL: tiles this cluster has issued so far
-            constexpr uint32_t A_LBO = A_MN ? (BK * 128) : 16, B_LBO = B_MN ? (BK * 128) : 16;
-            constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K * 128) : UMMA_K;
+            constexpr uint32_t A_LBO = A_MN ? (BKE * 128) : 16, B_LBO = B_MN ? (BKE * 128) : 16;      // MN-major: distance between 128 B atoms
+            constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K / ELT * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K / ELT * 128) : UMMA_K;   // bytes per MMA k-step (32 B of k)
             int tile = unit, next_tile;
             for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
@@ -290,6 +320,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         if (MX) {
                             const uint32_t idesc = p.idesc | (static_cast<uint32_t>(k) << 4) | (static_cast<uint32_t>(k) << 29);
                             ptx::mma_mxf8f6f4_cg<CG>(tmem_d, da, db, idesc, accum, tmem_sf, tmem_sf + sfb_off);
+                        } else if (BF) {
+                            ptx::mma_f16_cg<CG>(tmem_d, da, db, p.idesc, accum);
                         } else {
                             ptx::mma_f8f6f4_cg<CG>(tmem_d, da, db, p.idesc, accum);
                         }
@@ -349,7 +381,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         const int half = (warp - 2) >> 2;     // two warps per quadrant split the column chunks (even / odd)
         int acc = 0, acc_phase = 0;
         float alpha = 1.0f;
-        if (!MX) alpha = __fmul_rn(__ldg(p.a_scale_inv), __ldg(p.b_scale_inv));
+        if (!MX && !BF) alpha = __fmul_rn(__ldg(p.a_scale_inv), __ldg(p.b_scale_inv));
         const uint32_t tmem_empty_leader = CG == 2 ? ptx::mapa(ptx::smem_u32(&tmem_empty[0]), 0) : 0u;
         auto release_acc = [&](int a) {
             ptx::tc_fence_before();
@@ -371,6 +403,19 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tile_coords(tile, m_blk, n_blk);
                 const int row0 = m_blk * TM + static_cast<int>(rank) * BM + quad * 32;
                 const int n0 = n_blk * BN;
+                // cross-entropy epilogues: this lane's row
+                int64_t ce_lab = -1;
+                float ce_m = -INFINITY, ce_s = 0.f, ce_ll = 0.f, ce_lse = 0.f, ce_gs = 0.f;
+                bool ce_hit = false;
+                if constexpr (EPI != 0) {
+                    if (row0 + lane < p.M) {
+                        ce_lab = p.ce_labels[row0 + lane];
+                        if constexpr (EPI == 2) {
+                            ce_lse = p.ce_lse[row0 + lane];
+                            ce_gs = ce_lab != p.ce_ignore ? __ldg(p.ce_gscale) : 0.f;
+                        }
+                    }
+                }
                 // fused residual: this lane's 128 B row segment of R for one chunk lives in rv.  Software-pipelined through that single
                 // buffer: the first chunk is requested BEFORE waiting for the accumulator (its DRAM latency hides under the main loop's
                 // tail — the MX kernel at 256 columns has one accumulator, so its epilogue is exposed), the next chunk right after the
@@ -422,6 +467,30 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     }
                     if (OVL ? (n + 1 == nmine) : (c + 2 >= nchunks)) release_acc(acc);           // this warp's share of the accumulator is in registers
                     else __syncwarp();
+                    if constexpr (EPI == 1) {
+                        // statistics of the bf16-rounded logits (HF rounds the lm_head output to bf16 before the fp32 cross-entropy)
+                        if (col < p.N) {
+                            const int ncol = p.N - col < 64 ? p.N - col : 64;
+                            const int lj = (ce_lab >= col && ce_lab < col + ncol) ? static_cast<int>(ce_lab - col) : -1;
+                            float cm = -INFINITY;
+#pragma unroll
+                            for (int j = 0; j < 64; j++) {
+                                const float v = bf16_round(__uint_as_float(j < 32 ? r0[j] : r1[j - 32]));
+                                if (j < ncol) cm = fmaxf(cm, v);
+                                if (j == lj) { ce_ll = v; ce_hit = true; }
+                            }
+                            float cs = 0.f;
+#pragma unroll
+                            for (int j = 0; j < 64; j++) {
+                                const float v = bf16_round(__uint_as_float(j < 32 ? r0[j] : r1[j - 32]));
+                                if (j < ncol) cs += ex2_approx((v - cm) * CE_LOG2E);
+                            }
+                            const float nm = fmaxf(ce_m, cm);
+                            ce_s = ce_s * ex2_approx((ce_m - nm) * CE_LOG2E) + cs * ex2_approx((cm - nm) * CE_LOG2E);
+                            ce_m = nm;
+                        }
+                        continue;
+                    }
                     uint8_t* sbuf = stg + lane * 128;
                     const uint32_t sw = lane & 7;
                     if (col < p.N) {
@@ -454,6 +523,13 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
 #pragma unroll
                                     for (int j = 0; j < 8; j++) v[j] += rf[j];
                                 }
+                                if constexpr (EPI == 2) {
+#pragma unroll
+                                    for (int j = 0; j < 8; j++) {
+                                        const float pj = ex2_approx((bf16_round(v[j]) - ce_lse) * CE_LOG2E);
+                                        v[j] = (pj - (static_cast<int64_t>(col + g * 8 + j) == ce_lab ? 1.f : 0.f)) * ce_gs;
+                                    }
+                                }
                                 uint4 o;
                                 o.x = pack_bf16x2(v[0], v[1]); o.y = pack_bf16x2(v[2], v[3]);
                                 o.z = pack_bf16x2(v[4], v[5]); o.w = pack_bf16x2(v[6], v[7]);
@@ -471,6 +547,12 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         // rv is free again: next chunk's segment, under the store above.  Outside the `col < N` guard: the downward walk of
                         // the OVL kernel meets the chunks past the matrix edge FIRST, and the in-range ones after them still need their segment.
                         if (OVL ? (n + 1 < nmine) : (c + 2 < nchunks)) load_residual(c + (walk_down ? -2 : 2));
+                    }
+                }
+                if constexpr (EPI == 1) {
+                    if (row0 + lane < p.M) {
+                        p.ce_partials[static_cast<int64_t>(n_blk * 2 + half) * p.M + row0 + lane] = make_float2(ce_m, ce_s);
+                        if (ce_hit) p.ce_label_logit[row0 + lane] = ce_ll;
                     }
                 }
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
@@ -583,10 +665,10 @@ void gemm_debug(int d) { set_knob(g_debug_a, d, "llmfp8_gemm_debug"); }
 void gemm_force_bn(int bn) { set_knob(g_bn_override_a, bn, "llmfp8_gemm_force_bn"); }
 void gemm_force_cg(int cg) { set_knob(g_cg_override_a, cg, "llmfp8_gemm_force_cg"); }
 
-template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false>
+template <int CG, bool A_MN, bool B_MN, bool MX, bool RES = false, bool OVL = false, bool BF = false, int EPI = 0>
 static int launch_variant(const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& msa, const CUtensorMap& msb, const CUtensorMap& md,
                           const GemmParams& p, int grid, int smem_bytes, cudaStream_t stream) {
-    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES, OVL>;
+    auto kern = fp8_gemm_kernel<CG, A_MN, B_MN, MX, RES, OVL, BF, EPI>;
     static bool configured[64] = {};   // per device (the attribute lives in the device's context); benign race: the call is idempotent
     int dev = 0;
     if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= 64) dev = -1;
@@ -700,7 +782,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     LLMFP8_REQUIRE(BN == 128 || BN == 192 || BN == 256, "fp8_gemm: tile width %d is not built", BN);
     LLMFP8_REQUIRE(cg == 1 || cg == 2, "fp8_gemm: cta group %d is not built", cg);
 
-    GemmParams p;
+    GemmParams p = {};
     p.d = d; p.ldd = ldd; p.M = M; p.N = N; p.K = K;
     p.a_scale_inv = a_scale_inv; p.b_scale_inv = b_scale_inv; p.bias = bias; p.residual = residual; p.ldr = ldr; p.accumulate = accumulate; p.out_fp32 = out_fp32;
     p.idesc = mx ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN, 0, 0) : ptx::make_idesc_f8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN);
@@ -753,6 +835,83 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     else if (num_tiles * cg < grid) grid = num_tiles * cg;
     if (cg == 2) return dispatch<2>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
     return dispatch<1>(a_mn, b_mn, mx, ma, mb, msa, msb, md, p, grid, smem_bytes, stream);
+}
+
+// ------------------------------------------------------------------------------------------------ bf16 GEMM (kind::f16) and the lm_head epilogues
+template <int CG>
+static int dispatch_bf(bool a_mn, bool b_mn, int epi, const CUtensorMap& ma, const CUtensorMap& mb, const CUtensorMap& md, const GemmParams& p, int grid,
+                       int smem_bytes, cudaStream_t stream) {
+    if (epi == 1) return launch_variant<CG, false, false, false, false, false, true, 1>(ma, mb, ma, mb, md, p, grid, smem_bytes, stream);
+    if (epi == 2) return launch_variant<CG, false, false, false, false, false, true, 2>(ma, mb, ma, mb, md, p, grid, smem_bytes, stream);
+    if (!a_mn && !b_mn) return launch_variant<CG, false, false, false, false, false, true>(ma, mb, ma, mb, md, p, grid, smem_bytes, stream);
+    if (!a_mn && b_mn) return launch_variant<CG, false, true, false, false, false, true>(ma, mb, ma, mb, md, p, grid, smem_bytes, stream);
+    if (a_mn && b_mn) return launch_variant<CG, true, true, false, false, false, true>(ma, mb, ma, mb, md, p, grid, smem_bytes, stream);
+    set_error("bf16_gemm: operand layout combination (A MN-major, B K-major) is not built");
+    return -1;
+}
+
+// D[M, N] = A B^T (+ bias) (+ D) with bf16 operands.  lda / ldb: row pitches in ELEMENTS of the stored matrices ([M, K] or, MN-major, [K, M]).
+// epi 1 / 2: the cross-entropy epilogues (fprop layout, 256-column tiles so that the partial layout is fixed: ce_partials is [2 * ceil(N / 256), M]).
+int launch_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_t ldb, int b_mn, void* d, int64_t ldd, int out_fp32, int M, int N, int K,
+                     const void* bias, int accumulate, int max_ctas, int epi, const int64_t* ce_labels, const float* ce_lse, const float* ce_gscale,
+                     void* ce_partials, float* ce_label_logit, int64_t ce_ignore, cudaStream_t stream) {
+    LLMFP8_REQUIRE(M > 0 && N > 0 && K > 0, "bf16_gemm: empty problem M=%d N=%d K=%d", M, N, K);
+    LLMFP8_REQUIRE(lda % 8 == 0 && ldb % 8 == 0, "bf16_gemm: operand pitches must be multiples of 8 elements (lda=%lld ldb=%lld)", (long long)lda, (long long)ldb);
+    LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(a) | reinterpret_cast<uintptr_t>(b)) % 16 == 0, "bf16_gemm: operands must be 16 B aligned");
+    LLMFP8_REQUIRE(epi == 1 || (d && reinterpret_cast<uintptr_t>(d) % 16 == 0 && N % 8 == 0 && ldd % 8 == 0), "bf16_gemm: output must be 16 B aligned, N and ldd multiples of 8");
+    LLMFP8_REQUIRE(epi == 0 || (!a_mn && !b_mn && !accumulate && !out_fp32 && !bias && ce_labels), "lm_head epilogues: fprop layout, bf16 output, labels required");
+    LLMFP8_REQUIRE(epi != 1 || (ce_partials && ce_label_logit), "lm_head statistics need their output buffers");
+    LLMFP8_REQUIRE(epi != 2 || (ce_lse && ce_gscale), "lm_head gradient needs lse and the gradient scale");
+    const int g_debug = g_debug_a.load(std::memory_order_relaxed), g_cg_override = g_cg_override_a.load(std::memory_order_relaxed);
+    int grid = sm_count();
+    if (max_ctas > 0 && max_ctas < grid) grid = max_ctas;
+    int cg = g_cg_override ? g_cg_override : ((M > BM && grid >= 2 && static_cast<long>((M + 255) / 256) * ((N + 255) / 256) >= grid / 4) ? 2 : 1);
+    if (grid < 2) cg = 1;
+    if (cg == 2) grid &= ~1;
+    const int units = grid / cg;
+    const int BN = epi ? 256 : pick_bn(M, N, false, b_mn != 0, cg, units);
+    GemmParams p = {};
+    p.d = d; p.ldd = ldd; p.M = M; p.N = N; p.K = K;
+    p.bias = bias; p.accumulate = accumulate; p.out_fp32 = out_fp32;
+    p.idesc = ptx::make_idesc_f8(1 /*bf16*/, 1, a_mn, b_mn, BM * cg, BN);      // kind::f16 shares the field layout; format 1 = bf16
+    p.bn = BN;
+    p.debug = g_debug;
+    const int bn_cta = BN / cg;
+    p.b_rows_cta = b_mn ? (bn_cta + 63) / 64 * 64 : bn_cta;
+    p.acc_overlap = 0;
+    p.acc_stages = 2;
+    p.ce_labels = ce_labels; p.ce_lse = ce_lse; p.ce_gscale = ce_gscale; p.ce_partials = static_cast<float2*>(ce_partials); p.ce_label_logit = ce_label_logit;
+    p.ce_ignore = ce_ignore;
+    const int stage_bytes = BM * BK + p.b_rows_cta * BK;
+    const int fixed = 1024 + CTRL_BYTES + EPI_BYTES;
+    int stages = (SMEM_BUDGET - fixed) / stage_bytes;
+    if (stages > MAX_STAGES) stages = MAX_STAGES;
+    p.stages = stages;
+    const int smem_bytes = fixed + stages * stage_bytes;
+    CUtensorMap ma, mb, md;
+    int rc;
+    if (epi == 1) {
+        rc = 0;          // no D: the store map is never used (the A map stands in below)
+    } else if (out_fp32) {
+        rc = make_tensor_map_2d(&md, d, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, N, M, ldd * 4, 32, 32, CU_TENSOR_MAP_SWIZZLE_128B);
+    } else {
+        rc = make_tensor_map_2d(&md, d, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, N, M, ldd * 2, 64, 32, CU_TENSOR_MAP_SWIZZLE_128B);
+    }
+    if (rc) return rc;
+    // K-major [rows, K]: box = {64 k, tile rows};  MN-major [K, rows]: box = {64 rows, 64 k}
+    if (!a_mn) rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, K, M, lda * 2, BK / 2, BM, CU_TENSOR_MAP_SWIZZLE_128B);
+    else rc = make_tensor_map_2d(&ma, a, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, M, K, lda * 2, 64, BK / 2, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    if (!b_mn) rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, K, N, ldb * 2, BK / 2, bn_cta, CU_TENSOR_MAP_SWIZZLE_128B);
+    else rc = make_tensor_map_2d(&mb, b, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, N, K, ldb * 2, 64, BK / 2, CU_TENSOR_MAP_SWIZZLE_128B);
+    if (rc) return rc;
+    if (epi == 1) md = ma;
+    const int num_tiles = ((M + BM * cg - 1) / (BM * cg)) * ((N + BN - 1) / BN);
+    p.dynamic = ((g_debug & 8) || max_ctas > 0) ? 0 : 1;
+    if (p.dynamic) grid = num_tiles * cg;
+    else if (num_tiles * cg < grid) grid = num_tiles * cg;
+    if (cg == 2) return dispatch_bf<2>(a_mn != 0, b_mn != 0, epi, ma, mb, md, p, grid, smem_bytes, stream);
+    return dispatch_bf<1>(a_mn != 0, b_mn != 0, epi, ma, mb, md, p, grid, smem_bytes, stream);
 }
 
 }  // namespace llmfp8
