@@ -16,3 +16,6 @@ for t in ("mxfp8", "mxfp8_unordered"):
     print("bench", t, round(d["value"], 1), round(d["ms_per_step"], 2), d["clocks"]["sm_mhz"], d.get("timeline"))
 PY
 grep "G.m" gpurun_out/r02e_gemm_ab.txt
+# first hardware run of the bf16 GEMM + lm_head epilogues (last: a hang here must not cost the measurements above)
+timeout 300 python -m pytest tests/test_gpu_lm_head.py -q -m gpu -p no:cacheprovider -x > gpurun_out/r02e_pytest_lm_head.log 2>&1
+echo "pytest lm_head exit $?  $(tail -1 gpurun_out/r02e_pytest_lm_head.log)"; grep -E "^FAILED|^ERROR|^E  " gpurun_out/r02e_pytest_lm_head.log | head -20
