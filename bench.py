@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--scenario", default="mxfp8", choices=["mxfp8", "default", "hybrid"],
                     help="reference decoder swap: mxfp8 = te_llama_mxfp8.py, default = te_llama.py, hybrid = te_llama_hybrid.py")
     ap.add_argument("--batch", type=int, default=12, help="sequences per GPU (reference semantics: per-device batch)")
+    ap.add_argument("--global-batch", type=int, default=0,
+                    help="STRONG scaling: total sequences, split over the ranks (batch = global-batch / world); 0 = weak scaling with --batch per GPU")
     ap.add_argument("--seq", type=int, default=512)
     ap.add_argument("--layers", type=int, default=0, help="0 = the model's own depth")
     ap.add_argument("--graph", type=int, default=int(os.environ.get("LLMFP8_BENCH_GRAPH", "0")),
@@ -236,6 +238,11 @@ def main():
     dev = torch.device("cuda", local)
     lib = _lib.load()
     pk = peaks()
+    scaling = "weak"
+    if a.global_batch > 0:                 # "also report strong scaling (global M fixed, M_local = M / n)"
+        if a.global_batch % world:
+            raise SystemExit(f"--global-batch {a.global_batch} is not divisible by {world} ranks")
+        a.batch, scaling = a.global_batch // world, "strong"
 
     model = LinearPathStack(a.model, a.scenario, a.layers or None, device=dev, fuse_residual=False if a.no_fuse_residual else None)
     L = model.n_layers
@@ -472,7 +479,7 @@ def main():
     if rank == 0:
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": a.steps, "warmup": max(a.warmup, 3), "ms_per_step": ms_step,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "fp8_e4m3" + ("+e8m0" if a.scenario == "mxfp8" else "/e5m2") + " (fp32 accumulate, bf16 out)",
+            "higher_is_better": True, "scaling": scaling, "vs_baseline": None, "dtype": "fp8_e4m3" + ("+e8m0" if a.scenario == "mxfp8" else "/e5m2") + " (fp32 accumulate, bf16 out)",
             "data": "synthetic",
             "config": {"workload": workload_name(a, L), "tokens_per_gpu": M, "global_tokens": M * world, "layers": L,
                        "linear_params_per_layer": model.params_per_layer, "flops_per_step_per_gpu": flops_step,

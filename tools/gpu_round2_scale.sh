@@ -8,7 +8,7 @@ S=gpurun_out/r02_scale_summary.txt
 : > $S
 # Every line costs ~2 min x 8 GPUs = 16 GPU-minutes of the round's 180: run a SHORT list.  LINES="tag tag ..." selects (default below);
 # LINES=all runs everything (only with budget to spare).
-LINES=${LINES:-"base nvls32 nvls96 bucket256"}
+LINES=${LINES:-"base nvls32 nvls96 bucket256 cfg3b strong"}
 run() {  # tag, env assignments...
   tag=$1; shift
   case " $LINES " in *" all "*|*" $tag "*) ;; *) return 0;; esac
@@ -46,6 +46,33 @@ run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
 run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
 run nvls96 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=96
+# BASELINE.json configs[2]: Llama-3.2-3B, te_llama_hybrid recipe (delayed scaling: the amax MAX exchange is on the path), batch 16 x 512 per GPU
+run2() {  # tag, n, extra bench args...
+  tag=$1; n=$2; shift 2
+  case " $LINES " in *" all "*|*" $tag "*) ;; *) return 0;; esac
+  if [ "$n" = 1 ]; then
+    timeout 200 python bench.py --steps 4 --warmup 3 --no-cpu-baseline --no-roofline "$@" > gpurun_out/r02_scale_${tag}_n$n.json 2> gpurun_out/r02_scale_${tag}_n$n.err
+  else
+    LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $n --master-addr 127.0.0.1 --master-port 29513 \
+        bench.py --gpus $n --steps 4 --warmup 3 --no-roofline "$@" > gpurun_out/r02_scale_${tag}_n$n.json 2> gpurun_out/r02_scale_${tag}_n$n.err
+  fi
+  echo "$tag n=$n exit $?" >> $S
+  python - >> $S <<PY
+import json
+try:
+    d = json.loads(open("gpurun_out/r02_scale_${tag}_n$n.json").read().strip().splitlines()[-1])
+    tl = d.get("timeline") or {}
+    print("   ${tag} n=$n", round(d["value"]), "TF total", round(d["ms_per_step"], 1), "ms/step", d["scaling"], d["config"]["workload"][:60],
+          "fwd/bwd/tail ms", [round(tl.get(k, 0), 1) for k in ("forward_ms", "backward_ms", "reduce_tail_ms")])
+except Exception as e:
+    print("   ${tag}: parse failed", e)
+PY
+}
+run2 cfg3b 1 --model llama-3.2-3b --scenario hybrid --batch 16
+run2 cfg3b $N --model llama-3.2-3b --scenario hybrid --batch 16
+# strong scaling: 24 sequences in total, 24 on one GPU against 24 / N per GPU
+run2 strong 1 --global-batch 24
+run2 strong $N --global-batch 24
 # whole data-parallel step (collectives included) replayed from one CUDA graph: no host launch jitter between ranks
 case " $LINES " in *" all "*|*" graphdp "*) ;; *) cat $S; exit 0;; esac
 tag=graphdp; env LLMFP8_GRAPH_DP=1 LLMFP8_DIST_TIMEOUT_S=90 timeout 240 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
