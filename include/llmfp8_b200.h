@@ -161,6 +161,10 @@ void llmfp8_gemm_force_cg(int cg);
  * bit 5 = single accumulator under the fused-residual MXFP8 epilogue (default: overlapped accumulators there too), bit 6 = at most 5
  * ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier */
 void llmfp8_gemm_debug(int flags);
+/* experiments only (LLMFP8_ALLOW_TUNING=1): device buffer of 64 x 16 u64 that the first cluster of every following FP8 GEMM launch fills with clock64
+ * stamps of its MMA thread (slots 0-4: tile start, accumulator free, shared columns free, first stage full, last MMA issued) and of two epilogue
+ * warps (slots 5-8 and 10-13: accumulator full, first / second chunk loaded, tile done); NULL switches it off (tools/gemm_trace.py) */
+void llmfp8_gemm_trace(unsigned long long* device_buf);
 
 /* Block-scaled variant: sfa / sfb are swizzled E8M0 tensors whose blocks run along k.   [tex.generic_gemm with MXFP8 tensors] */
 int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,

@@ -51,6 +51,7 @@ _PROTOTYPES = {
     "llmfp8_gemm_force_bn": [i32],
     "llmfp8_gemm_force_cg": [i32],
     "llmfp8_gemm_debug": [i32],
+    "llmfp8_gemm_trace": [vp],
     "llmfp8_fp8_gemm": [vp, i64, i32, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, i32, vp, vp, vp, i32, i32, vp],
     "llmfp8_mxfp8_gemm": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, i32, vp, i32, i32, vp],
     "llmfp8_fp8_gemm_res": [vp, i64, i32, i32, vp, i64, i32, i32, vp, i64, i32, i32, i32, vp, vp, vp, vp, i64, i32, vp],
@@ -67,7 +68,7 @@ _PROTOTYPES = {
     "llmfp8_nvls_reset": [],
     "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }
-_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
+_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_trace": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
 EXPORTS = tuple(_PROTOTYPES)
 
 
@@ -157,7 +158,7 @@ class _Profiled:
 
     def __getattr__(self, name):
         fn = getattr(self._lib, name)
-        if name in ("llmfp8_gemm_force_bn", "llmfp8_gemm_force_cg", "llmfp8_gemm_debug", "llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
+        if name in ("llmfp8_gemm_trace", "llmfp8_gemm_force_bn", "llmfp8_gemm_force_cg", "llmfp8_gemm_debug", "llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
                     "llmfp8_rmsnorm_bwd_ws_rows", "llmfp8_lm_head_partials", "llmfp8_ce_reduce_ws_floats") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
             return fn
         import torch

@@ -140,6 +140,7 @@ int ce_reduce_ws_floats(int);
 void gemm_force_bn(int);
 void gemm_force_cg(int);
 void gemm_debug(int);
+void gemm_trace(unsigned long long*);
 
 }  // namespace llmfp8
 
@@ -252,6 +253,7 @@ int llmfp8_lm_head_dlogits(const void* x, int64_t ldx, const void* w, int64_t ld
 void llmfp8_gemm_force_bn(int bn) { gemm_force_bn(bn); }
 void llmfp8_gemm_force_cg(int cg) { gemm_force_cg(cg); }
 void llmfp8_gemm_debug(int flags) { gemm_debug(flags); }
+void llmfp8_gemm_trace(unsigned long long* device_buf) { gemm_trace(device_buf); }
 int llmfp8_mxfp8_gemm(const void* a, int64_t lda, int a_mn, const void* sfa, const void* b, int64_t ldb, int b_mn, const void* sfb, void* d,
                       int64_t ldd, int out_fp32, int M, int N, int K, const void* bias, int accumulate, int max_ctas, void* stream) {
     if (!sfa || !sfb) {

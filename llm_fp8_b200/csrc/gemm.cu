@@ -66,7 +66,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no ordering of the epilogue warps' first TMEM loads (OVL)
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
     // cross-entropy epilogues of the bf16 lm_head GEMM (EPI 1 / 2)
@@ -76,6 +76,7 @@ struct GemmParams {
     float2* ce_partials;        // EPI 1: [2 * num_n, M] (maximum, sum of exp(v - maximum)) per warp half and column tile
     float* ce_label_logit;      // EPI 1: [M]
     int64_t ce_ignore;          // rows with this label contribute no loss and no gradient
+    unsigned long long* trace;  // experiments only (llmfp8_gemm_trace): clock64 stamps of cluster 0's MMA thread and one epilogue warp, 16 per tile
 };
 
 __device__ __forceinline__ float bf16_round(float x) { return __uint_as_float(pack_bf16x2(x, 0.f) << 16); }
@@ -283,6 +284,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         if (rank == 0) {
             int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
             int tiles_done = 0;                 // OVL: tiles this cluster has issued so far
+            int trace_n = 0;
             constexpr uint32_t A_LBO = A_MN ? (BKE * 128) : 16, B_LBO = B_MN ? (BKE * 128) : 16;      // MN-major: distance between 128 B atoms
             constexpr uint32_t A_KSTEP = A_MN ? (UMMA_K / ELT * 128) : UMMA_K, B_KSTEP = B_MN ? (UMMA_K / ELT * 128) : UMMA_K;   // bytes per MMA k-step (32 B of k)
             int tile = unit, next_tile;
@@ -292,15 +294,21 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 // MX: the scale of column n lives in TMEM column (sf buffer) + 4 + (n - 128 * (n0 / 128)) / 32: a tile that starts 64 rows
                 // into a 128-row scale tile (BN = 192) skips the leading 32-row groups by advancing the column address
                 const uint32_t sfb_off = 4 + (((n_blk * BN) & 127) >> 5);
+                unsigned long long* tr = (p.trace && blockIdx.x == 0 && trace_n < 64) ? p.trace + 16 * trace_n : nullptr;
+                trace_n++;
+                if (tr && lane == 0) tr[0] = clock64();
                 ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
+                if (tr && lane == 0) tr[1] = clock64();
                 if constexpr (OVL) {
                     if (tiles_done > 0) ptx::mbar_wait(&ctrl->ovl_free, (tiles_done - 1) & 1);   // previous tile's shared columns are in registers
                     tiles_done++;
                 }
+                if (tr && lane == 0) tr[2] = clock64();
                 ptx::tc_fence_after();
                 const uint32_t tmem_d = tmem_base + acc * (OVL ? OVL_STRIDE : BN);
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&full_bar[stage], phase);
+                    if (tr && lane == 0 && kb == 0) tr[3] = clock64();
                     ptx::tc_fence_after();
                     const uint32_t sa = ptx::smem_u32(smem + stage * stage_bytes);
                     const uint32_t sb = sa + A_BYTES;
@@ -332,6 +340,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     if (MX && !(p.debug & 4)) sfi = (sfi + 1) & (SF_BUFS - 1);
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
+                if (tr && lane == 0) tr[4] = clock64();
                 if (ptx::elect_one_sync()) ptx::tc_commit_cg<CG>(&tmem_full[acc]);         // accumulator complete -> epilogue warps of both CTAs
                 __syncwarp();
                 if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
@@ -394,6 +403,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         if (!p.accumulate) {
             // ---- staged path: 32 x 128 B boxes (64 bf16 or 32 fp32 columns) -> swizzled smem -> TMA store (coalesced, clips partial tiles)
             uint8_t* stg = epi_base + (warp - 2) * EPI_BUF_BYTES;
+            int etrace_n = 0;
             const int ccols = p.out_fp32 ? 32 : 64;
             const int nchunks = BN / ccols;
             if (lane == 0) ptx::prefetch_tensormap(&map_d);
@@ -429,10 +439,13 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     for (int g = 0; g < (RES ? 8 : 1); g++)
                         rv[g] = (row < p.M && col + g * 8 < p.N) ? __ldg(reinterpret_cast<const uint4*>(rp + g * 8)) : make_uint4(0, 0, 0, 0);
                 };
+                unsigned long long* etr = (p.trace && blockIdx.x == 0 && (warp == 2 || warp == 6) && etrace_n < 64) ? p.trace + 16 * etrace_n + (warp == 2 ? 5 : 10) : nullptr;
+                etrace_n++;
                 if constexpr (RES) load_residual((OVL && acc == 0) ? half + 2 * (((nchunks - half + 1) >> 1) - 1) : half);   // the chunk the walk below starts with
                 if (p.debug & 128) ptx::mbar_wait_backoff(&tmem_full[acc], acc_phase, 128);      // experiment: sleeping instead of spinning epilogue warps
                 else ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
+                if (etr && lane == 0) etr[0] = clock64();
                 const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
                 // OVL: this warp's chunks are walked so that the one lying in the shared columns [192, 256) comes first — the LAST chunk of
                 // the accumulator at column 0 (walk down), the FIRST chunk of the one at column 192 (walk up).  bf16 output: 64-column
@@ -444,16 +457,11 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 for (int c = walk_down ? half + 2 * (nmine - 1) : half, n = 0; OVL ? (n < nmine) : (c < nchunks); c += walk_down ? -2 : 2, n++) {
                     const int col = n0 + c * ccols;
                     uint32_t r0[32], r1[32];
-                    if constexpr (OVL) {
-                        // TMEM reads share one port per SM (measured: the 64 shared columns took as long to drain as half the accumulator while
-                        // all eight warps loaded at once): the warp that does NOT own the shared chunk holds its first load back until its
-                        // quadrant sibling has the shared columns in registers, so the hand-over to the next tile's MMAs waits for 32 KB, not 64
-                        if (n == 0 && !owns_shared && !(p.debug & 256)) asm volatile("bar.sync %0, 64;" ::"r"(2 + quad) : "memory");
-                    }
                     ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
                     if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
                     ptx::tmem_ld_wait();
+                    if (etr && lane == 0 && n < 2) etr[1 + n] = clock64();
                     if constexpr (OVL) {
                         if (n == 0 && owns_shared) {                    // the shared columns are in registers: the next tile's MMAs may overwrite them
                             ptx::tc_fence_before();
@@ -462,7 +470,6 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                                 if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ctrl->ovl_free), 0));
                                 else ptx::mbar_arrive(&ctrl->ovl_free);
                             }
-                            if (!p.out_fp32 && !(p.debug & 256)) asm volatile("bar.arrive %0, 64;" ::"r"(2 + quad) : "memory");   // sibling warp may load now
                         }
                     }
                     if (OVL ? (n + 1 == nmine) : (c + 2 >= nchunks)) release_acc(acc);           // this warp's share of the accumulator is in registers
@@ -549,6 +556,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         if (OVL ? (n + 1 < nmine) : (c + 2 < nchunks)) load_residual(c + (walk_down ? -2 : 2));
                     }
                 }
+                if (etr && lane == 0) etr[3] = clock64();
                 if constexpr (EPI == 1) {
                     if (row0 + lane < p.M) {
                         p.ce_partials[static_cast<int64_t>(n_blk * 2 + half) * p.M + row0 + lane] = make_float2(ce_m, ce_s);
@@ -661,6 +669,8 @@ static void set_knob(std::atomic<int>& k, int v, const char* what) {
     if (v != 0 && !tuning_allowed()) { set_error("%s ignored: set LLMFP8_ALLOW_TUNING=1 before loading the library (tuning / tests only)", what); return; }
     k.store(v, std::memory_order_relaxed);
 }
+static std::atomic<unsigned long long*> g_trace{nullptr};
+void gemm_trace(unsigned long long* buf) { if (buf == nullptr || tuning_allowed()) g_trace.store(buf, std::memory_order_relaxed); }
 void gemm_debug(int d) { set_knob(g_debug_a, d, "llmfp8_gemm_debug"); }
 void gemm_force_bn(int bn) { set_knob(g_bn_override_a, bn, "llmfp8_gemm_force_bn"); }
 void gemm_force_cg(int cg) { set_knob(g_cg_override_a, cg, "llmfp8_gemm_force_cg"); }
@@ -788,6 +798,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     p.idesc = mx ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN, 0, 0) : ptx::make_idesc_f8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, BN);
     p.bn = BN;
     p.debug = g_debug;
+    p.trace = g_trace.load(std::memory_order_relaxed);
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
     // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one

@@ -210,6 +210,37 @@ def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
         mem("copy bf16 [M,H] (torch, reference point for the short kernels)", lambda: x.clone(), 4 * M * H)
         del x, w1, fc1, da
 
+    if "lmhead" in args.only:
+        # lm_head + cross-entropy at the model's head shape, next to the reference's sequence in torch
+        # (bf16 matmul -> logits [M, V] -> fp32 cross-entropy), forward and forward + backward; bf16 tcgen05 GEMM vs cuBLAS at the head's shapes
+        V = {"llama1b": 128256, "llama3b": 128256, "llama8b": 128256, "qwen14b": 152064}[args.model]
+        Mh = min(M, 4096)
+        xh = (torch.randn(Mh, H, device=dev, generator=g)).bfloat16().requires_grad_(True)
+        wh = (torch.randn(V, H, device=dev, generator=g) * 0.02).bfloat16().requires_grad_(True)
+        lab = torch.randint(0, V, (Mh,), device=dev, generator=g)
+        fl = 2.0 * Mh * V * H
+
+        def rec_tf(name, fn, flops):
+            med, best = timeit(fn, iters=5, warm=2, flush=False)
+            emit({"kernel": f"{name} M={Mh} V={V} H={H}", "M": Mh, "ms": med, "ms_best": best, "TFLOPs": flops / med / 1e9,
+                  "frac_bf16_measured": flops / med / 1e9 / bf16_tf})
+
+        def ours_fb():
+            xh.grad = wh.grad = None
+            te.lm_head_cross_entropy(xh, wh, lab).backward()
+
+        def torch_fb():
+            xh.grad = wh.grad = None
+            torch.nn.functional.cross_entropy((xh @ wh.t()).float(), lab).backward()
+        with torch.no_grad():
+            rec_tf("lm_head loss fwd (ours: GEMM + CE statistics in the epilogue, no logits)", lambda: te.lm_head_cross_entropy(xh.detach(), wh.detach(), lab), fl)
+            rec_tf("lm_head loss fwd (torch: bf16 matmul + fp32 cross_entropy)", lambda: torch.nn.functional.cross_entropy((xh @ wh.t()).float(), lab), fl)
+            rec_tf("bf16 GEMM logits (ours, tcgen05 kind::f16)", lambda: te.bf16_gemm(xh.detach(), False, wh.detach(), False, Mh, V, H), fl)
+            rec_tf("bf16 GEMM logits (torch.matmul, cuBLAS)", lambda: xh @ wh.t(), fl)
+        rec_tf("lm_head loss fwd+bwd (ours: 4 GEMM passes)", ours_fb, 4 * fl)
+        rec_tf("lm_head loss fwd+bwd (torch: 3 GEMM passes + logits in fp32)", torch_fb, 3 * fl)
+        del xh, wh
+
     if not args.only or "gemm" in args.only:
         one = torch.ones(1, device=dev)
         layers = [("qkv", QKV, H), ("proj", H, H), ("fc1", 2 * I, H), ("fc2", H, I)]
