@@ -43,7 +43,6 @@ constexpr int GROUP_M = 16;      // rasterisation group, in 128-row blocks
 constexpr int MAX_STAGES = 8;
 constexpr int SF_COL0 = 448;     // TMEM columns 448..511: four rotating scale-factor buffers of 16 columns (SFA 4 + SFB up to 12), so the
 constexpr int SF_BUFS = 4;       // smem->TMEM copy for k-block i+1 never waits for the MMAs of k-block i to finish reading theirs
-constexpr int SF_STAGE_BYTES = 3 * 512;   // per stage and CTA: 1 SFA tile + 2 SFB tiles
 constexpr int SMEM_BUDGET = 227 * 1024;
 constexpr int EPI_BUF_BYTES = 4096;          // one TMA-store box: 32 rows x 128 B
 constexpr int EPI_BYTES = EPI_WARPS * EPI_BUF_BYTES;
@@ -66,8 +65,9 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no 224-column MX tiles, bit 9 = 224-column MX tiles also with an MN-major B under CTA pairs
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
+    int sf_tiles;               // MX: 512 B scale tiles per stage = 1 (SFA) + 2 or 3 (SFB)
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
     // cross-entropy epilogues of the bf16 lm_head GEMM (EPI 1 / 2)
     const int64_t* ce_labels;   // [M] class index per row
@@ -171,7 +171,8 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     uint8_t* smem = smem_raw + ((1024u - (ptx::smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the shared address space (STS, not generic ST)
     uint8_t* epi_base = smem + STAGES * stage_bytes;          // 8 epilogue warps x 4 KB, 1024 B aligned (128B-swizzled TMA-store boxes)
     uint8_t* sf_base = epi_base + EPI_BYTES;
-    GemmCtrl* ctrl = reinterpret_cast<GemmCtrl*>(sf_base + (MX ? STAGES * SF_STAGE_BYTES : 0));
+    const int sf_stage_bytes = MX ? 512 * p.sf_tiles : 0;
+    GemmCtrl* ctrl = reinterpret_cast<GemmCtrl*>(sf_base + STAGES * sf_stage_bytes);
     uint64_t* full_bar = ctrl->full;
     uint64_t* empty_bar = ctrl->empty;
     uint64_t* tmem_full = ctrl->tmem_full;
@@ -241,7 +242,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             const int b_chunks = p.b_rows_cta / CW;     // MN-major B: 128-byte-wide column chunks (the last one may over-fetch)
             const int bn_cta = BN / CG;
             const bool sf_load = MX && !(p.debug & 2);
-            const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? SF_STAGE_BYTES : 0));
+            const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? sf_stage_bytes : 0));
             int tile = unit, next_tile;
             for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
@@ -268,9 +269,9 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         for (int j = 0; j < b_chunks; j++) tma2d<CG>(&map_b, fb, fb_leader, sb + j * (BKE * 128), nb0 + j * CW, k0);
                     }
                     if (sf_load) {
-                        uint8_t* ssf = sf_base + stage * SF_STAGE_BYTES;
+                        uint8_t* ssf = sf_base + stage * sf_stage_bytes;
                         tma3d<CG>(&map_sfa, fb, fb_leader, ssf, 0, kb, m_blk * CG + static_cast<int>(rank));
-                        tma3d<CG>(&map_sfb, fb, fb_leader, ssf + 512, 0, kb, n0 >> 7);     // two 128-row scale tiles (zero-filled past the end)
+                        tma3d<CG>(&map_sfb, fb, fb_leader, ssf + 512, 0, kb, n0 >> 7);     // two (three at 224 columns) 128-row scale tiles, zero-filled past the end
                     }
                     }
                     __syncwarp();
@@ -315,10 +316,11 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     const uint32_t tmem_sf = tmem_base + SF_COL0 + 16 * sfi;
                     if (ptx::elect_one_sync()) {
                     if (MX && !((p.debug & 1) && (kb | tile) != 0)) {
-                        const uint32_t ssf = ptx::smem_u32(sf_base + stage * SF_STAGE_BYTES);
+                        const uint32_t ssf = ptx::smem_u32(sf_base + stage * sf_stage_bytes);
                         ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf, ptx::make_smem_desc(ssf, 0, 128, 0));
                         ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf + 4, ptx::make_smem_desc(ssf + 512, 0, 128, 0));
                         ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf + 8, ptx::make_smem_desc(ssf + 1024, 0, 128, 0));
+                        if (p.sf_tiles == 4) ptx::tc_cp_32x128b_warpx4_cg<CG>(tmem_sf + 12, ptx::make_smem_desc(ssf + 1536, 0, 128, 0));
                     }
 #pragma unroll
                     for (int k = 0; k < BK / UMMA_K; k++) {
@@ -405,7 +407,11 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             uint8_t* stg = epi_base + (warp - 2) * EPI_BUF_BYTES;
             int etrace_n = 0;
             const int ccols = p.out_fp32 ? 32 : 64;
-            const int nchunks = BN / ccols;
+            const int nchunks = (BN + ccols - 1) / ccols;
+            // column offset of chunk c inside the tile.  A tile width that is not a multiple of the chunk (224 = 3.5 x 64) lets the LAST chunk
+            // start early so that it ends with the tile: it re-stores 32 columns its neighbour chunk stores too — the same accumulators, the
+            // same bytes — instead of needing a second, narrower store box
+            auto coff = [&](int c) { return c * ccols + ccols <= BN ? c * ccols : BN - ccols; };
             if (lane == 0) ptx::prefetch_tensormap(&map_d);
             int tile = unit, next_tile;
             for (bool more = true; more; tile = next_tile) {
@@ -433,7 +439,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 uint4 rv[RES ? 8 : 1];
                 auto load_residual = [&](int c) {
                     const int row = row0 + lane;
-                    const int col = n0 + c * ccols;
+                    const int col = n0 + coff(c);
                     const uint16_t* rp = static_cast<const uint16_t*>(p.residual) + static_cast<int64_t>(row) * p.ldr + col;
 #pragma unroll
                     for (int g = 0; g < (RES ? 8 : 1); g++)
@@ -455,10 +461,10 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 const bool owns_shared = OVL && (p.out_fp32 || half == (acc == 0 ? 1 : 0));
 #pragma unroll 1
                 for (int c = walk_down ? half + 2 * (nmine - 1) : half, n = 0; OVL ? (n < nmine) : (c < nchunks); c += walk_down ? -2 : 2, n++) {
-                    const int col = n0 + c * ccols;
+                    const int col = n0 + coff(c);
                     uint32_t r0[32], r1[32];
-                    ptx::tmem_ld_32x32b_x32(taddr + c * ccols, r0);
-                    if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + c * ccols + 32, r1);
+                    ptx::tmem_ld_32x32b_x32(taddr + coff(c), r0);
+                    if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + coff(c) + 32, r1);
                     if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
                     ptx::tmem_ld_wait();
                     if (etr && lane == 0 && n < 2) etr[1 + n] = clock64();
@@ -737,23 +743,33 @@ static int dispatch(bool a_mn, bool b_mn, bool mx, const CUtensorMap& ma, const 
 
 // Tile width: minimise (waves x per-tile cost).  Narrow tiles cost more per column: their shared-memory traffic per MMA cycle is
 // higher (measured, profiles/r01_gemm_bn_sweep: 192 runs 10-25 % and 128 30-35 % below 256 in the 1-CTA kernel).
-static int pick_bn(int M, int N, bool mx, bool b_mn, int cg, int units) {
+static int pick_bn(int M, int N, int K, bool mx, bool b_mn, int cg, int units) {
+    const double k_cycles = 15500.0 * K / 4096.0;             // issue span of one 256 x 256 tile's main loop (measured at K = 4096)
     if (const int f = g_bn_override_a.load(std::memory_order_relaxed)) return f;
-    const int cand[3] = {256, 192, 128};
-    const double eff1[3] = {1.0, b_mn ? 0.76 : 0.88, 0.70};
-    const double eff2[3] = {1.0, 0.90, 0.80};
+    const int cand[4] = {256, 224, 192, 128};
+    const double eff1[4] = {1.0, 0.94, b_mn ? 0.76 : 0.88, 0.70};
+    const double eff2[4] = {1.0, 0.97, 0.90, 0.80};
     int best = 0;
     double best_cost = 1e300;
     const int num_m = (M + BM * cg - 1) / (BM * cg);
-    for (int i = 0; i < 3; i++) {
+    for (int i = 0; i < 4; i++) {
         const int bn = cand[i];
         if (cg == 2 && bn == 192 && b_mn) continue;           // 96 MN-major columns per CTA is not a whole swizzle chunk
+        if (bn == 224 && (!mx || (g_debug_a.load(std::memory_order_relaxed) & 256))) continue;   // 224 exists for the block-scaled kernel only (below)
+        if (bn == 224 && cg == 2 && b_mn && !(g_debug_a.load(std::memory_order_relaxed) & 512)) continue;   // 112 MN-major columns per CTA: behind debug bit 9 until validated
         if (bn > 128 && N <= bn - 64) continue;               // do not pad tiny N
         double e = cg == 2 ? eff2[i] : eff1[i];
-        if (mx) e *= bn > 192 ? 0.95 : 0.85;                   // MX at 256 has one accumulator (epilogue exposed); narrower tiles pay more scale copies per FLOP
+        if (mx) {
+            // 512 TMEM columns = accumulators + 64 columns of scale factors.  At 256 the two accumulators overlap by 64 columns: the next
+            // tile's MMAs wait until the previous tile has COMPLETED and its shared columns are drained — the tensor pipe runs empty once per
+            // tile (clock trace, profiles/r02/f_gemm_clock_trace_fc1.txt: ~2700 of ~19100 cycles per tile at K = 4096).  At 224 two whole
+            // accumulators fit ([0, 224), [224, 448)) and the pipe never drains; narrower tiles pay more scale copies per FLOP.
+            if (bn == 256) e *= k_cycles / (k_cycles + 2700.0);
+            else if (bn < 224) e *= 0.85;
+        }
         const long tiles = static_cast<long>(num_m) * ((N + bn - 1) / bn);
-        const long waves = (tiles + units - 1) / units;
-        const double cost = static_cast<double>(waves) * bn / e;
+        // tiles are handed to whichever cluster is free (cluster launch control): the cost is work plus half a tile of tail, not whole waves
+        const double cost = (static_cast<double>(tiles) / units + (tiles % units ? 0.5 : 0.0)) * bn / e;
         if (cost < best_cost) { best_cost = cost; best = bn; }
     }
     return best ? best : 128;
@@ -788,8 +804,8 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     if (grid < 2) cg = 1;
     if (cg == 2) grid &= ~1;
     const int units = grid / cg;
-    const int BN = pick_bn(M, N, mx, b_mn != 0, cg, units);
-    LLMFP8_REQUIRE(BN == 128 || BN == 192 || BN == 256, "fp8_gemm: tile width %d is not built", BN);
+    const int BN = pick_bn(M, N, K, mx, b_mn != 0, cg, units);
+    LLMFP8_REQUIRE(BN == 128 || BN == 192 || BN == 256 || (BN == 224 && mx), "fp8_gemm: tile width %d is not built", BN);
     LLMFP8_REQUIRE(cg == 1 || cg == 2, "fp8_gemm: cta group %d is not built", cg);
 
     GemmParams p = {};
@@ -804,8 +820,9 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
     // (debug bit 5 keeps the fused-residual kernel on a single accumulator)
     p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || !(g_debug & 32))) ? 1 : 0;
-    p.acc_stages = (mx && BN > 192 && !p.acc_overlap) ? 1 : 2;
-    const int stage_bytes = BM * BK + p.b_rows_cta * BK + (mx ? SF_STAGE_BYTES : 0);
+    p.acc_stages = (mx && BN > 224 && !p.acc_overlap) ? 1 : 2;      // 224 columns: two whole accumulators beside the scale factors
+    p.sf_tiles = mx ? (BN == 224 ? 4 : 3) : 0;
+    const int stage_bytes = BM * BK + p.b_rows_cta * BK + 512 * p.sf_tiles;
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;
     int stages = (SMEM_BUDGET - fixed) / stage_bytes;
     if (stages > MAX_STAGES) stages = MAX_STAGES;
@@ -831,7 +848,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
         const int64_t kt = (K + 127) / 128;
         rc = make_tensor_map_3d(&msa, sfa, CU_TENSOR_MAP_DATA_TYPE_UINT32, 128, kt, (M + 127) / 128, 512, 512 * kt, 128, 1, 1);
         if (rc) return rc;
-        rc = make_tensor_map_3d(&msb, sfb, CU_TENSOR_MAP_DATA_TYPE_UINT32, 128, kt, (N + 127) / 128, 512, 512 * kt, 128, 1, 2);
+        rc = make_tensor_map_3d(&msb, sfb, CU_TENSOR_MAP_DATA_TYPE_UINT32, 128, kt, (N + 127) / 128, 512, 512 * kt, 128, 1, p.sf_tiles - 1);
         if (rc) return rc;
     } else {
         msa = ma;
@@ -880,7 +897,7 @@ int launch_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_
     if (grid < 2) cg = 1;
     if (cg == 2) grid &= ~1;
     const int units = grid / cg;
-    const int BN = epi ? 256 : pick_bn(M, N, false, b_mn != 0, cg, units);
+    const int BN = epi ? 256 : pick_bn(M, N, K, false, b_mn != 0, cg, units);
     GemmParams p = {};
     p.d = d; p.ldd = ldd; p.M = M; p.N = N; p.K = K;
     p.bias = bias; p.accumulate = accumulate; p.out_fp32 = out_fp32;
