@@ -1,0 +1,24 @@
+#!/bin/bash
+# Final pass of round 2 on one B200 (the tree as it ships): GPU suite, headline bench lines (with the CPU baselines), reference arm, then the
+# ncu evidence for profiles/: launch list of a 2-layer step and --set full captures of EVERY GEMM launch of one step (fprop, dgrad, wgrad of
+# qkv / proj / fc1 / fc2) and of every quantiser, for the MXFP8 and the per-tensor scenario.  Summarise here with: python tools/ncu_summary.py r02
+mkdir -p gpurun_out
+timeout 500 python -m pytest tests/ -q -m gpu -p no:cacheprovider > gpurun_out/final_pytest_gpu.log 2>&1
+echo "pytest gpu exit $?  $(tail -1 gpurun_out/final_pytest_gpu.log)"; grep -E "^FAILED|^ERROR" gpurun_out/final_pytest_gpu.log | head
+python -c "import __graft_entry__ as g; g.smoke()" > gpurun_out/final_smoke.log 2>&1; echo "smoke exit $?"
+timeout 400 python bench.py --steps 20 --warmup 3 > gpurun_out/final_bench_mxfp8.json 2> gpurun_out/final_bench_mxfp8.err; echo "bench mxfp8 exit $?"
+timeout 300 python bench.py --steps 20 --warmup 3 --scenario default --no-cpu-baseline > gpurun_out/final_bench_default.json 2> gpurun_out/final_bench_default.err; echo "bench default exit $?"
+timeout 300 python bench.py --steps 20 --warmup 3 --scenario hybrid --no-cpu-baseline > gpurun_out/final_bench_hybrid.json 2> gpurun_out/final_bench_hybrid.err; echo "bench hybrid exit $?"
+timeout 300 python bench.py --impl reference --steps 5 --warmup 1 > gpurun_out/final_bench_reference.json 2> gpurun_out/final_bench_reference.err; echo "bench reference exit $?"
+timeout 300 python tools/microbench.py --model llama8b --out gpurun_out/final_micro_llama8b.jsonl > gpurun_out/final_micro.log 2>&1; echo "microbench exit $?"
+for sc in mxfp8 default; do
+  sfx=""; [ $sc = default ] && sfx="_pt"
+  CMD="python bench.py --layers 2 --steps 1 --warmup 3 --no-cpu-baseline --no-roofline --scenario $sc"
+  if [ $sc = mxfp8 ]; then
+    timeout 300 ncu --metrics gpu__time_duration.sum --clock-control none -c 1200 --csv --log-file gpurun_out/launches.csv $CMD > gpurun_out/final_ncu_list.log 2>&1; echo "ncu list exit $?"
+  fi
+  # 3 warm-up steps x 24 GEMM launches are skipped; the next 24 are one whole timed-region step of the 2-layer stack
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:fp8_gemm_kernel -s 72 -c 24 -f -o gpurun_out/prof_gemm$sfx $CMD > gpurun_out/final_ncu_gemm$sfx.log 2>&1; echo "ncu gemm $sc exit $?"
+  timeout 600 ncu --set full --clock-control none --import-source on -k regex:"quantize_kernel|swiglu|rmsnorm|cast_amax" -s 90 -c 40 -f -o gpurun_out/prof_quant$sfx $CMD > gpurun_out/final_ncu_quant$sfx.log 2>&1; echo "ncu quant $sc exit $?"
+done
+ls -la gpurun_out | head -40

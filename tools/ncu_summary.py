@@ -22,7 +22,8 @@ KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum
         "sm__cycles_elapsed.avg.per_second", "smsp__inst_executed.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum"]
 
 # first match wins (so "dswiglu" is tested before "swiglu")
-ENTRY = {"fp8_gemm_kernel": None, "mx_quantize_kernel": "llmfp8_mx_quantize", "dswiglu_quant_kernel": "llmfp8_dswiglu_quant_bwd",
+ENTRY = {"fp8_gemm_kernel": None, "mx_dswiglu_quantize_kernel": "llmfp8_mx_dswiglu_quantize", "mx_swiglu_quantize_kernel": "llmfp8_mx_swiglu_quantize",
+         "mx_quantize_kernel": "llmfp8_mx_quantize", "dswiglu_quant_kernel": "llmfp8_dswiglu_quant_bwd",
          "swiglu_quant_kernel": "llmfp8_swiglu_quant_fwd", "rmsnorm_fwd_kernel": "llmfp8_rmsnorm_quant_fwd", "rmsnorm_bwd_kernel": "llmfp8_rmsnorm_bwd",
          "cast_amax_bgrad_kernel": "llmfp8_quant_cast_amax_bgrad", "cast_amax_kernel": "llmfp8_quant_cast_amax"}
 
@@ -97,7 +98,7 @@ def main():
     launches(tag)
     tp = os.path.join(PROF, "ncu_traffic.json")
     traffic = json.load(open(tp)) if os.path.exists(tp) else {}
-    for name in ("prof_gemm", "prof_quant"):
+    for name in ("prof_gemm", "prof_quant", "prof_gemm_pt", "prof_quant_pt"):
         report(name, tag, traffic)
     json.dump(traffic, open(tp, "w"), indent=1)
     print(json.dumps(traffic, indent=1))
