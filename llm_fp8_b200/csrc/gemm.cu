@@ -65,7 +65,7 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no 224-column MX tiles, bit 9 = 224-column MX tiles also with an MN-major B under CTA pairs
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int sf_tiles;               // MX: 512 B scale tiles per stage = 1 (SFA) + 2 or 3 (SFB)
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
@@ -755,8 +755,12 @@ static int pick_bn(int M, int N, int K, bool mx, bool b_mn, int cg, int units) {
     for (int i = 0; i < 4; i++) {
         const int bn = cand[i];
         if (cg == 2 && bn == 192 && b_mn) continue;           // 96 MN-major columns per CTA is not a whole swizzle chunk
-        if (bn == 224 && (!mx || (g_debug_a.load(std::memory_order_relaxed) & 256))) continue;   // 224 exists for the block-scaled kernel only (below)
-        if (bn == 224 && cg == 2 && b_mn && !(g_debug_a.load(std::memory_order_relaxed) & 512)) continue;   // 112 MN-major columns per CTA: behind debug bit 9 until validated
+        // 224 columns (two whole accumulators beside the scale factors, no hand-over) is built and bit-identical to 256 on its FIRST column
+        // tile — and faults (misaligned address) on every other one: tiles then start 96 / 64 / 32 rows into a 128-row scale tile, and the
+        // block-scaled MMA takes its SFB operand from EVEN TMEM columns only (192-column tiles start at offsets 0 / 64: columns 0 / 2, fine;
+        // 224 needs columns 3 and 1; tcgen05.cp cannot shift by one column).  Measured on hardware (profiles/r02/g_gemm224_offsets.txt).
+        // Never picked: what remains is the forced single-tile case the test keeps alive for the 3-tile SFB / half-chunk code under it.
+        if (bn == 224) continue;
         if (bn > 128 && N <= bn - 64) continue;               // do not pad tiny N
         double e = cg == 2 ? eff2[i] : eff1[i];
         if (mx) {

@@ -206,11 +206,9 @@ def test_fp8_gemm_forced_variant(cg, bn, a_mn, b_mn, force):
     check(got, want + bias.float(), tol=1e-5)
 
 
-@pytest.mark.parametrize("cg,bn", VARIANTS + [(2, 192), (1, 224), (2, 224)])
+@pytest.mark.parametrize("cg,bn", VARIANTS + [(2, 192)])
 def test_mxfp8_gemm_forced_variant(cg, bn, force):
-    """MX with every variant: 192 starts every other tile 64 rows into a 128-row scale tile (TMEM column offset 2); 224 (two whole
-    accumulators beside the scale factors) starts tiles 0 / 96 / 64 / 32 rows into one, straddles three scale tiles, and ends with a
-    half-width epilogue chunk."""
+    """MX with every variant: 192 starts every other tile 64 rows into a 128-row scale tile (TMEM column offset 2)."""
     ops = _ops()
     force(bn, cg)
     M, N, K = 640, 1600, 1024
@@ -395,25 +393,21 @@ def test_mxfp8_dgrad_wgrad_at_8b_shapes_vs_oracle_sample(name, T, N, K):
     check(dwb[nrows.cuda()], ref_matmul(deq_col(dyo, T, N).t()[nrows], deq_col(xo, T, K).t()))
 
 
-@pytest.mark.parametrize("M,N,K", [(6144, 28672, 4096), (6144, 4096, 4096), (1000, 3000, 2080)])
-def test_mxfp8_gemm_224_matches_256_bit_for_bit(M, N, K, force):
-    """The 224-column tiling changes which CTA computes which columns, not the arithmetic: every output element is the same fp32 sum of the
-    same products in the same k order, rounded once — bit-identical to the 256-column kernel, bf16 and fp32 outputs, with bias and residual."""
+@pytest.mark.parametrize("cg", [1, 2])
+def test_mxfp8_gemm_224_single_column_tile_matches_256(cg, force):
+    """224-column tiles (two whole TMEM accumulators beside the scale factors) work — bit-identical to 256 — only while every tile starts on a
+    scale-tile boundary, i.e. for N <= 224: any further tile starts 96 / 64 / 32 rows into a scale tile and the block-scaled MMA rejects the odd
+    SFB column (gemm.cu: pick_bn).  This keeps the code under it (third SFB tile per stage, re-storing last epilogue chunk) exercised."""
     ops = _ops()
-    dev = "cuda"
-    g = torch.Generator(device=dev).manual_seed(M + N + K)
-    x = torch.randint(0, 120, (M, K), device=dev, dtype=torch.uint8, generator=g)
-    w = torch.randint(0, 120, (N, K), device=dev, dtype=torch.uint8, generator=g)
-    sx = torch.randint(120, 134, (ops.mx_scale_bytes(M, K),), device=dev, dtype=torch.uint8, generator=g)
-    sw = torch.randint(120, 134, (ops.mx_scale_bytes(N, K),), device=dev, dtype=torch.uint8, generator=g)
-    bias = torch.randn(N, device=dev, generator=g).bfloat16()
-    res = torch.randn(M, N, device=dev, generator=g).bfloat16() * 100
-    out = {}
-    for bn in (256, 224):
-        force(bn, 0)
-        out[bn] = (ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias),
-                   ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, out_dtype=torch.float32),
-                   ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res))
+    M, N, K = 512, 224, 512
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randint(0, 120, (M, K), device="cuda", dtype=torch.uint8, generator=g)
+    w = torch.randint(0, 120, (N, K), device="cuda", dtype=torch.uint8, generator=g)
+    sx = torch.randint(120, 134, (ops.mx_scale_bytes(M, K),), device="cuda", dtype=torch.uint8, generator=g)
+    sw = torch.randint(120, 134, (ops.mx_scale_bytes(N, K),), device="cuda", dtype=torch.uint8, generator=g)
+    force(256, cg)
+    want = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K)
+    force(224, cg)
+    got = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K)
     torch.cuda.synchronize()
-    for a, b in zip(out[256], out[224]):
-        assert torch.equal(a, b)
+    assert torch.equal(want, got)
