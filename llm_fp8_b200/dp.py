@@ -72,12 +72,13 @@ class GradAllReducer:
         NCCL's NVLS algorithms have no AVG / pre-multiplied sum, so with AVG it falls back to a 32-channel ring.  Measured at 8 B200s
         (mxfp8, same box): SUM -> NVLS / 24 channels 170.7 ms per step, AVG -> Ring 175.0 ms.  DDP itself pre-divides
         (train_multi_gpu.py:355-378).  A caller that ignores `loss_scale` gets summed, not averaged, gradients."""
-        # bucket_bytes > 0 (LLMFP8_GRAD_BUCKET_MB; default 0 = one collective per gradient): large gradients are held back until that many
+        # bucket_bytes > 0 (LLMFP8_GRAD_BUCKET_MB; 0 = one collective per gradient): large gradients are held back until that many
         # bytes are pending and then all-reduced as ONE coalesced group (ncclGroupStart / End: one fused launch over the gradients' own
         # memory, still no copies) — 6 collectives per decoder layer become 1-2, at the price of starting each a little later.
-        # Unmeasured (written after the round-1 GPU budget was spent); tools/gpu_round2_scale.sh has the A/B.
         if bucket_bytes is None:
-            bucket_bytes = int(float(os.environ.get("LLMFP8_GRAD_BUCKET_MB", "0")) * (1 << 20))
+            # default 256 MB: measured on 8 B200s (profiles/r02/scale8_*): one collective per gradient 171.9 ms per step (6.45x one GPU, 35 ms
+            # of reductions still outstanding when backward returns), 256 MB groups 154.8 ms (7.17x, 12 ms outstanding)
+            bucket_bytes = int(float(os.environ.get("LLMFP8_GRAD_BUCKET_MB", "256")) * (1 << 20))
         self.bucket_bytes = max(0, int(bucket_bytes))
         self._pending: List[torch.Tensor] = []
         self._pending_bytes = 0

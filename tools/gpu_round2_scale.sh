@@ -42,6 +42,9 @@ run cga1 NCCL_CGA_CLUSTER_SIZE=1
 run cg1 LLMFP8_GEMM_FORCE_CG=1                         # single-CTA GEMM tiles: do they coexist better with the all-reduce kernels?
 run bucket256 LLMFP8_GRAD_BUCKET_MB=256                # coalesced gradient groups: ~2 NCCL launches per decoder layer instead of 6
 run bucket512 LLMFP8_GRAD_BUCKET_MB=512                # ~1 per layer
+run bucket128 LLMFP8_GRAD_BUCKET_MB=128
+run bucket1024 LLMFP8_GRAD_BUCKET_MB=1024
+run bucket0 LLMFP8_GRAD_BUCKET_MB=0                    # one collective per gradient (the round-1 behaviour)
 # in-switch gradient reduce (own multimem kernel, csrc/nvls_reduce.cu) — only after tools/gpu_nvls2.sh passed on two GPUs
 run nvls32 LLMFP8_NVLS_REDUCE=1
 run nvls8 LLMFP8_NVLS_REDUCE=1 LLMFP8_NVLS_CTAS=8
