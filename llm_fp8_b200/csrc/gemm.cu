@@ -65,11 +65,9 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = no 448-column MX super-tiles, bit 9 = super-tiles also with an MN-major B under CTA pairs (96 columns per CTA)
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int sf_tiles;               // MX: 512 B scale tiles per stage = 1 (SFA) + 2 or 3 (SFB)
-    int st;                     // MX super-tiles: a unit of work is 448 output columns = a 256-column sub-tile + a 192-column one (kernel comment)
-    uint32_t idesc_b;           // super-tiles: instruction descriptor of the 192-column sub-tile
     int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
     // cross-entropy epilogues of the bf16 lm_head GEMM (EPI 1 / 2)
     const int64_t* ce_labels;   // [M] class index per row
@@ -184,25 +182,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const uint32_t rank = CG == 2 ? ptx::cluster_ctarank() : 0u;    // 0 = leader (issues the MMAs)
     const int unit = blockIdx.x / CG, num_units = gridDim.x / CG;     // dynamic mode: unit = this cluster's own (first) tile
-    // Super-tiles (MX, staged epilogue).  512 TMEM columns hold 64 columns of scale factors and EITHER two 256-column accumulators that
-    // overlap by 64 (OVL: the next tile's MMAs wait until the previous tile has completed and drained the shared columns — the tensor pipe
-    // runs empty once per tile: ~2700 of ~19100 cycles at K = 4096, profiles/r02/f_gemm_clock_trace_fc1.txt) OR one of 256 and one of 192 side
-    // by side.  So the unit of work becomes 448 output columns: a 256-column sub-tile on the accumulator at column 0, then a 192-column one on
-    // the accumulator at column 256, each with its own epilogue — consecutive sub-tiles always alternate accumulators, no hand-over, the pipe
-    // never drains.  Every sub-tile starts on a multiple of 64 columns, so its SFB operand sits at an even TMEM column (224-column tiles, the
-    // uniform alternative, fault on that: pick_bn).  A ragged last unit has one sub-tile only (192 wide if that covers the rest).
-    const bool ST = MX && p.st != 0;
-    constexpr int ST_W = 448;
-    const int num_m = (p.M + TM - 1) / TM, num_n = ST ? (p.N + ST_W - 1) / ST_W : (p.N + BN - 1) / BN;
-    struct SubTile { int n0, bn, acc; };
-    auto sub_tiles = [&](int n_blk, SubTile (&st)[2]) {
-        if (!ST) { st[0].n0 = n_blk * BN; st[0].bn = BN; st[0].acc = -1; return 1; }
-        const int base = n_blk * ST_W, rem = p.N - base;
-        st[0].n0 = base; st[0].bn = 256; st[0].acc = 0;
-        if (rem > 256) { st[1].n0 = base + 256; st[1].bn = 192; st[1].acc = 1; return 2; }
-        if (rem <= 192) { st[0].bn = 192; st[0].acc = 1; }
-        return 1;
-    };
+    const int num_m = (p.M + TM - 1) / TM, num_n = (p.N + BN - 1) / BN;
     const int num_tiles = num_m * num_n;
     const int num_kb = (p.K + BKE - 1) / BKE;
 
@@ -260,17 +240,14 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
         {
             int stage = 0, phase = 0;
             const int b_chunks = p.b_rows_cta / CW;     // MN-major B: 128-byte-wide column chunks (the last one may over-fetch)
+            const int bn_cta = BN / CG;
             const bool sf_load = MX && !(p.debug & 2);
             const uint32_t tx_bytes = CG * (stage_bytes + (sf_load ? sf_stage_bytes : 0));
             int tile = unit, next_tile;
             for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
-                const int m0 = m_blk * TM + rank * BM;
-                SubTile sts[2];
-                const int nsub = sub_tiles(n_blk, sts);
-                for (int si = 0; si < nsub; si++) {
-                const int n0 = sts[si].n0, nb0 = n0 + rank * (sts[si].bn / CG);     // a 192-column sub-tile over-fetches B rows into the 256-column slot
+                const int m0 = m_blk * TM + rank * BM, n0 = n_blk * BN, nb0 = n0 + rank * bn_cta;
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&empty_bar[stage], phase ^ 1);     // all lanes poll (keeps the warp converged and its values uniform)
                     if (ptx::elect_one_sync()) {
@@ -300,15 +277,13 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     __syncwarp();
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
-                }
                 more = sched.advance(tile, next_tile);
             }
         }
     } else if (warp == 1) {
         // ================================ MMA issuer (one thread of the leader CTA)
         if (rank == 0) {
-            int stage = 0, phase = 0, acc = 0, sfi = 0;
-            uint32_t use_par = 0;               // bit a: parity of how often accumulator a has been handed to the epilogue (its barriers' phase)
+            int stage = 0, phase = 0, acc = 0, acc_phase = 0, sfi = 0;
             int tiles_done = 0;                 // OVL: tiles this cluster has issued so far
             int trace_n = 0;
             constexpr uint32_t A_LBO = A_MN ? (BKE * 128) : 16, B_LBO = B_MN ? (BKE * 128) : 16;      // MN-major: distance between 128 B atoms
@@ -319,16 +294,11 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 tile_coords(tile, m_blk, n_blk);
                 // MX: the scale of column n lives in TMEM column (sf buffer) + 4 + (n - 128 * (n0 / 128)) / 32: a tile that starts 64 rows
                 // into a 128-row scale tile (BN = 192) skips the leading 32-row groups by advancing the column address
-                SubTile sts[2];
-                const int nsub = sub_tiles(n_blk, sts);
-                for (int si = 0; si < nsub; si++) {
-                if (ST) acc = sts[si].acc;
-                const uint32_t idesc_t = (ST && sts[si].bn == 192) ? p.idesc_b : p.idesc;
-                const uint32_t sfb_off = 4 + ((sts[si].n0 & 127) >> 5);
+                const uint32_t sfb_off = 4 + (((n_blk * BN) & 127) >> 5);
                 unsigned long long* tr = (p.trace && blockIdx.x == 0 && trace_n < 64) ? p.trace + 16 * trace_n : nullptr;
                 trace_n++;
                 if (tr && lane == 0) tr[0] = clock64();
-                ptx::mbar_wait(&tmem_empty[acc], ((use_par >> acc) & 1) ^ 1);
+                ptx::mbar_wait(&tmem_empty[acc], acc_phase ^ 1);
                 if (tr && lane == 0) tr[1] = clock64();
                 if constexpr (OVL) {
                     if (tiles_done > 0) ptx::mbar_wait(&ctrl->ovl_free, (tiles_done - 1) & 1);   // previous tile's shared columns are in registers
@@ -336,7 +306,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 }
                 if (tr && lane == 0) tr[2] = clock64();
                 ptx::tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * (ST ? 256 : (OVL ? OVL_STRIDE : BN));
+                const uint32_t tmem_d = tmem_base + acc * (OVL ? OVL_STRIDE : BN);
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     if (tr && lane == 0 && kb == 0) tr[3] = clock64();
@@ -358,7 +328,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         const uint64_t db = ptx::make_smem_desc(sb + k * B_KSTEP, B_LBO, 1024, 2);
                         const uint32_t accum = (kb | k) != 0;
                         if (MX) {
-                            const uint32_t idesc = idesc_t | (static_cast<uint32_t>(k) << 4) | (static_cast<uint32_t>(k) << 29);
+                            const uint32_t idesc = p.idesc | (static_cast<uint32_t>(k) << 4) | (static_cast<uint32_t>(k) << 29);
                             ptx::mma_mxf8f6f4_cg<CG>(tmem_d, da, db, idesc, accum, tmem_sf, tmem_sf + sfb_off);
                         } else if (BF) {
                             ptx::mma_f16_cg<CG>(tmem_d, da, db, p.idesc, accum);
@@ -375,9 +345,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 if (tr && lane == 0) tr[4] = clock64();
                 if (ptx::elect_one_sync()) ptx::tc_commit_cg<CG>(&tmem_full[acc]);         // accumulator complete -> epilogue warps of both CTAs
                 __syncwarp();
-                use_par ^= 1u << acc;
-                if (!ST && ++acc == ACC_STAGES) acc = 0;
-                }
+                if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
                 more = sched.advance(tile, next_tile);
             }
         } else {
@@ -439,23 +407,18 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             uint8_t* stg = epi_base + (warp - 2) * EPI_BUF_BYTES;
             int etrace_n = 0;
             const int ccols = p.out_fp32 ? 32 : 64;
-            uint32_t use_par = 0;               // bit a: parity of how often this warp has drained accumulator a
+            const int nchunks = (BN + ccols - 1) / ccols;
+            // column offset of chunk c inside the tile.  A tile width that is not a multiple of the chunk (224 = 3.5 x 64) lets the LAST chunk
+            // start early so that it ends with the tile: it re-stores 32 columns its neighbour chunk stores too — the same accumulators, the
+            // same bytes — instead of needing a second, narrower store box
+            auto coff = [&](int c) { return c * ccols + ccols <= BN ? c * ccols : BN - ccols; };
             if (lane == 0) ptx::prefetch_tensormap(&map_d);
             int tile = unit, next_tile;
             for (bool more = true; more; tile = next_tile) {
                 int m_blk, n_blk;
                 tile_coords(tile, m_blk, n_blk);
                 const int row0 = m_blk * TM + static_cast<int>(rank) * BM + quad * 32;
-                SubTile sts[2];
-                const int nsub = sub_tiles(n_blk, sts);
-                for (int si = 0; si < nsub; si++) {
-                if (ST) acc = sts[si].acc;
-                const int n0 = sts[si].n0, BNs = sts[si].bn;
-                const int nchunks = (BNs + ccols - 1) / ccols;
-                // column offset of chunk c inside the tile.  A tile width that is not a multiple of the chunk (224 = 3.5 x 64) lets the LAST chunk
-                // start early so that it ends with the tile: it re-stores 32 columns its neighbour chunk stores too — the same accumulators, the
-                // same bytes — instead of needing a second, narrower store box
-                auto coff = [&](int c) { return c * ccols + ccols <= BNs ? c * ccols : BNs - ccols; };
+                const int n0 = n_blk * BN;
                 // cross-entropy epilogues: this lane's row
                 int64_t ce_lab = -1;
                 float ce_m = -INFINITY, ce_s = 0.f, ce_ll = 0.f, ce_lse = 0.f, ce_gs = 0.f;
@@ -485,11 +448,11 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 unsigned long long* etr = (p.trace && blockIdx.x == 0 && (warp == 2 || warp == 6) && etrace_n < 64) ? p.trace + 16 * etrace_n + (warp == 2 ? 5 : 10) : nullptr;
                 etrace_n++;
                 if constexpr (RES) load_residual((OVL && acc == 0) ? half + 2 * (((nchunks - half + 1) >> 1) - 1) : half);   // the chunk the walk below starts with
-                if (p.debug & 128) ptx::mbar_wait_backoff(&tmem_full[acc], (use_par >> acc) & 1, 128);      // experiment: sleeping instead of spinning epilogue warps
-                else ptx::mbar_wait(&tmem_full[acc], (use_par >> acc) & 1);
+                if (p.debug & 128) ptx::mbar_wait_backoff(&tmem_full[acc], acc_phase, 128);      // experiment: sleeping instead of spinning epilogue warps
+                else ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
                 if (etr && lane == 0) etr[0] = clock64();
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (ST ? 256 : (OVL ? OVL_STRIDE : BN));
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
                 // OVL: this warp's chunks are walked so that the one lying in the shared columns [192, 256) comes first — the LAST chunk of
                 // the accumulator at column 0 (walk down), the FIRST chunk of the one at column 192 (walk up).  bf16 output: 64-column
                 // chunks, the shared one belongs to one `half`; fp32 output: 32-column chunks, each half owns one of the two shared chunks.
@@ -606,9 +569,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                         if (ce_hit) p.ce_label_logit[row0 + lane] = ce_ll;
                     }
                 }
-                use_par ^= 1u << acc;
-                if (!ST && ++acc == ACC_STAGES) acc = 0;
-                }
+                if (++acc == ACC_STAGES) { acc = 0; acc_phase ^= 1; }
                 more = sched.advance(tile, next_tile);
             }
             if (lane == 0) ptx::tma_store_wait<0>();
@@ -860,15 +821,11 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     p.trace = g_trace.load(std::memory_order_relaxed);
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 127) / 128 * 128 : bn_cta;
-    // MX where the heuristic wants 256 columns, staged epilogue: 448-column super-tiles (a 256- and a 192-column accumulator side by side: kernel
-    // comment) when the main loop is short enough for the 256-column hand-over to matter and N is wide enough to alternate; debug bit 8 turns
-    // them off.  Otherwise two overlapped accumulators (OVL kernels); debug bit 4 falls back to one (debug bit 5 keeps the fused-residual
-    // kernel on a single accumulator)
-    p.st = (mx && BN == 256 && !accumulate && N > 256 && K <= 8192 && !(g_debug & 256) && !(cg == 2 && b_mn && !(g_debug & 512))) ? 1 : 0;
-    p.idesc_b = p.st ? ptx::make_idesc_mxf8(a_fmt, b_fmt, a_mn, b_mn, BM * cg, 192, 0, 0) : 0;
-    p.acc_overlap = (!p.st && !(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || !(g_debug & 32))) ? 1 : 0;
-    p.acc_stages = (mx && BN > 224 && !p.acc_overlap && !p.st) ? 1 : 2;      // 224 columns: two whole accumulators beside the scale factors
-    p.sf_tiles = mx ? ((BN == 224 || p.st) ? 4 : 3) : 0;
+    // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
+    // (debug bit 5 keeps the fused-residual kernel on a single accumulator)
+    p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || !(g_debug & 32))) ? 1 : 0;
+    p.acc_stages = (mx && BN > 224 && !p.acc_overlap) ? 1 : 2;      // 224 columns: two whole accumulators beside the scale factors
+    p.sf_tiles = mx ? (BN == 224 ? 4 : 3) : 0;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + 512 * p.sf_tiles;
     const int fixed = 1024 /*alignment slack*/ + CTRL_BYTES /*barriers, CLC responses*/ + EPI_BYTES /*epilogue staging*/;
     int stages = (SMEM_BUDGET - fixed) / stage_bytes;
@@ -902,7 +859,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
         msb = mb;
     }
 
-    const int num_tiles = ((M + BM * cg - 1) / (BM * cg)) * (p.st ? (N + 447) / 448 : (N + BN - 1) / BN);
+    const int num_tiles = ((M + BM * cg - 1) / (BM * cg)) * ((N + BN - 1) / BN);
     // dynamic (default): one cluster per tile, handed out by cluster launch control; static (debug bit 3, or a caller-imposed CTA
     // budget): persistent grid, round-robin tiles
     p.dynamic = ((g_debug & 8) || max_ctas > 0) ? 0 : 1;

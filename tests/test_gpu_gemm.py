@@ -411,41 +411,3 @@ def test_mxfp8_gemm_224_single_column_tile_matches_256(cg, force):
     got = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K)
     torch.cuda.synchronize()
     assert torch.equal(want, got)
-
-
-@pytest.mark.parametrize("cg", [1, 2])
-@pytest.mark.parametrize("layout", ["fprop", "dgrad", "wgrad"])
-@pytest.mark.parametrize("M,N,K", [(512, 448, 512), (1000, 3000, 2080), (640, 1544, 640), (6144, 4096, 4096), (768, 704, 1024), (384, 640, 512)])
-def test_mxfp8_gemm_super_tiles_bit_identical(M, N, K, layout, cg, force):
-    """448-column super-tiles (a 256- and a 192-column TMEM accumulator side by side; gemm.cu) against the 256-column overlapped-accumulator
-    kernel (debug bit 8): the tiling decides which CTA computes which columns, not the arithmetic — every element is the same fp32 sum of the
-    same products in the same k order, rounded once — so results are bit-identical: bf16 and fp32 outputs, bias, fused residual, ragged last
-    units with one sub-tile (N mod 448 in (0, 192], (192, 256], (256, 448))."""
-    ops = _ops()
-    from llm_fp8_b200 import _lib
-    lib = _lib.load()
-    if layout != "fprop" and (M % 32 or N % 32):
-        pytest.skip("MN-major MX operands need whole 32-row blocks")
-    dev = "cuda"
-    g = torch.Generator(device=dev).manual_seed(M + N + K)
-    a_mn, b_mn = layout == "wgrad", layout != "fprop"
-    a = torch.randint(0, 120, (K, M) if a_mn else (M, K), device=dev, dtype=torch.uint8, generator=g)
-    b = torch.randint(0, 120, (K, N) if b_mn else (N, K), device=dev, dtype=torch.uint8, generator=g)
-    sa = torch.randint(120, 134, (ops.mx_scale_bytes(M, K),), device=dev, dtype=torch.uint8, generator=g)
-    sb = torch.randint(120, 134, (ops.mx_scale_bytes(N, K),), device=dev, dtype=torch.uint8, generator=g)
-    bias = torch.randn(N, device=dev, generator=g).bfloat16()
-    res = torch.randn(M, N, device=dev, generator=g).bfloat16() * 100
-    out = {}
-    try:
-        for mode in (256, 512):                        # 256: no super-tiles; 512: super-tiles also for an MN-major B under CTA pairs
-            lib.llmfp8_gemm_debug(mode)
-            force(256, cg)
-            o = [ops.mxfp8_gemm(a, sa, a_mn, b, sb, b_mn, M, N, K, bias=bias), ops.mxfp8_gemm(a, sa, a_mn, b, sb, b_mn, M, N, K, out_dtype=torch.float32)]
-            if layout == "fprop":
-                o.append(ops.mxfp8_gemm(a, sa, a_mn, b, sb, b_mn, M, N, K, bias=bias, residual=res))
-            torch.cuda.synchronize()
-            out[mode] = o
-    finally:
-        lib.llmfp8_gemm_debug(0)
-    for x, y in zip(out[256], out[512]):
-        assert torch.equal(x, y)
