@@ -76,9 +76,10 @@ class GradAllReducer:
         # bytes are pending and then all-reduced as ONE coalesced group (ncclGroupStart / End: one fused launch over the gradients' own
         # memory, still no copies) — 6 collectives per decoder layer become 1-2, at the price of starting each a little later.
         if bucket_bytes is None:
-            # default 256 MB: measured on 8 B200s (profiles/r02/scale8_*): one collective per gradient 171.9 ms per step (6.45x one GPU, 35 ms
-            # of reductions still outstanding when backward returns), 256 MB groups 154.8 ms (7.17x, 12 ms outstanding)
-            bucket_bytes = int(float(os.environ.get("LLMFP8_GRAD_BUCKET_MB", "256")) * (1 << 20))
+            # default 512 MB: measured on 8 B200s (profiles/r02/scale8*_*): one collective per gradient 171.9 ms per step (6.45x one GPU, 35 ms
+            # of reductions still outstanding when backward returns); groups of 128 / 256 / 512 / 1024 MB 154.5 / 154.8 / 152.1 / 152.5 ms
+            # (7.0-7.2x, 9-12 ms outstanding)
+            bucket_bytes = int(float(os.environ.get("LLMFP8_GRAD_BUCKET_MB", "512")) * (1 << 20))
         self.bucket_bytes = max(0, int(bucket_bytes))
         self._pending: List[torch.Tensor] = []
         self._pending_bytes = 0
