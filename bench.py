@@ -445,6 +445,10 @@ def main():
             d = by.setdefault(n, {"unit": u, "work": 0.0, "ms": 0.0, "launches": 0})
             d["work"] += w; d["ms"] += ms; d["launches"] += 1
         shares = {n.replace("llmfp8_", ""): round(d["ms"] / tot, 4) for n, d in sorted(by.items(), key=lambda kv: -kv[1]["ms"])}
+        # what the step spends OUTSIDE this library's kernels (torch ops of the stand-in loss and attention slice, launch gaps): the timed step
+        # minus the sum of the per-launch times of the serialised profile step
+        shares["_library_kernels_ms"] = round(tot, 3)
+        shares["_step_ms_minus_library_kernels_ms"] = round(ms_step - tot, 3)
         gname = "llmfp8_mxfp8_gemm" if a.scenario == "mxfp8" else "llmfp8_fp8_gemm"
         traffic = None
         tp = os.path.join(ROOT, "profiles", "ncu_traffic.json")

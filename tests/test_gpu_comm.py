@@ -66,10 +66,6 @@ def test_cabi_nccl_single_rank_roundtrip():
 
 
 # ------------------------------------------------------------------------------------------------ in-switch gradient reduce (NVLS)
-EXPERIMENTAL = pytest.mark.skipif(os.environ.get("LLMFP8_EXPERIMENTAL", "0") != "1",
-                                  reason="code path written without a GPU at hand: set LLMFP8_EXPERIMENTAL=1 to run it")
-
-
 def _nvls_worker(rank, world, port, out):
     """(1) llmfp8_nvls_allreduce_sum_bf16 on arena homes of awkward sizes, launched back to back on a side stream (signal pads reused),
     against the sum computed on the host; (2) a 2-block FP8 stack stepped once with the NCCL reducer and once with the in-switch
@@ -170,7 +166,6 @@ def _nvls_worker(rank, world, port, out):
     dist.destroy_process_group()
 
 
-@EXPERIMENTAL
 @pytest.mark.timeout(300)
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
 def test_nvls_gradient_reduce_two_gpus(tmp_path):

@@ -7,7 +7,7 @@ mkdir -p gpurun_out
 # data-parallel correctness of the FP8 path (tests/test_gpu_dp2.py): scales identical across ranks, gradients == single GPU on the concatenated batch
 timeout 500 python -m pytest tests/test_gpu_dp2.py tests/test_gpu_comm.py -q -s -m gpu -p no:cacheprovider > gpurun_out/r02_test_dp2.log 2>&1
 echo "test_dp2 exit $?"; grep -E "^\[dp2\]|passed|failed" gpurun_out/r02_test_dp2.log
-LLMFP8_EXPERIMENTAL=1 timeout 280 python -m pytest tests/test_gpu_comm.py -x -q -m gpu -p no:cacheprovider -k nvls > gpurun_out/r02_test_nvls2.log 2>&1
+timeout 280 python -m pytest tests/test_gpu_comm.py -x -q -m gpu -p no:cacheprovider -k nvls > gpurun_out/r02_test_nvls2.log 2>&1
 rc=$?; echo "test_nvls exit $rc"; tail -25 gpurun_out/r02_test_nvls2.log
 [ $rc -ne 0 ] && exit $rc
 LLMFP8_DIST_TIMEOUT_S=90 timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node 2 --master-addr 127.0.0.1 --master-port 29531 \
