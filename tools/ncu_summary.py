@@ -60,9 +60,13 @@ def launches(tag):
 
 def report(name, tag, traffic):
     rep = os.path.join(OUT, f"{name}.ncu-rep")
-    if not os.path.exists(rep):
+    csv_path = os.path.join(OUT, f"{name}_raw.csv")       # exported on the GPU box (the reports themselves exceed gpurun's 64 MiB return limit)
+    if os.path.exists(csv_path):
+        raw = open(csv_path).read()
+    elif os.path.exists(rep):
+        raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
+    else:
         return
-    raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(raw.splitlines()))
     hdr, units = rows[0], rows[1]
     idx = {h: i for i, h in enumerate(hdr)}
