@@ -210,6 +210,54 @@ def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
         mem("copy bf16 [M,H] (torch, reference point for the short kernels)", lambda: x.clone(), 4 * M * H)
         del x, w1, fc1, da
 
+    if "sustained" in args.only:
+        # the twelve GEMMs of one decoder layer (fprop, dgrad, wgrad of qkv / proj / fc1 / fc2) back to back for ~3 s: what the GEMMs alone
+        # sustain under the board's power cap — the ceiling for the in-step GEMM rate bench.py reports (roofline.achieved)
+        import time
+        one = torch.ones(1, device=dev)
+        ops_list, fl = [], 0.0
+        for lname, N, K in [("qkv", QKV, H), ("proj", H, H), ("fc1", 2 * I, H), ("fc2", H, I)]:
+            xb = torch.randn(M, K, device=dev, generator=g).bfloat16()
+            wb = (torch.randn(N, K, device=dev, generator=g) * 0.02).bfloat16()
+            dyb = (torch.randn(M, N, device=dev, generator=g) * 1e-3).bfloat16()
+            xm, wm, dym = ops.mx_quantize(xb, True, True), ops.mx_quantize(wb, True, True), ops.mx_quantize(dyb, True, True)
+            X, W, DY = ops.QTensor(xm.row, 0, one), ops.QTensor(wm.row, 0, one), ops.QTensor(dym.row, 1, one)
+            for mx in (False, True):
+                if mx:
+                    fns = [lambda xm=xm, wm=wm, N=N, K=K: ops.mxfp8_gemm(xm.row, xm.sf_row, False, wm.row, wm.sf_row, False, M, N, K),
+                           lambda dym=dym, wm=wm, N=N, K=K: ops.mxfp8_gemm(dym.row, dym.sf_row, False, wm.col, wm.sf_col, True, M, K, N),
+                           lambda dym=dym, xm=xm, N=N, K=K: ops.mxfp8_gemm(dym.col, dym.sf_col, True, xm.col, xm.sf_col, True, N, K, M)]
+                else:
+                    fns = [lambda X=X, W=W, N=N, K=K: ops.fp8_gemm(X, False, W, False, M, N, K),
+                           lambda DY=DY, W=W, N=N, K=K: ops.fp8_gemm(DY, False, W, True, M, K, N),
+                           lambda DY=DY, X=X, N=N, K=K: ops.fp8_gemm(DY, True, X, True, N, K, M)]
+                ops_list.append((mx, fns))
+            fl += 3 * 2.0 * M * N * K
+        for want_mx in (True, False):
+            fns = [f for mx, fs in ops_list if mx == want_mx for f in fs]
+            for f in fns:
+                f()
+            torch.cuda.synchronize()
+            global _clocks, _last_clocks
+            if _clocks is None:
+                _clocks = NvmlClocks(torch.cuda.current_device())
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            with _clocks:
+                t0, n = time.time(), 0
+                e0.record()
+                while time.time() - t0 < 3.0:
+                    for f in fns:
+                        f()
+                    n += 1
+                    if n % 8 == 0:
+                        torch.cuda.synchronize()
+                e1.record()
+                torch.cuda.synchronize()
+            _last_clocks = _clocks.record()
+            ms = e0.elapsed_time(e1) / n
+            emit({"kernel": f"sustained: the 12 GEMMs of a layer back to back, {'mxfp8' if want_mx else 'per-tensor'}, {n} rounds", "M": M, "ms": ms,
+                  "TFLOPs": fl / ms / 1e9, "frac_2x_bf16_sustained_proxy": None, "frac_fp8_nominal": fl / ms / 1e9 / 4500.0})
+
     if "lmhead" in args.only:
         # lm_head + cross-entropy at the model's head shape, next to the reference's sequence in torch
         # (bf16 matmul -> logits [M, V] -> fp32 cross-entropy), forward and forward + backward; bf16 tcgen05 GEMM vs cuBLAS at the head's shapes
