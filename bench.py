@@ -462,6 +462,8 @@ def main():
                     "achieved": ach, "peak": peak, "unit": "TFLOP/s", "frac": ach / peak,
                     "peak_note": f"2 x {pk['src']} sustained bf16 cuBLAS TFLOP/s (MEASURED_PEAKS.json has no FP8 figure; FP8 dense = 2 x bf16 on this part)",
                     "frac_of_nominal_fp8_4500": ach / FP8_NOMINAL_TFLOPS, "frac_of_measured_bf16": ach / pk["bf16_sustained"],
+                    "power_cap_note": "the board is at its 1000 W cap: the twelve GEMMs of a layer back to back, alone, sustain 2288 TF (mxfp8) / 2554 TF "
+                                      "(per-tensor) at Llama-3.1-8B shapes (profiles/r02/k_micro_sustained_gemms.jsonl) - the in-step rate is at that ceiling",
                     "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"], "share_of_step": d["ms"] / tot,
                     **_traffic(traffic, gname)}
         qn = max((n for n in by if by[n]["unit"] == "byte"), key=lambda n: by[n]["ms"], default=None)
