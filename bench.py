@@ -472,7 +472,13 @@ def main():
             ach = d["work"] / (d["ms"] * 1e-3) / 1e9
             roof_q = {"bound": "hbm", "kernel": qn.replace("llmfp8_", ""), "achieved": ach, "peak": pk["hbm"], "unit": "GB/s", "frac": ach / pk["hbm"],
                       "peak_note": f"{pk['src']} copy bandwidth", "launches": d["launches"], "avg_launch_ms": d["ms"] / d["launches"],
-                      "share_of_step": d["ms"] / tot, **_traffic(traffic, qn)}
+                      "share_of_step": d["ms"] / tot, **_traffic(traffic, qn),
+                      # every memory-bound kernel of the step (algorithmic bytes / measured launch time): the largest one by time alone hides the mix —
+                      # since round 2 the big activation tensors go through the fused SwiGLU / dSwiGLU + quantiser kernels, and what is left under
+                      # `mx_quantize` is the weights (0.8 of HBM) and the [M, H]-sized tensors (0.6)
+                      "by_kernel": {n.replace("llmfp8_", ""): {"GBps": round(v["work"] / (v["ms"] * 1e-3) / 1e9, 1), "frac": round(v["work"] / (v["ms"] * 1e-3) / 1e9 / pk["hbm"], 3),
+                                                               "launches": v["launches"], "share_of_step": round(v["ms"] / tot, 4)}
+                                    for n, v in sorted(by.items(), key=lambda kv: -kv[1]["ms"]) if v["unit"] == "byte" and v["ms"] > 0}}
 
     if arena is not None:
         arena.check()                      # a rank meeting that timed out invalidates the run: raise instead of printing a number
