@@ -150,6 +150,14 @@ int llmfp8_ce_reduce(const void* partials, int n_partials, int M, const float* l
 int llmfp8_lm_head_dlogits(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, int64_t ignore_index,
                            const float* lse, const float* gscale, void* dlogits, int64_t ldd, void* stream);
 
+/* Fused AdamW + MXFP8 requantise: one pass over a GEMM weight [rows, cols] (bf16; rows, cols % 32 == 0) that applies
+ * torch.optim.AdamW's update (decoupled weight decay; the reference's optimizer, train_fp8.py:200-204) with bf16 state exp_avg / exp_avg_sq — all
+ * three updated in place, fp32 arithmetic — and emits the MXFP8 copies of the UPDATED weight (q_row / q_col + swizzled E8M0 scales, layouts of
+ * llmfp8_mx_quantize; either may be NULL), bit-identical to llmfp8_mx_quantize of it: the next forward finds its weight casts done.
+ * bias_correction{1,2} = 1 - beta{1,2}^step, computed by the host. */
+int llmfp8_adamw_mx_step(void* w, const void* grad, void* exp_avg, void* exp_avg_sq, int64_t rows, int64_t cols, float lr, float beta1, float beta2, float eps,
+                         float weight_decay, float bias_correction1, float bias_correction2, void* q_row, void* sf_row, void* q_col, void* sf_col, void* stream);
+
 /* Tuning / tests only: force the GEMM tile width (128 | 192 | 256; 0 = automatic).  The three knobs below are process-wide, so they
  * are INERT (non-zero values are ignored, llmfp8_last_error says so) unless the process was started with LLMFP8_ALLOW_TUNING=1 — the test
  * suite and tools/ set it, a training process does not; values are atomics (a racing launch sees the old or the new value). */

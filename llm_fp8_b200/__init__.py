@@ -9,7 +9,8 @@ from .fp8 import (flush_all, fp8_autocast, get_fp8_recipe, is_fp8_available, is_
 from .modules import (LayerNormLinear, LayerNormMLP, Linear, MultiheadAttention, RotaryPositionEmbedding, TransformerLayer,
                       apply_rotary_pos_emb)
 from .lm_head import LMHeadLoss, bf16_gemm, lm_head_cross_entropy
+from .optim import FusedAdamW
 from .recipe import DelayedScaling, Format, MXFP8BlockScaling
 
 __all__ = ["Linear", "LayerNormLinear", "LayerNormMLP", "MultiheadAttention", "RotaryPositionEmbedding", "TransformerLayer",
-           "fp8_autocast", "is_fp8_available", "is_mxfp8_available", "DelayedScaling", "MXFP8BlockScaling", "Format", "ops", "LMHeadLoss", "lm_head_cross_entropy", "bf16_gemm"]
+           "fp8_autocast", "is_fp8_available", "is_mxfp8_available", "DelayedScaling", "MXFP8BlockScaling", "Format", "ops", "LMHeadLoss", "lm_head_cross_entropy", "bf16_gemm", "FusedAdamW"]

@@ -43,6 +43,7 @@ _PROTOTYPES = {
     "llmfp8_rmsnorm_rsigma": [vp, vp, i64, i64, f32, vp],
     "llmfp8_mx_scale_bytes": [i64, i64],
     "llmfp8_bf16_gemm": [vp, i64, i32, vp, i64, i32, vp, i64, i32, i32, i32, i32, vp, i32, i32, vp],
+    "llmfp8_adamw_mx_step": [vp, vp, vp, vp, i64, i64, f32, f32, f32, f32, f32, f32, f32, vp, vp, vp, vp, vp],
     "llmfp8_lm_head_partials": [i32],
     "llmfp8_lm_head_ce_stats": [vp, i64, vp, i64, i32, i32, i32, vp, vp, vp, vp],
     "llmfp8_ce_reduce_ws_floats": [i32],
@@ -137,6 +138,9 @@ def _work(name: str, a):
     if name == "llmfp8_mx_dswiglu_quantize":      # read da + gate | up (6 B per [M, I] element), write the copies + scales of [M, 2I]
         mi = float(a[2]) * a[3]
         return "byte", 6.0 * mi + 2.0 * (mi + mi / 32) * ((a[4] is not None) + (a[6] is not None))
+    if name == "llmfp8_adamw_mx_step":        # read w, g, m, v; write w, m, v; write the copies + scales
+        rc = float(a[4]) * a[5]
+        return "byte", 14.0 * rc + (rc + rc / 32) * ((a[13] is not None) + (a[15] is not None))
     if name == "llmfp8_bf16_gemm":
         return "flop", 2.0 * a[9] * a[10] * a[11]
     if name in ("llmfp8_lm_head_ce_stats", "llmfp8_lm_head_dlogits"):

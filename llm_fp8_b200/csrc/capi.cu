@@ -135,6 +135,7 @@ int nvls_timeouts_async(unsigned int*, cudaStream_t);
 int nvls_reset();
 int launch_bf16_gemm(const void*, int64_t, int, const void*, int64_t, int, void*, int64_t, int, int, int, int, const void*, int, int, int, const int64_t*,
                      const float*, const float*, void*, float*, int64_t, cudaStream_t);
+int launch_adamw_mx(void*, const void*, void*, void*, int64_t, int64_t, float, float, float, float, float, float, float, void*, void*, void*, void*, cudaStream_t);
 int launch_ce_reduce(const void*, int, int, const float*, const int64_t*, int64_t, float*, float*, float*, cudaStream_t);
 int ce_reduce_ws_floats(int);
 void gemm_force_bn(int);
@@ -235,6 +236,11 @@ int llmfp8_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_
                      const void* bias, int accumulate, int max_ctas, void* stream) {
     return launch_bf16_gemm(a, lda, a_mn, b, ldb, b_mn, d, ldd, out_fp32, M, N, K, bias, accumulate, max_ctas, 0, nullptr, nullptr, nullptr, nullptr, nullptr, 0,
                             S(stream));
+}
+int llmfp8_adamw_mx_step(void* w, const void* grad, void* exp_avg, void* exp_avg_sq, int64_t rows, int64_t cols, float lr, float beta1, float beta2, float eps,
+                         float weight_decay, float bias_correction1, float bias_correction2, void* q_row, void* sf_row, void* q_col, void* sf_col, void* stream) {
+    return launch_adamw_mx(w, grad, exp_avg, exp_avg_sq, rows, cols, lr, beta1, beta2, eps, weight_decay, bias_correction1, bias_correction2, q_row, sf_row,
+                           q_col, sf_col, S(stream));
 }
 int llmfp8_lm_head_partials(int V) { return 2 * ((V + 255) / 256); }
 int llmfp8_lm_head_ce_stats(const void* x, int64_t ldx, const void* w, int64_t ldw, int M, int V, int H, const int64_t* labels, void* partials,

@@ -94,18 +94,22 @@ def _weight_pt(wcache, first, key, weight, ff, pf: ScalePool, slot) -> "ops.QTen
 
 def _weight_mx(wcache, first, key, weight, need_col: bool) -> "ops.MXTensor":
     """MXFP8 copies (rowwise for fprop, colwise for dgrad) of a weight under the same `is_first_microbatch` contract."""
-    if wcache is not None and first is False:
+    if wcache is not None:
         hit = wcache.get(key)
         if hit is not None and (hit.col is not None or not need_col):
-            return hit
+            if first is False:
+                return hit
+            # copies deposited by optim.FusedAdamW in the optimizer's own pass over this weight: valid for every forward until the weight
+            # changes again (same storage, same version counter — any in-place torch update since would have bumped it)
+            if hit.src is not None and hit.src == (weight.data_ptr(), weight._version):
+                return hit
     wq = ops.mx_quantize(weight, True, need_col)
     if wcache is not None and first is not None:
         wcache[key] = wq
     return wq
 
 
-# Experimental, off unless LLMFP8_WGRAD_STREAM=1 (written without a GPU at hand; tests/test_gpu_modules.py has the gated check):
-# dgrad and wgrad of one linear are independent.  With the wgrad GEMM issued on a side stream its CTAs fill the SMs that the dgrad
+# LLMFP8_WGRAD_STREAM (default 1): dgrad and wgrad of one linear are independent.  With the wgrad GEMM issued on a side stream its CTAs fill the SMs that the dgrad
 # GEMM's last, partial wave leaves idle (an [M, 4096] output at 8B shapes is 5.2 waves of 256 x 256 tiles: 14 % of that launch) and
 # run under the RMSNorm backward / dSwiGLU that follow on the main stream.  The main stream rejoins before backward returns, so
 # autograd (and the gradient all-reduce hooks) see the weight gradient in stream order as before.

@@ -78,6 +78,7 @@ class MXTensor:
     sf_row: Optional[torch.Tensor] = None   # uint8 swizzled, scale matrix (r, c/32)
     col: Optional[torch.Tensor] = None      # uint8 [R, C]
     sf_col: Optional[torch.Tensor] = None   # uint8 swizzled, scale matrix (c, r/32)
+    src: Optional[tuple] = None             # (data_ptr, version) of the bf16 tensor these copies were made from, when its producer vouches for it
 
 
 def mx_scale_bytes(rows: int, k: int) -> int:
