@@ -20,10 +20,12 @@ def _ref_adamw(w, g, m, v, step, lr, b1, b2, eps, wd):
 
 
 def _close_bf16(got, want, what):
-    """equal up to one bf16 ulp on isolated elements (fma contraction / op order), never more"""
+    """equal up to one bf16 ulp on isolated elements (fma contraction / op order), never more; where the two terms of an update cancel
+    (b1 m = -(1 - b1) g) the fused multiply-add leaves a residue of fp32 rounding size where separate roundings leave 0: absolute floor"""
     d = (got.float() - want.float()).abs()
-    ulp = want.float().abs().clamp_min(1e-30) * 2 ** -7
-    assert (d <= ulp).all(), f"{what}: max diff {d.max().item():.3e}"
+    ulp = want.float().abs() * 2 ** -7 + want.float().abs().max() * 2 ** -20
+    bad = (d > ulp).nonzero()
+    assert bad.numel() == 0, f"{what}: {bad.shape[0]} elements off by more than a bf16 ulp, first at {bad[0].tolist()}: got {got[tuple(bad[0])].item()!r} want {want[tuple(bad[0])].item()!r}"
     assert (d > 0).float().mean().item() < 0.02, f"{what}: {100 * (d > 0).float().mean().item():.2f} % of elements differ"
 
 
@@ -74,13 +76,20 @@ def test_fused_adamw_end_to_end_and_forward_skips_its_weight_casts():
     g = torch.Generator().manual_seed(1)
     for step in range(3):
         x = torch.randn(2, 128, model.H, generator=g).bfloat16().cuda()
-        for net, o in ((model, opt), (twin, ref)):
-            o.zero_grad()
-            net(x).float().pow(2).mean().backward()
-            o.step()
+        opt.zero_grad()
+        model(x).float().pow(2).mean().backward()
+        # the SAME gradients for both optimizers: Adam normalises them, so two models one bf16 ulp apart drift chaotically (measured: 0.7 % of the
+        # elements move in opposite directions by the third step) — what is under test is the update rule, not that feedback
+        for p, q in zip(model.parameters(), twin.parameters()):
+            q.grad = p.grad.detach().clone()
+        opt.step()
+        ref.step()
     for (n, p), (_, q) in zip(model.named_parameters(), twin.named_parameters()):
-        d = (p.float() - q.float()).abs().max().item()
-        assert d <= 2e-2 * q.float().abs().max().item() + 1e-6, f"{n}: {d}"      # torch's bf16 AdamW rounds after every op; ours once
+        d = (p.float() - q.float()).abs()
+        spacing = q.float().abs().max().item() * 2 ** -7                # one bf16 step at the largest weight
+        # torch's bf16 AdamW rounds after every elementwise op, ours once per tensor: a step or two apart on some elements, equal on average
+        assert d.max().item() <= 4 * spacing + 1e-8, f"{n}: max diff {d.max().item():.3e} vs bf16 spacing {spacing:.3e}"
+        assert d.mean().item() <= 0.25 * spacing + 1e-9, f"{n}: mean diff {d.mean().item():.3e} vs bf16 spacing {spacing:.3e}"
     # the forward after a step: no weight casts (4 GEMM weights per layer), identical bytes
     x = torch.randn(2, 128, model.H, generator=g).bfloat16().cuda()
     n0 = lib.llmfp8_launch_count()

@@ -18,7 +18,7 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 import llm_fp8_b200 as te  # noqa: E402
-from llm_fp8_b200 import ops  # noqa: E402
+from llm_fp8_b200 import _lib, ops  # noqa: E402
 
 SHAPES = {  # H, I, qkv_out, M
     "llama1b": (2048, 8192, 3072, 8192),
@@ -257,6 +257,25 @@ def run_one(args, emit, M, H, I, QKV, hbm, bf16_tf, src):
             ms = e0.elapsed_time(e1) / n
             emit({"kernel": f"sustained: the 12 GEMMs of a layer back to back, {'mxfp8' if want_mx else 'per-tensor'}, {n} rounds", "M": M, "ms": ms,
                   "TFLOPs": fl / ms / 1e9, "frac_2x_bf16_sustained_proxy": None, "frac_fp8_nominal": fl / ms / 1e9 / 4500.0})
+
+    if "optim" in args.only:
+        # fused AdamW + MXFP8 requantise of the fc1 weight [2I, H] against what it replaces: torch.optim.AdamW's step on that weight + the block
+        # quantiser's pass over the updated weight in the next forward
+        w = (torch.randn(2 * I, H, device=dev, generator=g) * 0.02).bfloat16().requires_grad_(True)
+        w.grad = (torch.randn(2 * I, H, device=dev, generator=g) * 1e-4).bfloat16()
+        mm, vv = torch.zeros_like(w), torch.zeros_like(w)
+        out = ops._mx_out(2 * I, H, True, True, w.device)
+        lib = _lib.load()
+        st = torch.cuda.current_stream().cuda_stream
+        n = 2 * I * H
+
+        def fused():
+            lib.llmfp8_adamw_mx_step(w.data_ptr(), w.grad.data_ptr(), mm.data_ptr(), vv.data_ptr(), 2 * I, H, 1e-4, 0.9, 0.95, 1e-8, 0.1, 0.1, 0.05,
+                                     out.row.data_ptr(), out.sf_row.data_ptr(), out.col.data_ptr(), out.sf_col.data_ptr(), st)
+        topt = torch.optim.AdamW([w], lr=1e-4, betas=(0.9, 0.95), weight_decay=0.1)
+        mem("O1 fused AdamW + MX requantise W1[2I,H] (one pass)", fused, int(16.0625 * n))
+        mem("O1 torch.optim.AdamW step W1[2I,H] (bf16 state; comparison point)", lambda: topt.step(), int(14 * n))
+        mem("O1 torch.optim.AdamW step + mx_quantize row+col (what the fused pass replaces)", lambda: (topt.step(), ops.mx_quantize(w.detach(), True, True)), int(18.0625 * n))
 
     if "lmhead" in args.only:
         # lm_head + cross-entropy at the model's head shape, next to the reference's sequence in torch
