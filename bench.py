@@ -49,6 +49,10 @@ def parse():
     ap.add_argument("--graph", type=int, default=int(os.environ.get("LLMFP8_BENCH_GRAPH", "0")),
                     help="1: capture the whole forward+backward step in one CUDA graph and replay it (N=1 only; same kernels, no host launch cost)")
     ap.add_argument("--no-fuse-residual", action="store_true", help="run the plain h = h + f(h) layer form (separate elementwise passes)")
+    ap.add_argument("--optimizer", default="none", choices=["none", "fused", "torch"],
+                    help="NOT the headline (SURVEY.md section 8 leaves the optimizer outside the path): also step AdamW inside the timed region — "
+                         "'fused' = llm_fp8_b200.FusedAdamW (its pass over the weights emits their MXFP8 copies, the forward skips its casts), "
+                         "'torch' = torch.optim.AdamW")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-roofline", action="store_true")
     ap.add_argument("--cpu-sample-tokens", type=int, default=1536)
@@ -64,7 +68,8 @@ def peaks():
 
 
 def workload_name(a, layers):
-    return f"{a.model} linear path x{layers} layers, scenario={a.scenario}, batch {a.batch} x seq {a.seq} per GPU, fwd+bwd"
+    opt = "" if getattr(a, "optimizer", "none") == "none" else f" + AdamW step ({a.optimizer})"
+    return f"{a.model} linear path x{layers} layers, scenario={a.scenario}, batch {a.batch} x seq {a.seq} per GPU, fwd+bwd{opt}"
 
 
 # ------------------------------------------------------------------------------------------------ clocks
@@ -285,7 +290,15 @@ def main():
             reducer.finish()
         return loss
 
+    optimizer = None
+    if a.optimizer == "fused":
+        optimizer = te.FusedAdamW(model, lr=1e-5, betas=(0.9, 0.95), weight_decay=0.01)
+    elif a.optimizer == "torch":
+        optimizer = torch.optim.AdamW(model.parameters(), lr=1e-5, betas=(0.9, 0.95), weight_decay=0.01)
+
     def zero():
+        if optimizer is not None:
+            optimizer.step()                 # inside the timed region, after the gradient reduction
         for p in model.parameters():
             p.grad = None
 
