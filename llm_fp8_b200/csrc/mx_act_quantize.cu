@@ -11,6 +11,7 @@
 // activation in place (bf16, into the gate / up buffers), run the 1x32 and 32x1 block passes of mx_quantize.cu over those buffers, stage
 // the e4m3 tiles in shared memory and TMA-store them; scale tiles (512 B, pre-swizzled for tcgen05.cp) leave with vector stores.
 // Default path of functional.MXLayerNormMLPFn (LLMFP8_MX_FUSED_ACT=0 restores the two-kernel sequence).
+#include <cstdlib>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
@@ -416,6 +417,14 @@ __global__ void __launch_bounds__(AB_THREADS, 1) mx_dswiglu_quantize_kernel(cons
 
 // ------------------------------------------------------------------------------------------------ host side
 int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t stream);
+// mx_act_quantize2.cu: the two-CTAs-per-SM form of both kernels (same bytes).  A/B switch for one measurement: LLMFP8_ACT_V1=1 keeps this file's kernels.
+int launch_mx_swiglu_quantize2(const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col, cudaStream_t stream);
+int launch_mx_dswiglu_quantize2(const void* da, const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col,
+                                float* dbias_ws, cudaStream_t stream);
+static bool act_v1() {
+    static const bool v1 = [] { const char* e = getenv("LLMFP8_ACT_V1"); return e && e[0] == '1'; }();
+    return v1;
+}
 
 static int act_common_checks(const char* who, const void* fc1_out, int64_t M, int64_t I, const void* q_row, const void* sf_row, const void* q_col,
                              const void* sf_col, int64_t out_cols) {
@@ -435,6 +444,7 @@ static int act_common_checks(const char* who, const void* fc1_out, int64_t M, in
 int launch_mx_swiglu_quantize(const void* fc1_out, int64_t M, int64_t I, void* q_row, void* sf_row, void* q_col, void* sf_col, cudaStream_t stream) {
     if (int rc = act_common_checks("mx_swiglu_quantize", fc1_out, M, I, q_row, sf_row, q_col, sf_col, I)) return rc;
     if (M == 0 || I == 0) return 0;
+    if (!act_v1()) return launch_mx_swiglu_quantize2(fc1_out, M, I, q_row, sf_row, q_col, sf_col, stream);
     const int do_row = q_row != nullptr, do_col = q_col != nullptr;
     const uint16_t* base = static_cast<const uint16_t*>(fc1_out);
     CUtensorMap m_g, m_u, m_row, m_col;
@@ -471,6 +481,11 @@ int launch_mx_dswiglu_quantize(const void* da, const void* fc1_out, int64_t M, i
     if (dbias_ws) {
         cudaError_t e = cudaMemsetAsync(dbias_ws, 0, sizeof(float) * 2 * I, stream);
         if (e != cudaSuccess) { set_error("mx_dswiglu_quantize: memset: %s", cudaGetErrorString(e)); return (int)e; }
+    }
+    if (!act_v1()) {
+        if (int rc = launch_mx_dswiglu_quantize2(da, fc1_out, M, I, q_row, sf_row, q_col, sf_col, dbias_ws, stream)) return rc;
+        if (dbias_ws) return launch_f32_to_bf16(dbias_ws, dbias_bf16, 2 * I, stream);
+        return 0;
     }
     const uint16_t* base = static_cast<const uint16_t*>(fc1_out);
     CUtensorMap m_da, m_g, m_u, m_row, m_col;

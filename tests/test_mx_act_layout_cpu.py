@@ -50,25 +50,60 @@ def _quantise_tile(a_tile):
     return q_row.view(torch.uint8), e_row, q_col.view(torch.uint8), e_col
 
 
-def model_fwd(fc1, M, I):
-    """mx_swiglu_quantize_kernel: tiles over [M, I]; gate view = fc1[:, :I], up view = fc1[:, I:] (two tensor maps, each bounded to I)."""
+def _tile_rows(x, r0, c0, rows):
+    """TMA load of a rows x 128 box at (r0, c0): zero fill outside the tensor."""
+    t = torch.zeros(rows, AT, dtype=x.dtype)
+    r1, c1 = min(r0 + rows, x.shape[0]), min(c0 + AT, x.shape[1])
+    if r1 > r0 and c1 > c0:
+        t[: r1 - r0, : c1 - c0] = x[r0:r1, c0:c1]
+    return t
+
+
+def _store_rows(dst, tile, r0, c0):
+    r1, c1 = min(r0 + tile.shape[0], dst.shape[0]), min(c0 + AT, dst.shape[1])
+    if r1 > r0 and c1 > c0:
+        dst[r0:r1, c0:c1] = tile[: r1 - r0, : c1 - c0]
+
+
+def model_fwd(fc1, M, I, grid=3):
+    """mx_swiglu_quantize2_kernel (mx_act_quantize2.cu): 64-row tiles over [M, I], row-tile count rounded up to even so every 128-row scale
+    tile is written whole; gate view = fc1[:, :I], up view = fc1[:, I:] (two tensor maps, each bounded to I); each CTA owns a contiguous
+    range of tiles; a tile fills 8 consecutive bytes per (row & 31) of its rowwise scale tile (staging sf_row[32][8]) and 2 per column of
+    its colwise one (sf_col[128][2])."""
+    R = 64
     gate, up = fc1[:, :I], fc1[:, I:]
-    tiles_c, tiles_r = (I + AT - 1) // AT, (M + AT - 1) // AT
+    tiles_c, tiles_r128 = (I + AT - 1) // AT, (M + AT - 1) // AT
+    tiles_r = 2 * tiles_r128
+    ntiles = tiles_c * tiles_r
     q_row = torch.zeros(M, I, dtype=torch.uint8)
     q_col = torch.zeros(M, I, dtype=torch.uint8)
-    sf_row = torch.zeros(tiles_r * tiles_c * 512, dtype=torch.uint8)
-    sf_col = torch.zeros(tiles_c * tiles_r * 512, dtype=torch.uint8)
-    for t in range(tiles_r * tiles_c):
-        tr, tc = t // tiles_c, t % tiles_c
-        g, u = _tile(gate, tr * AT, tc * AT), _tile(up, tr * AT, tc * AT)
-        a = fo.swiglu_ref(torch.cat((g, u), 1)).bfloat16()
-        qr, er, qc, ec = _quantise_tile(a)
-        _store(q_row, qr, tr * AT, tc * AT)
-        _store(q_col, qc, tr * AT, tc * AT)
-        off = (tr * tiles_c + tc) * 512
-        sf_row[off:off + 512] = _sf_tile_row(er)
-        off = (tc * tiles_r + tr) * 512
-        sf_col[off:off + 512] = _sf_tile_col(ec)
+    sf_row = torch.full((tiles_r128 * tiles_c * 512,), 0xAA, dtype=torch.uint8)           # poison: every byte must be written
+    sf_col = torch.full((tiles_c * tiles_r128 * 512,), 0xAA, dtype=torch.uint8)
+    seen = 0
+    for cta in range(grid):
+        for t in range(ntiles * cta // grid, ntiles * (cta + 1) // grid):
+            seen += 1
+            tr, tc = t // tiles_c, t % tiles_c
+            row0, col0 = tr * R, tc * AT
+            g, u = _tile_rows(gate, row0, col0, R), _tile_rows(up, row0, col0, R)
+            a = fo.swiglu_ref(torch.cat((g, u), 1)).bfloat16()
+            q_r, e_r = fo.mx_quantize_rowwise(a)                      # e_r [64, 4]
+            q_c, e_c = fo.mx_quantize_colwise(a)                      # e_c [128, 2]
+            _store_rows(q_row, q_r.view(torch.uint8), row0, col0)
+            _store_rows(q_col, q_c.view(torch.uint8), row0, col0)
+            upper = 1 if (row0 & 64) else 0
+            stage = torch.zeros(32, 8, dtype=torch.uint8)             # s.sf_row[r & 31][(r >> 5) * 4 + blk]
+            for r in range(R):
+                for blk in range(4):
+                    stage[r & 31, (r >> 5) * 4 + blk] = e_r[r, blk]
+            base = ((row0 >> 7) * tiles_c + tc) * 512
+            for q in range(32):
+                sf_row[base + q * 16 + upper * 8: base + q * 16 + upper * 8 + 8] = stage[q]
+            base = (tc * tiles_r128 + (row0 >> 7)) * 512
+            for c in range(AT):                                       # s.sf_col[c][rb]
+                for rb in range(2):
+                    sf_col[base + (c & 31) * 16 + (c >> 5) * 4 + upper * 2 + rb] = e_c[c, rb]
+    assert seen == ntiles
     return q_row, sf_row, q_col, sf_col
 
 
@@ -92,14 +127,15 @@ def _dswiglu(da, g, u):
 
 
 def model_bwd(da, fc1, M, I, grid=3):
-    """mx_dswiglu_quantize_kernel (ring version): 64-row tiles over [M, I], row-tile count rounded up to even so every 128-row scale tile is
-    written whole; each CTA owns a contiguous range of tiles in COLUMN-major order; output [M, 2I] = (dgate | dup) with the dup half at
-    tile column tiles_c + tc; a 64-row tile fills 8 consecutive bytes per (row & 31) of its rowwise scale tile and 2 per column of its
-    colwise one (the staging arrays sf_row[2][32][8] / sf_col[2][128][2]); bias sums flushed when the tile column changes."""
-    R = 64
+    """mx_dswiglu_quantize2_kernel (mx_act_quantize2.cu): 32-row tiles over [M, I], row-tile count rounded up to a multiple of four so every
+    128-row scale tile is written whole; each CTA owns a contiguous range of tiles in COLUMN-major order; output [M, 2I] = (dgate | dup)
+    with the dup half at tile column tiles_c + tc; a 32-row tile fills 4 consecutive bytes per (row & 31) of its rowwise scale tile and
+    one per column of its colwise one (the staging arrays sf_row[2][32][4] / sf_col[2][128]); bias sums flushed when the tile column
+    changes."""
+    R = 32
     gate, up = fc1[:, :I], fc1[:, I:]
     tiles_c, tiles_r128 = I // AT, (M + AT - 1) // AT
-    tiles_r = 2 * tiles_r128
+    tiles_r = 4 * tiles_r128
     ntiles = tiles_c * tiles_r
     q_row = torch.zeros(M, 2 * I, dtype=torch.uint8)
     q_col = torch.zeros(M, 2 * I, dtype=torch.uint8)
@@ -107,13 +143,6 @@ def model_bwd(da, fc1, M, I, grid=3):
     sf_col = torch.full((2 * tiles_c * tiles_r128 * 512,), 0xAA, dtype=torch.uint8)
     dbias = torch.zeros(2 * I, dtype=torch.float64)
     flushes = 0
-
-    def tile64(x, r0, c0):
-        t = torch.zeros(R, AT, dtype=x.dtype)
-        r1 = min(r0 + R, x.shape[0])
-        if r1 > r0:
-            t[: r1 - r0] = x[r0:r1, c0:c0 + AT]
-        return t
 
     for cta in range(grid):
         t0, t1 = ntiles * cta // grid, ntiles * (cta + 1) // grid
@@ -127,30 +156,28 @@ def model_bwd(da, fc1, M, I, grid=3):
                     dbias[I + cur_tc * AT:I + cur_tc * AT + AT] += acc[AT:]
                     flushes += 1
                 acc, cur_tc = torch.zeros(2 * AT, dtype=torch.float64), tc
-            dg, du = _dswiglu(tile64(da, row0, col0), tile64(gate, row0, col0), tile64(up, row0, col0))
+            dg, du = _dswiglu(_tile_rows(da, row0, col0, R), _tile_rows(gate, row0, col0, R), _tile_rows(up, row0, col0, R))
             acc[:AT] += dg.double().sum(0)
             acc[AT:] += du.double().sum(0)
-            V = torch.cat((dg, du), 0).bfloat16()                       # the virtual 128 x 128 tile: rows 0..63 dgate, 64..127 dup
-            qr, er, qc, ec = _quantise_tile(V)
-            upper = 1 if (row0 & 64) else 0
+            V = torch.cat((dg, du), 0).bfloat16()                       # the virtual 64 x 128 tile: rows 0..31 dgate, 32..63 dup
+            q_r, e_r = fo.mx_quantize_rowwise(V)                        # e_r [64, 4]
+            q_c, e_c = fo.mx_quantize_colwise(V)                        # e_c [128, 2]
+            qr, qc = q_r.view(torch.uint8), q_c.view(torch.uint8)
+            quarter = (row0 >> 5) & 3
             for h in range(2):
                 r1 = min(row0 + R, M)
                 if r1 > row0:
                     q_row[row0:r1, h * I + col0:h * I + col0 + AT] = qr[h * R:h * R + (r1 - row0)]
                     q_col[row0:r1, h * I + col0:h * I + col0 + AT] = qc[h * R:h * R + (r1 - row0)]
-                # rowwise scale staging: s.sf_row[r >> 6][r & 31][((r >> 5) & 1) * 4 + blk], written out as 8 bytes at q * 16 + upper * 8
-                stage = torch.zeros(32, 8, dtype=torch.uint8)
+                # rowwise scale staging: s.sf_row[r >> 5][r & 31][blk], written out as 4 bytes at q * 16 + quarter * 4
+                base = ((row0 >> 7) * (2 * tiles_c) + h * tiles_c + tc) * 512
                 for r in range(h * R, h * R + R):
                     for blk in range(4):
-                        stage[r & 31, ((r >> 5) & 1) * 4 + blk] = er[r, blk]
-                base = ((row0 >> 7) * (2 * tiles_c) + h * tiles_c + tc) * 512
-                for q in range(32):
-                    sf_row[base + q * 16 + upper * 8: base + q * 16 + upper * 8 + 8] = stage[q]
-                # colwise: s.sf_col[rb >> 1][c][rb & 1], written as 2 bytes at (c & 31) * 16 + (c >> 5) * 4 + upper * 2
+                        sf_row[base + (r & 31) * 16 + quarter * 4 + blk] = e_r[r, blk]
+                # colwise: s.sf_col[rb][c], one byte at (c & 31) * 16 + (c >> 5) * 4 + quarter
                 base = ((h * tiles_c + tc) * tiles_r128 + (row0 >> 7)) * 512
                 for c in range(AT):
-                    for k in range(2):
-                        sf_col[base + (c & 31) * 16 + (c >> 5) * 4 + upper * 2 + k] = ec[c, 2 * h + k]
+                    sf_col[base + (c & 31) * 16 + (c >> 5) * 4 + quarter] = e_c[c, h]
         if cur_tc >= 0:
             dbias[cur_tc * AT:cur_tc * AT + AT] += acc[:AT]
             dbias[I + cur_tc * AT:I + cur_tc * AT + AT] += acc[AT:]
