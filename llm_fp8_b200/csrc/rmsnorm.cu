@@ -5,7 +5,9 @@
 // Replaces TE's rmsnorm_fwd(+fp8 cast)/rmsnorm_bwd reached from LayerNormLinear / LayerNormMLP
 // (te_llama.py:45-63).  The sum-of-squares reduction ORDER is the one oracle_c.c:orc_rms_rsigma fixes:
 // chunk c (8 elements) -> thread c % 128, in-thread fma chain, xor butterfly, ((w0+w1)+w2)+w3.
+#include <cstdlib>
 #include "common.cuh"
+#include "ptx.cuh"
 
 namespace llmfp8 {
 
@@ -253,6 +255,138 @@ __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(c
         }
 }
 
+// K5, TMA-staged (the default; LLMFP8_K5_V1=1 keeps the register-prefetch kernel above for one A/B): whole rows of x, dy (and dres) stream
+// into a ring of shared-memory stages with 1-D bulk copies (cp.async.bulk, mbarrier completion) and the 256 threads take their 16 B chunks
+// from the ring.  The kernel above keeps ONE row of loads in flight per CTA (32 KB per SM with two resident CTAs — half of what the HBM
+// latency-bandwidth product asks for, 0.59 of the measured peak); here every CTA has stages - 1 rows in flight.  Thread 0 is the
+// producer: the block barrier of the row reduction already proves that every thread holds its chunks of the current stage in registers,
+// so right after it the slot is refilled with the row `stages` iterations ahead — no second barrier, no producer warp.
+// Same arithmetic, same thread -> chunk mapping, same dgamma partial layout.
+template <int NIT, bool ADD>
+__global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_tma_kernel(const uint8_t* __restrict__ dy, const uint8_t* __restrict__ x,
+                                                                                   const uint4* __restrict__ gamma, const float* __restrict__ rsigma,
+                                                                                   const uint8_t* __restrict__ dres, uint4* __restrict__ dx,
+                                                                                   float* __restrict__ dgamma_part, int64_t M, int H, int stages) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* ring = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
+    const uint32_t row_bytes = static_cast<uint32_t>(H) * 2u;
+    const uint32_t stage_bytes = ((ADD ? 3u : 2u) * row_bytes + 127u) & ~127u;
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + stages * stage_bytes);
+    float* red = reinterpret_cast<float*>(full + stages);           // [2][RB_T / 32]
+    const int t = threadIdx.x;
+    auto load_row = [&](int64_t row, int stage) {                   // thread 0 only
+        uint8_t* dst = ring + stage * stage_bytes;
+        ptx::mbar_arrive_expect_tx(&full[stage], (ADD ? 3u : 2u) * row_bytes);
+        ptx::bulk_load_1d(dst, x + row * row_bytes, row_bytes, &full[stage]);
+        ptx::bulk_load_1d(dst + row_bytes, dy + row * row_bytes, row_bytes, &full[stage]);
+        if constexpr (ADD) ptx::bulk_load_1d(dst + 2 * row_bytes, dres + row * row_bytes, row_bytes, &full[stage]);
+    };
+    if (t == 0) {
+        for (int i = 0; i < stages; i++) ptx::mbar_init(&full[i], 1);
+        ptx::fence_barrier_init();
+    }
+    __syncthreads();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
+    if (t == 0) {
+        int64_t row = blockIdx.x;
+        for (int i = 0; i < stages && row < M; i++, row += gridDim.x) load_row(row, i);
+    }
+
+    const int nchunk = H / 8;
+    f32x2 dg[NIT][4], g2[NIT][4];
+#pragma unroll
+    for (int it = 0; it < NIT; it++) {
+        float gf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (it * RB_T + t < nchunk) unpack8(__ldg(gamma + it * RB_T + t), gf);
+#pragma unroll
+        for (int k = 0; k < 4; k++) {
+            dg[it][k] = pk2(0.f, 0.f);
+            g2[it][k] = pk2(gf[2 * k], gf[2 * k + 1]);
+        }
+    }
+    const float inv_h = 1.0f / static_cast<float>(H);
+    const int64_t ahead = static_cast<int64_t>(stages) * gridDim.x;
+    int stage = 0, phase = 0, par = 0;
+    int64_t row = blockIdx.x;
+    float nrs = row < M ? rsigma[row] : 0.f;
+    for (; row < M; row += gridDim.x, par ^= 1) {
+        const float rs = nrs;
+        if (row + gridDim.x < M) nrs = rsigma[row + gridDim.x];
+        const f32x2 rs2 = pk2(rs, rs);
+        ptx::mbar_wait(&full[stage], phase);
+        const uint4* sx = reinterpret_cast<const uint4*>(ring + stage * stage_bytes);
+        const uint4* sdy = reinterpret_cast<const uint4*>(ring + stage * stage_bytes + row_bytes);
+        const uint4* sres = reinterpret_cast<const uint4*>(ring + stage * stage_bytes + 2 * row_bytes);
+        f32x2 xh[NIT][4], tg[NIT][4];       // xhat = x * rs ; tg = dy * gamma
+        f32x2 fr[ADD ? NIT : 1][4];         // the residual-branch gradient, unpacked BEFORE the barrier that frees the stage
+        f32x2 dot2 = pk2(0.f, 0.f);
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RB_T + t < nchunk) {
+                float fx[8], fdy[8];
+                unpack8(sx[it * RB_T + t], fx);
+                unpack8(sdy[it * RB_T + t], fdy);
+                if constexpr (ADD) {
+                    float f[8];
+                    unpack8(sres[it * RB_T + t], f);
+#pragma unroll
+                    for (int k = 0; k < 4; k++) fr[it][k] = pk2(f[2 * k], f[2 * k + 1]);
+                }
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    const f32x2 dy2 = pk2(fdy[2 * k], fdy[2 * k + 1]);
+                    xh[it][k] = mul2(pk2(fx[2 * k], fx[2 * k + 1]), rs2);
+                    tg[it][k] = mul2(dy2, g2[it][k]);
+                    dot2 = fma2(tg[it][k], xh[it][k], dot2);
+                    dg[it][k] = fma2(dy2, xh[it][k], dg[it][k]);
+                }
+            }
+        float d0, d1;
+        upk2(dot2, d0, d1);
+        const float dot = warp_sum(d0 + d1);
+        if ((t & 31) == 0) red[par * (RB_T / 32) + (t >> 5)] = dot;
+        __syncthreads();                                             // also: every thread has its chunks of this stage in registers
+        if (t == 0 && row + ahead < M) load_row(row + ahead, stage);
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+        float tot = 0.f;
+#pragma unroll
+        for (int w = 0; w < RB_T / 32; w++) tot += red[par * (RB_T / 32) + w];
+        // dx = rs * tg - (rs * c) * xhat
+        const float nc = -(rs * (tot * inv_h));
+        const f32x2 nc2 = pk2(nc, nc);
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RB_T + t < nchunk) {
+                uint32_t o[4];
+#pragma unroll
+                for (int k = 0; k < 4; k++) {
+                    float lo, hi;
+                    upk2(fma2(xh[it][k], nc2, mul2(tg[it][k], rs2)), lo, hi);
+                    if constexpr (ADD) {
+                        float rlo, rhi;
+                        upk2(fr[it][k], rlo, rhi);
+                        lo += rlo;
+                        hi += rhi;
+                    }
+                    o[k] = pack_bf16x2(lo, hi);
+                }
+                dx[row * nchunk + it * RB_T + t] = make_uint4(o[0], o[1], o[2], o[3]);
+            }
+    }
+    float* out = dgamma_part + static_cast<int64_t>(blockIdx.x) * H;
+#pragma unroll
+    for (int it = 0; it < NIT; it++)
+        if (it * RB_T + t < nchunk) {
+            float v[8];
+#pragma unroll
+            for (int k = 0; k < 4; k++) upk2(dg[it][k], v[2 * k], v[2 * k + 1]);
+            float4* o4 = reinterpret_cast<float4*>(out + (it * RB_T + t) * 8);
+            o4[0] = make_float4(v[0], v[1], v[2], v[3]);
+            o4[1] = make_float4(v[4], v[5], v[6], v[7]);
+        }
+}
+
 // dgamma[c] = sum over the per-CTA partial rows.  CTA = 32 columns x 8 partial-row lanes: every warp reads 128 B rows, each thread
 // keeps four independent accumulators (the one-thread-per-column chain this replaces spent ~30 us on 444 dependent loads).
 constexpr int CR_COLS = 32, CR_LANES = 8;
@@ -299,6 +433,44 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
     if (M == 0) return 0;
     const int nit = static_cast<int>((H / 8 + RB_T - 1) / RB_T);
     int grid = 0;
+    static const bool k5_v1 = [] { const char* e = getenv("LLMFP8_K5_V1"); return e && e[0] == '1'; }();
+    if (!k5_v1) {
+        // ring: as many whole-row stages as fit in ~100 KB (two CTAs per SM) or ~200 KB (one CTA: H > 4096), at most 4
+        const int64_t stage_bytes = (((dres ? 3 : 2) * H * 2) + 127) / 128 * 128;
+        const int64_t budget = nit <= 2 ? 100 * 1024 : 200 * 1024;
+        int stages = static_cast<int>(budget / stage_bytes);
+        stages = stages > 4 ? 4 : stages;
+        LLMFP8_REQUIRE(stages >= 2, "rmsnorm_bwd: hidden size %lld leaves no room for a two-stage ring", (long long)H);
+        const int smem = static_cast<int>(stages * stage_bytes + stages * 8 + 2 * (RB_T / 32) * 4 + 128);
+#define RMSB_TMA(N, ADD)                                                                                                                       \
+    do {                                                                                                                                       \
+        auto kern = rmsnorm_bwd_tma_kernel<N, ADD>;                                                                                            \
+        cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);                                         \
+        if (e != cudaSuccess) { set_error("rmsnorm_bwd: smem attr: %s", cudaGetErrorString(e)); return (int)e; }                               \
+        int per_sm = 0;                                                                                                                        \
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, RB_T, smem) != cudaSuccess || per_sm < 1) per_sm = 1;           \
+        const int64_t cap = static_cast<int64_t>(sm_count()) * per_sm;                                                                         \
+        grid = static_cast<int>(M < cap ? M : cap);                                                                                            \
+        if (grid > rmsnorm_bwd_grid(M)) grid = rmsnorm_bwd_grid(M);                                                                            \
+        LLMFP8_LAUNCH(kern, grid, RB_T, smem, stream, (const uint8_t*)dy, (const uint8_t*)x, (const uint4*)gamma, rsigma, (const uint8_t*)dres, \
+                      (uint4*)dx, ws, M, (int)H, stages);                                                                                      \
+    } while (0)
+#define RMSB_TMA_CASE(N)                 \
+    case N:                              \
+        if (dres) RMSB_TMA(N, true);     \
+        else RMSB_TMA(N, false);         \
+        break;
+        switch (nit) {
+            RMSB_TMA_CASE(1) RMSB_TMA_CASE(2) RMSB_TMA_CASE(3) RMSB_TMA_CASE(4)
+            default: set_error("rmsnorm_bwd: hidden size too large"); return -1;
+        }
+#undef RMSB_TMA
+#undef RMSB_TMA_CASE
+        LLMFP8_LAUNCH_CHECK("rmsnorm_bwd");
+        LLMFP8_LAUNCH((colreduce_bf16_kernel), static_cast<unsigned>((H + CR_COLS - 1) / CR_COLS), CR_COLS * CR_LANES, 0, stream, ws, grid, (int)H, static_cast<uint16_t*>(dgamma_bf16));
+        LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
+        return 0;
+    }
 #define RMSB_LAUNCH(N, ADD)                                                                                                                    \
     do {                                                                                                                                       \
         grid = resident_grid(rmsnorm_bwd_kernel<N, ADD>, RB_T, M);                                                                             \

@@ -325,6 +325,27 @@ def test_rmsnorm_bwd_with_residual_gradient():
         assert (dx1.float() - two_step).abs().max().item() <= 2.0 ** -7 * two_step.abs().max().item()
 
 
+@pytest.mark.parametrize("M,H", [(1, 16), (2, 4096), (5, 8192), (700, 4096), (1200, 3072)])
+@pytest.mark.parametrize("with_dres", [False, True])
+def test_rmsnorm_bwd_ring_edges(M, H, with_dres):
+    """K5's shared-memory ring (rmsnorm.cu: rows streamed with cp.async.bulk, thread 0 refills a slot right after the row barrier): fewer
+    rows than ring slots, more rows than resident CTAs x slots (several wraps of the mbarrier phases), the smallest and the largest hidden
+    size, with and without the residual-branch gradient — against the fp32 autograd reference."""
+    ops = _ops()
+    x, dy, dres = gen((M, H), 14), gen((M, H), 15), gen((M, H), 16)
+    g = torch.Generator().manual_seed(19)
+    gamma = (1 + 0.1 * torch.randn(H, generator=g)).bfloat16()
+    rs = ops.rmsnorm_rsigma(dev(x), 1e-5)
+    dx, dgamma = ops.rmsnorm_bwd(dev(dy), dev(x), dev(gamma), rs, add=dev(dres) if with_dres else None)
+    xf = x.float().requires_grad_(True)
+    gf = gamma.float().requires_grad_(True)
+    y, _ = fo.rmsnorm_ref(xf, gf, 1e-5)
+    y.backward(dy.float())
+    want = xf.grad + (dres.float() if with_dres else 0)
+    assert torch.allclose(dx.float().cpu(), want, rtol=2e-2, atol=2e-2 * want.abs().max().item())
+    assert torch.allclose(dgamma.float().cpu(), gf.grad, rtol=2e-2, atol=2e-2 * gf.grad.abs().max().item())
+
+
 # ------------------------------------------------------------------------------------------------ activation + MX quantiser in one pass
 import os  # noqa: E402
 
