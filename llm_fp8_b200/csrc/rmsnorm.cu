@@ -90,11 +90,124 @@ __global__ void __launch_bounds__(RMS_T) rmsnorm_fwd_kernel(const uint4* __restr
     if (OUT_MODE == 0 && amax) block_amax_to_global(m, red_amax, amax);
 }
 
+// K1 / K1r through a shared-memory ring (the default; LLMFP8_QUANT_V1=1 keeps the kernel above): a CTA of 256 threads works on TWO
+// consecutive rows per step — threads 0..127 on the first, 128..255 on the second, each half with the row kernel's thread -> chunk
+// mapping and reduction order, so rsigma and the fp8 bytes are the same bit for bit — and the row pairs stream through a ring of
+// stages filled by 1-D bulk copies (cp.async.bulk; one copy per pair: the two rows are contiguous).  Thread 0 refills a slot right
+// after the block barrier of the reduction, which also proves that every thread has its chunks in registers.
+template <int FMT, int NIT, int OUT_MODE>
+__global__ void __launch_bounds__(2 * RMS_T) rmsnorm_fwd_ring_kernel(const uint8_t* __restrict__ x, const uint4* __restrict__ gamma, uint2* __restrict__ q,
+                                                                     float* __restrict__ rsigma, int64_t M, int H, float eps,
+                                                                     const float* __restrict__ scale_ptr, float* __restrict__ amax, int stages) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* ring = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
+    const uint32_t row_bytes = static_cast<uint32_t>(H) * 2u;
+    const uint32_t stage_bytes = (2u * row_bytes + 127u) & ~127u;
+    uint64_t* full = reinterpret_cast<uint64_t*>(ring + stages * stage_bytes);
+    __shared__ float red[2][2][4];
+    __shared__ float red_amax[8];
+    const int t = threadIdx.x, grp = t >> 7, tt = t & (RMS_T - 1);
+    const int64_t npairs = (M + 1) / 2;
+    auto load_pair = [&](int64_t p, int stage) {                    // thread 0 only
+        const uint32_t bytes = (2 * p + 1 < M ? 2u : 1u) * row_bytes;
+        ptx::mbar_arrive_expect_tx(&full[stage], bytes);
+        ptx::bulk_load_1d(ring + stage * stage_bytes, x + 2 * p * row_bytes, bytes, &full[stage]);
+    };
+    if (t == 0) {
+        for (int i = 0; i < stages; i++) ptx::mbar_init(&full[i], 1);
+        ptx::fence_barrier_init();
+    }
+    __syncthreads();
+    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
+    pdl_launch_dependents();
+    if (t == 0) {
+        int64_t p = blockIdx.x;
+        for (int i = 0; i < stages && p < npairs; i++, p += gridDim.x) load_pair(p, i);
+    }
+    const int nchunk = H / 8;
+    const float scale = (OUT_MODE == 0 && scale_ptr) ? __ldg(scale_ptr) : 1.0f;
+    uint4 g[NIT];
+    if (OUT_MODE == 0) {
+#pragma unroll
+        for (int it = 0; it < NIT; it++)
+            if (it * RMS_T + tt < nchunk) g[it] = __ldg(gamma + it * RMS_T + tt);
+    }
+    const int64_t ahead = static_cast<int64_t>(stages) * gridDim.x;
+    float m = 0.f;
+    int stage = 0, phase = 0, par = 0;
+    for (int64_t p = blockIdx.x; p < npairs; p += gridDim.x, par ^= 1) {
+        const int64_t row = 2 * p + grp;
+        const bool live = row < M;
+        ptx::mbar_wait(&full[stage], phase);
+        const uint4* src = reinterpret_cast<const uint4*>(ring + stage * stage_bytes + grp * row_bytes);
+        uint4 v[NIT];
+        float acc = 0.f;
+#pragma unroll
+        for (int it = 0; it < NIT; it++) {
+            if (it * RMS_T + tt < nchunk) {
+                v[it] = live ? src[it * RMS_T + tt] : make_uint4(0, 0, 0, 0);
+                float f[8];
+                unpack8(v[it], f);
+#pragma unroll
+                for (int j = 0; j < 8; j++) acc = __fmaf_rn(f[j], f[j], acc);
+            }
+        }
+        acc = warp_sum_pinned(acc);
+        if ((tt & 31) == 0) red[par][grp][tt >> 5] = acc;
+        __syncthreads();                                            // also: every thread has its chunks of this slot in registers
+        if (t == 0 && p + ahead < npairs) load_pair(p + ahead, stage);
+        if (++stage == stages) { stage = 0; phase ^= 1; }
+        const float total = __fadd_rn(__fadd_rn(__fadd_rn(red[par][grp][0], red[par][grp][1]), red[par][grp][2]), red[par][grp][3]);
+        const float mean = __fdiv_rn(total, static_cast<float>(H));
+        const float rs = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+        if (!live) continue;
+        if (tt == 0) rsigma[row] = rs;
+        if (OUT_MODE == 0) {
+            uint2* qr = q + row * nchunk;
+#pragma unroll
+            for (int it = 0; it < NIT; it++) {
+                if (it * RMS_T + tt < nchunk) {
+                    float f[8], gf[8];
+                    unpack8(v[it], f);
+                    unpack8(g[it], gf);
+#pragma unroll
+                    for (int j = 0; j < 8; j++) f[j] = __fmul_rn(__fmul_rn(f[j], rs), gf[j]);
+                    m = amax8(f, m);
+                    qr[it * RMS_T + tt] = quant8<FMT>(f, scale);
+                }
+            }
+        }
+    }
+    if (OUT_MODE == 0 && amax) block_amax_to_global(m, red_amax, amax);
+}
+
+static bool rms_v1() {
+    static const bool v1 = [] { const char* e = getenv("LLMFP8_QUANT_V1"); return e && e[0] == '1'; }();
+    return v1;
+}
+
 template <int FMT, int OUT_MODE>
 static int dispatch_rms_fwd(int nit, int grid, cudaStream_t s, const uint4* x, const uint4* g, uint2* q, float* rs, int64_t M, int H, float eps,
                             const float* scale, float* amax) {
+    // ring: row pairs, as many stages as fit in ~104 KB (two CTAs per SM), at most 8
+    const int64_t stage_bytes = (4 * static_cast<int64_t>(H) + 127) / 128 * 128;
+    int stages = static_cast<int>(104 * 1024 / stage_bytes);
+    stages = stages > 8 ? 8 : stages;
+    const int smem = static_cast<int>(stages * stage_bytes + stages * 8 + 128);
+    const bool ring = !rms_v1() && stages >= 2;
 #define RMS_CASE(N)                                                                                              \
     case N:                                                                                                      \
+        if (ring) {                                                                                              \
+            auto kern = rmsnorm_fwd_ring_kernel<FMT, N, OUT_MODE>;                                               \
+            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);       \
+            if (e != cudaSuccess) { set_error("rmsnorm: smem attr: %s", cudaGetErrorString(e)); return (int)e; } \
+            int per_sm = 0;                                                                                      \
+            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 2 * RMS_T, smem) != cudaSuccess || per_sm < 1) per_sm = 1; \
+            const int64_t cap = static_cast<int64_t>(sm_count()) * per_sm, npairs = (M + 1) / 2;                 \
+            grid = static_cast<int>(npairs < cap ? npairs : cap);                                                \
+            LLMFP8_LAUNCH(kern, grid, 2 * RMS_T, smem, s, reinterpret_cast<const uint8_t*>(x), g, q, rs, M, H, eps, scale, amax, stages); \
+            break;                                                                                               \
+        }                                                                                                        \
         grid = resident_grid(rmsnorm_fwd_kernel<FMT, N, OUT_MODE>, RMS_T, M);                                    \
         LLMFP8_LAUNCH((rmsnorm_fwd_kernel<FMT, N, OUT_MODE>), grid, RMS_T, 0, s, x, g, q, rs, M, H, eps, scale, amax);        \
         break;
@@ -435,11 +548,12 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
     int grid = 0;
     static const bool k5_v1 = [] { const char* e = getenv("LLMFP8_K5_V1"); return e && e[0] == '1'; }();
     if (!k5_v1) {
-        // ring: as many whole-row stages as fit in ~100 KB (two CTAs per SM) or ~200 KB (one CTA: H > 4096), at most 4
+        // ring: as many whole-row stages as fit in ~104 KB (two CTAs per SM) or ~208 KB (one CTA: H > 4096), at most 8.  Bytes in flight are
+        // what counts: with 4 stages the 2-row form (96 KB in flight per SM) measured 0.65 of the HBM peak, the 3-row form (144 KB) 0.82.
         const int64_t stage_bytes = (((dres ? 3 : 2) * H * 2) + 127) / 128 * 128;
-        const int64_t budget = nit <= 2 ? 100 * 1024 : 200 * 1024;
+        const int64_t budget = nit <= 2 ? 104 * 1024 : 208 * 1024;
         int stages = static_cast<int>(budget / stage_bytes);
-        stages = stages > 4 ? 4 : stages;
+        stages = stages > 8 ? 8 : stages;
         LLMFP8_REQUIRE(stages >= 2, "rmsnorm_bwd: hidden size %lld leaves no room for a two-stage ring", (long long)H);
         const int smem = static_cast<int>(stages * stage_bytes + stages * 8 + 2 * (RB_T / 32) * 4 + 128);
 #define RMSB_TMA(N, ADD)                                                                                                                       \
