@@ -4,64 +4,22 @@
 //   K4  amax_scale_update  amax history roll + scale / scale_inv update  (one launch for all fp8 tensors)
 // Replaces TE's cast/cast_transpose_dbias + amax_and_scale_update ops reached from te_llama.py:76-80.
 // Arithmetic is the oracle's (oracle/oracle_c.c orc_quantize_bf16 / orc_amax_scale_update), bit for bit.
-#include <cstdlib>
 #include "common.cuh"
 #include "ptx.cuh"
 #include "tensormap.cuh"
 
 namespace llmfp8 {
 
-// LLMFP8_QUANT_V1=1: the register-staged K2 / K2b kernels instead of the shared-memory rings (one A/B measurement)
-static bool quant_v1() {
-    static const bool v1 = [] { const char* e = getenv("LLMFP8_QUANT_V1"); return e && e[0] == '1'; }();
-    return v1;
-}
-
 // ------------------------------------------------------------------------------------------- K2
-// Each thread owns UNROLL units of 8 elements (one 16 B load, one 8 B store), a warp's units contiguous in memory so every request
-// covers whole 32 B sectors exactly once; all UNROLL loads are issued before the first use.
-template <int FMT, int UNROLL>
-__global__ void __launch_bounds__(256) cast_amax_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t nunits,
-                                                        const float* __restrict__ scale_ptr, float* __restrict__ amax) {
-    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_launch_dependents();
-    __shared__ float red[8];
-    const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
-    const f32x2 scale2 = pk2(scale, scale);
-    float m = 0.f;
-    const int64_t base = static_cast<int64_t>(blockIdx.x) * (256 * UNROLL) + threadIdx.x;
-    uint4 v[UNROLL];
-#pragma unroll
-    for (int u = 0; u < UNROLL; u++)
-        if (base + u * 256 < nunits) v[u] = ldg_stream(x + base + u * 256);
-#pragma unroll
-    for (int u = 0; u < UNROLL; u++) {
-        if (base + u * 256 < nunits) {
-            float f[8];
-            unpack8(v[u], f);
-            uint32_t h[4];
-#pragma unroll
-            for (int k = 0; k < 4; k++) {
-                m = fmaxf(m, fmaxf(fabsf(f[2 * k]), fabsf(f[2 * k + 1])));
-                float lo, hi;
-                upk2(mul2(pk2(f[2 * k], f[2 * k + 1]), scale2), lo, hi);
-                h[k] = cvt_fp8x2<FMT>(lo, hi);
-            }
-            q[base + u * 256] = make_uint2(h[0] | (h[1] << 16), h[2] | (h[3] << 16));
-        }
-    }
-    if (amax) block_amax_to_global(m, red, amax);
-}
-
 // K2 through a shared-memory ring: persistent CTAs (two per SM), each streaming 16 KB chunks of x with 1-D bulk copies (cp.async.bulk,
 // mbarrier completion) into a ring that keeps `stages - 1` chunks in flight per CTA; the 256 threads take one 16 B unit per 4 KB sub-block
 // from the ring, quantise and store 8 B.  Thread 0 is the producer: the block barrier after the ring reads proves the slot is free.
-// The register-staged kernel above has all of a CTA's loads in flight at once and then none while it computes and retires; at [M, H]
-// sizes (a 20 us kernel) its CTA churn leaves the SMs idle 22 % of the time (ncu: sm__cycles_active / elapsed).
+// (Round 1's register-staged form — 8 loads per thread in flight, then none while the CTA computes and retires — measured 0.832 of the
+// HBM peak on the fc1 weight against 0.858 here; at [M, H] sizes both take 20.5 us: a kernel that short is ramp and tail.)
 constexpr int CR_CHUNK = 16384;                 // bytes of bf16 input per stage
 constexpr int CR_UNITS = CR_CHUNK / 16 / 256;   // 16 B units per thread and stage
 template <int FMT>
-__global__ void __launch_bounds__(256, 2) cast_amax_ring_kernel(const uint8_t* __restrict__ x, uint2* __restrict__ q, int64_t nbytes,
+__global__ void __launch_bounds__(256, 2) cast_amax_kernel(const uint8_t* __restrict__ x, uint2* __restrict__ q, int64_t nbytes,
                                                                 const float* __restrict__ scale_ptr, float* __restrict__ amax, int stages) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* ring = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
@@ -129,8 +87,7 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
     LLMFP8_REQUIRE((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(q)) % 16 == 0, "cast_amax: pointers must be 16 B aligned");
     LLMFP8_REQUIRE(fmt == FMT_E4M3 || fmt == FMT_E5M2, "cast_amax: bad fp8 format %d", fmt);
     if (n == 0) return 0;
-    const int64_t nunits = n / 8;
-    if (!quant_v1()) {
+    {
         const int stages = 6;                                       // 96 KB per CTA, two CTAs per SM: 160 KB of loads in flight per SM
         const int smem = stages * CR_CHUNK + stages * 8 + 128;
         const int64_t nchunks = (n * 2 + CR_CHUNK - 1) / CR_CHUNK;
@@ -138,27 +95,17 @@ int launch_cast_amax(const void* x, void* q, int64_t n, int fmt, const float* sc
         const int grid = static_cast<int>(nchunks < cap ? nchunks : cap);
         cudaError_t e;
         if (fmt == FMT_E4M3) {
-            e = cudaFuncSetAttribute(cast_amax_ring_kernel<FMT_E4M3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(cast_amax_kernel<FMT_E4M3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { set_error("cast_amax: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-            LLMFP8_LAUNCH((cast_amax_ring_kernel<FMT_E4M3>), grid, 256, smem, stream, static_cast<const uint8_t*>(x), static_cast<uint2*>(q), n * 2, scale, amax, stages);
+            LLMFP8_LAUNCH((cast_amax_kernel<FMT_E4M3>), grid, 256, smem, stream, static_cast<const uint8_t*>(x), static_cast<uint2*>(q), n * 2, scale, amax, stages);
         } else {
-            e = cudaFuncSetAttribute(cast_amax_ring_kernel<FMT_E5M2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(cast_amax_kernel<FMT_E5M2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { set_error("cast_amax: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-            LLMFP8_LAUNCH((cast_amax_ring_kernel<FMT_E5M2>), grid, 256, smem, stream, static_cast<const uint8_t*>(x), static_cast<uint2*>(q), n * 2, scale, amax, stages);
+            LLMFP8_LAUNCH((cast_amax_kernel<FMT_E5M2>), grid, 256, smem, stream, static_cast<const uint8_t*>(x), static_cast<uint2*>(q), n * 2, scale, amax, stages);
         }
         LLMFP8_LAUNCH_CHECK("cast_amax");
         return 0;
     }
-    constexpr int UNROLL = 8;
-    const int64_t want = (nunits + 256 * UNROLL - 1) / (256 * UNROLL);
-    LLMFP8_REQUIRE(want < (int64_t(1) << 31), "cast_amax: tensor too large (%lld elements)", (long long)n);
-    const int grid = static_cast<int>(want);
-    if (fmt == FMT_E4M3)
-        LLMFP8_LAUNCH((cast_amax_kernel<FMT_E4M3, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
-    else
-        LLMFP8_LAUNCH((cast_amax_kernel<FMT_E5M2, UNROLL>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), nunits, scale, amax);
-    LLMFP8_LAUNCH_CHECK("cast_amax");
-    return 0;
 }
 
 // K2 on a column slice: x is [R, C] with row pitch ldx elements (a view into a wider matrix), q is dense [R, C].
@@ -225,68 +172,14 @@ int launch_cast_amax_2d(const void* x, int64_t ldx, void* q, int64_t R, int64_t 
 // A CTA walks `rows_per_cta` rows of its 256-column strip, keeping 8 fp32 column sums per thread, then folds the
 // 8 row lanes through shared memory and adds the strip's sums into the fp32 workspace with atomics.
 constexpr int BG_CV = 32, BG_RL = 8, BG_COLS = BG_CV * 8;
-template <int FMT>
-__global__ void __launch_bounds__(256) cast_amax_bgrad_kernel(const uint4* __restrict__ x, uint2* __restrict__ q, int64_t R, int64_t C,
-                                                              int64_t rows_per_cta, const float* __restrict__ scale_ptr,
-                                                              float* __restrict__ amax, float* __restrict__ colsum_ws) {
-    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_launch_dependents();
-    __shared__ float red[8];
-    __shared__ float part[BG_RL][BG_COLS + 8];
-    const float scale = scale_ptr ? __ldg(scale_ptr) : 1.0f;
-    const int cv = threadIdx.x % BG_CV, rl = threadIdx.x / BG_CV;
-    const int64_t col0 = static_cast<int64_t>(blockIdx.x) * BG_COLS + cv * 8;
-    const int64_t r_begin = static_cast<int64_t>(blockIdx.y) * rows_per_cta;
-    const int64_t r_end = r_begin + rows_per_cta < R ? r_begin + rows_per_cta : R;
-    const bool col_ok = col0 < C;
-    const int64_t rowvec = C / 8;
-    float m = 0.f;
-    float cs[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-    if (col_ok) {
-        constexpr int UN = 4;
-        for (int64_t r0 = r_begin + rl; r0 < r_end; r0 += BG_RL * UN) {
-            uint4 v[UN];
-#pragma unroll
-            for (int u = 0; u < UN; u++) {
-                const int64_t r = r0 + u * BG_RL;
-                if (r < r_end) v[u] = ldg_stream(x + r * rowvec + col0 / 8);
-            }
-#pragma unroll
-            for (int u = 0; u < UN; u++) {
-                const int64_t r = r0 + u * BG_RL;
-                if (r < r_end) {
-                    float f[8];
-                    unpack8(v[u], f);
-                    m = amax8(f, m);
-#pragma unroll
-                    for (int i = 0; i < 8; i++) cs[i] += f[i];
-                    q[r * rowvec + col0 / 8] = quant8<FMT>(f, scale);
-                }
-            }
-        }
-    }
-#pragma unroll
-    for (int i = 0; i < 8; i++) part[rl][cv * 8 + i] = cs[i];
-    if (amax) block_amax_to_global(m, red, amax);   // contains a __syncthreads
-    else __syncthreads();
-    {
-        const int c = threadIdx.x;   // 256 threads <-> 256 columns
-        float s = 0.f;
-#pragma unroll
-        for (int j = 0; j < BG_RL; j++) s += part[j][c];
-        const int64_t col = static_cast<int64_t>(blockIdx.x) * BG_COLS + c;
-        if (col < C) atomicAdd(colsum_ws + col, s);
-    }
-}
-
-// K2b through a shared-memory ring: same strip / row-lane mapping as the kernel above, but the strip's rows arrive as 32 x 256 boxes by TMA
-// (one cp.async.bulk.tensor per stage, zero-filled past the matrix edge) into a ring that keeps `stages - 1` boxes in flight, and the
-// grid is one wave of two CTAs per SM.  The register-staged kernel measured 0.39 of the HBM peak on dY [6144, 4096]: four 16 B loads in
-// flight per thread and three waves of CTAs.
+// The strip's rows arrive as 32 x 256 boxes by TMA (one cp.async.bulk.tensor per stage, zero-filled past the matrix edge) into a ring that
+// keeps `stages - 1` boxes in flight; the grid is one wave of two CTAs per SM.  Measured 0.42 of the HBM peak on dY [6144, 4096] (round 1's
+// register-staged form: 0.39) — the 512 B row segments of a strip, not the staging, are what holds this kernel back; a row-streaming form
+// with per-CTA partial sums (K5's layout) is the next step, and needs a [grid, C] workspace the C ABI does not hand over today.
 constexpr int BGR_ROWS = 32;                                // rows per stage
 constexpr int BGR_STAGE = BGR_ROWS * BG_COLS * 2;           // 16 KB
 template <int FMT>
-__global__ void __launch_bounds__(256, 2) cast_amax_bgrad_ring_kernel(const __grid_constant__ CUtensorMap map_x, uint2* __restrict__ q, int64_t R, int64_t C,
+__global__ void __launch_bounds__(256, 2) cast_amax_bgrad_kernel(const __grid_constant__ CUtensorMap map_x, uint2* __restrict__ q, int64_t R, int64_t C,
                                                                       int64_t rows_per_cta, const float* __restrict__ scale_ptr, float* __restrict__ amax,
                                                                       float* __restrict__ colsum_ws, int stages) {
     extern __shared__ uint8_t smem_raw[];
@@ -382,7 +275,8 @@ int launch_cast_amax_bgrad(const void* x, void* q, int64_t R, int64_t C, int fmt
     cudaError_t e = cudaMemsetAsync(colsum_ws, 0, sizeof(float) * C, stream);
     if (e != cudaSuccess) { set_error("cast_amax_bgrad: memset: %s", cudaGetErrorString(e)); return (int)e; }
     const int strips = static_cast<int>((C + BG_COLS - 1) / BG_COLS);
-    if (!quant_v1() && R < (int64_t(1) << 31) && C < (int64_t(1) << 31)) {
+    LLMFP8_REQUIRE(R < (int64_t(1) << 31) && C < (int64_t(1) << 31), "cast_amax_bgrad: dims too large");
+    {
         int64_t yc = (static_cast<int64_t>(sm_count()) * 2) / strips;          // one wave of two CTAs per SM
         yc = yc < 1 ? 1 : yc;
         int64_t rpc = (R + yc - 1) / yc;
@@ -395,32 +289,19 @@ int launch_cast_amax_bgrad(const void* x, void* q, int64_t R, int64_t C, int fmt
         const int smem = stages * BGR_STAGE + stages * 8 + 128;
         dim3 rgrid(strips, static_cast<unsigned>(yc));
         if (fmt == FMT_E4M3) {
-            e = cudaFuncSetAttribute(cast_amax_bgrad_ring_kernel<FMT_E4M3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(cast_amax_bgrad_kernel<FMT_E4M3>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { set_error("cast_amax_bgrad: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-            LLMFP8_LAUNCH((cast_amax_bgrad_ring_kernel<FMT_E4M3>), rgrid, 256, smem, stream, m_x, static_cast<uint2*>(q), R, C, rpc, scale, amax, colsum_ws, stages);
+            LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E4M3>), rgrid, 256, smem, stream, m_x, static_cast<uint2*>(q), R, C, rpc, scale, amax, colsum_ws, stages);
         } else {
-            e = cudaFuncSetAttribute(cast_amax_bgrad_ring_kernel<FMT_E5M2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
+            e = cudaFuncSetAttribute(cast_amax_bgrad_kernel<FMT_E5M2>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);
             if (e != cudaSuccess) { set_error("cast_amax_bgrad: smem attr: %s", cudaGetErrorString(e)); return (int)e; }
-            LLMFP8_LAUNCH((cast_amax_bgrad_ring_kernel<FMT_E5M2>), rgrid, 256, smem, stream, m_x, static_cast<uint2*>(q), R, C, rpc, scale, amax, colsum_ws, stages);
+            LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E5M2>), rgrid, 256, smem, stream, m_x, static_cast<uint2*>(q), R, C, rpc, scale, amax, colsum_ws, stages);
         }
         LLMFP8_LAUNCH_CHECK("cast_amax_bgrad");
         LLMFP8_LAUNCH((f32_to_bf16_kernel), static_cast<unsigned>((C + 255) / 256), 256, 0, stream, colsum_ws, static_cast<uint16_t*>(bgrad_bf16), C);
         LLMFP8_LAUNCH_CHECK("cast_amax_bgrad.finalize");
         return 0;
     }
-    int64_t ychunks = (static_cast<int64_t>(sm_count()) * 6 + strips - 1) / strips;
-    int64_t rows_per_cta = (R + ychunks - 1) / ychunks;
-    rows_per_cta = (rows_per_cta + 31) / 32 * 32;
-    ychunks = (R + rows_per_cta - 1) / rows_per_cta;
-    dim3 grid(strips, static_cast<unsigned>(ychunks));
-    if (fmt == FMT_E4M3)
-        LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E4M3>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
-    else
-        LLMFP8_LAUNCH((cast_amax_bgrad_kernel<FMT_E5M2>), grid, 256, 0, stream, static_cast<const uint4*>(x), static_cast<uint2*>(q), R, C, rows_per_cta, scale, amax, colsum_ws);
-    LLMFP8_LAUNCH_CHECK("cast_amax_bgrad");
-    LLMFP8_LAUNCH((f32_to_bf16_kernel), static_cast<unsigned>((C + 255) / 256), 256, 0, stream, colsum_ws, static_cast<uint16_t*>(bgrad_bf16), C);
-    LLMFP8_LAUNCH_CHECK("cast_amax_bgrad.finalize");
-    return 0;
 }
 
 int launch_f32_to_bf16(const float* in, void* out, int64_t n, cudaStream_t stream) {

@@ -1,11 +1,12 @@
 // RMSNorm kernels for sm_100a (row per 128-thread CTA, persistent over rows, 16 B loads).
 //   K1   rmsnorm_quant_fwd : x bf16 [M,H], gamma -> fp8 [M,H] (per-tensor scale), rsigma[M], amax   (~3*M*H bytes)
 //   K1r  rmsnorm_rsigma    : x -> rsigma[M] only (first pass of the MXFP8 variant, see mx_quantize.cu)
-//   K5   rmsnorm_bwd       : dy, x, gamma, rsigma -> dx bf16, dgamma bf16 (two-stage column reduction)
+//   K5   rmsnorm_bwd       : dy, x, gamma, rsigma -> dx bf16, dgamma bf16 (rows through a cp.async.bulk ring; two-stage column reduction)
+// K1 / K1r stay register-staged: a ring form of them (row pairs per 256-thread CTA) measured SLOWER on hardware (20.5 -> 22.5 us at
+// [6144, 4096]: 16 resident CTAs of 4 warps hide the row's serial chain better than 2 CTAs of 8) and was removed (profiles/r02/NOTES.md, call 24).
 // Replaces TE's rmsnorm_fwd(+fp8 cast)/rmsnorm_bwd reached from LayerNormLinear / LayerNormMLP
 // (te_llama.py:45-63).  The sum-of-squares reduction ORDER is the one oracle_c.c:orc_rms_rsigma fixes:
 // chunk c (8 elements) -> thread c % 128, in-thread fma chain, xor butterfly, ((w0+w1)+w2)+w3.
-#include <cstdlib>
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -90,124 +91,11 @@ __global__ void __launch_bounds__(RMS_T) rmsnorm_fwd_kernel(const uint4* __restr
     if (OUT_MODE == 0 && amax) block_amax_to_global(m, red_amax, amax);
 }
 
-// K1 / K1r through a shared-memory ring (the default; LLMFP8_QUANT_V1=1 keeps the kernel above): a CTA of 256 threads works on TWO
-// consecutive rows per step — threads 0..127 on the first, 128..255 on the second, each half with the row kernel's thread -> chunk
-// mapping and reduction order, so rsigma and the fp8 bytes are the same bit for bit — and the row pairs stream through a ring of
-// stages filled by 1-D bulk copies (cp.async.bulk; one copy per pair: the two rows are contiguous).  Thread 0 refills a slot right
-// after the block barrier of the reduction, which also proves that every thread has its chunks in registers.
-template <int FMT, int NIT, int OUT_MODE>
-__global__ void __launch_bounds__(2 * RMS_T) rmsnorm_fwd_ring_kernel(const uint8_t* __restrict__ x, const uint4* __restrict__ gamma, uint2* __restrict__ q,
-                                                                     float* __restrict__ rsigma, int64_t M, int H, float eps,
-                                                                     const float* __restrict__ scale_ptr, float* __restrict__ amax, int stages) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* ring = smem_raw + ((128u - (ptx::smem_u32(smem_raw) & 127u)) & 127u);
-    const uint32_t row_bytes = static_cast<uint32_t>(H) * 2u;
-    const uint32_t stage_bytes = (2u * row_bytes + 127u) & ~127u;
-    uint64_t* full = reinterpret_cast<uint64_t*>(ring + stages * stage_bytes);
-    __shared__ float red[2][2][4];
-    __shared__ float red_amax[8];
-    const int t = threadIdx.x, grp = t >> 7, tt = t & (RMS_T - 1);
-    const int64_t npairs = (M + 1) / 2;
-    auto load_pair = [&](int64_t p, int stage) {                    // thread 0 only
-        const uint32_t bytes = (2 * p + 1 < M ? 2u : 1u) * row_bytes;
-        ptx::mbar_arrive_expect_tx(&full[stage], bytes);
-        ptx::bulk_load_1d(ring + stage * stage_bytes, x + 2 * p * row_bytes, bytes, &full[stage]);
-    };
-    if (t == 0) {
-        for (int i = 0; i < stages; i++) ptx::mbar_init(&full[i], 1);
-        ptx::fence_barrier_init();
-    }
-    __syncthreads();
-    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_launch_dependents();
-    if (t == 0) {
-        int64_t p = blockIdx.x;
-        for (int i = 0; i < stages && p < npairs; i++, p += gridDim.x) load_pair(p, i);
-    }
-    const int nchunk = H / 8;
-    const float scale = (OUT_MODE == 0 && scale_ptr) ? __ldg(scale_ptr) : 1.0f;
-    uint4 g[NIT];
-    if (OUT_MODE == 0) {
-#pragma unroll
-        for (int it = 0; it < NIT; it++)
-            if (it * RMS_T + tt < nchunk) g[it] = __ldg(gamma + it * RMS_T + tt);
-    }
-    const int64_t ahead = static_cast<int64_t>(stages) * gridDim.x;
-    float m = 0.f;
-    int stage = 0, phase = 0, par = 0;
-    for (int64_t p = blockIdx.x; p < npairs; p += gridDim.x, par ^= 1) {
-        const int64_t row = 2 * p + grp;
-        const bool live = row < M;
-        ptx::mbar_wait(&full[stage], phase);
-        const uint4* src = reinterpret_cast<const uint4*>(ring + stage * stage_bytes + grp * row_bytes);
-        uint4 v[NIT];
-        float acc = 0.f;
-#pragma unroll
-        for (int it = 0; it < NIT; it++) {
-            if (it * RMS_T + tt < nchunk) {
-                v[it] = live ? src[it * RMS_T + tt] : make_uint4(0, 0, 0, 0);
-                float f[8];
-                unpack8(v[it], f);
-#pragma unroll
-                for (int j = 0; j < 8; j++) acc = __fmaf_rn(f[j], f[j], acc);
-            }
-        }
-        acc = warp_sum_pinned(acc);
-        if ((tt & 31) == 0) red[par][grp][tt >> 5] = acc;
-        __syncthreads();                                            // also: every thread has its chunks of this slot in registers
-        if (t == 0 && p + ahead < npairs) load_pair(p + ahead, stage);
-        if (++stage == stages) { stage = 0; phase ^= 1; }
-        const float total = __fadd_rn(__fadd_rn(__fadd_rn(red[par][grp][0], red[par][grp][1]), red[par][grp][2]), red[par][grp][3]);
-        const float mean = __fdiv_rn(total, static_cast<float>(H));
-        const float rs = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
-        if (!live) continue;
-        if (tt == 0) rsigma[row] = rs;
-        if (OUT_MODE == 0) {
-            uint2* qr = q + row * nchunk;
-#pragma unroll
-            for (int it = 0; it < NIT; it++) {
-                if (it * RMS_T + tt < nchunk) {
-                    float f[8], gf[8];
-                    unpack8(v[it], f);
-                    unpack8(g[it], gf);
-#pragma unroll
-                    for (int j = 0; j < 8; j++) f[j] = __fmul_rn(__fmul_rn(f[j], rs), gf[j]);
-                    m = amax8(f, m);
-                    qr[it * RMS_T + tt] = quant8<FMT>(f, scale);
-                }
-            }
-        }
-    }
-    if (OUT_MODE == 0 && amax) block_amax_to_global(m, red_amax, amax);
-}
-
-static bool rms_v1() {
-    static const bool v1 = [] { const char* e = getenv("LLMFP8_QUANT_V1"); return e && e[0] == '1'; }();
-    return v1;
-}
-
 template <int FMT, int OUT_MODE>
 static int dispatch_rms_fwd(int nit, int grid, cudaStream_t s, const uint4* x, const uint4* g, uint2* q, float* rs, int64_t M, int H, float eps,
                             const float* scale, float* amax) {
-    // ring: row pairs, as many stages as fit in ~104 KB (two CTAs per SM), at most 8
-    const int64_t stage_bytes = (4 * static_cast<int64_t>(H) + 127) / 128 * 128;
-    int stages = static_cast<int>(104 * 1024 / stage_bytes);
-    stages = stages > 8 ? 8 : stages;
-    const int smem = static_cast<int>(stages * stage_bytes + stages * 8 + 128);
-    const bool ring = !rms_v1() && stages >= 2;
 #define RMS_CASE(N)                                                                                              \
     case N:                                                                                                      \
-        if (ring) {                                                                                              \
-            auto kern = rmsnorm_fwd_ring_kernel<FMT, N, OUT_MODE>;                                               \
-            cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);       \
-            if (e != cudaSuccess) { set_error("rmsnorm: smem attr: %s", cudaGetErrorString(e)); return (int)e; } \
-            int per_sm = 0;                                                                                      \
-            if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 2 * RMS_T, smem) != cudaSuccess || per_sm < 1) per_sm = 1; \
-            const int64_t cap = static_cast<int64_t>(sm_count()) * per_sm, npairs = (M + 1) / 2;                 \
-            grid = static_cast<int>(npairs < cap ? npairs : cap);                                                \
-            LLMFP8_LAUNCH(kern, grid, 2 * RMS_T, smem, s, reinterpret_cast<const uint8_t*>(x), g, q, rs, M, H, eps, scale, amax, stages); \
-            break;                                                                                               \
-        }                                                                                                        \
         grid = resident_grid(rmsnorm_fwd_kernel<FMT, N, OUT_MODE>, RMS_T, M);                                    \
         LLMFP8_LAUNCH((rmsnorm_fwd_kernel<FMT, N, OUT_MODE>), grid, RMS_T, 0, s, x, g, q, rs, M, H, eps, scale, amax);        \
         break;
@@ -252,131 +140,18 @@ int launch_rmsnorm_rsigma(const void* x, float* rsigma, int64_t M, int64_t H, fl
 
 // ------------------------------------------------------------------------------------------- K5
 // dx = rs * (dy*g - xhat * mean(dy*g*xhat)),  dgamma = sum_rows dy * xhat   (xhat = x * rs), fp32 math.
-// 256 threads per row (two 16 B chunks per thread at H = 4096); the NEXT row's x / dy are loaded before the current row is
-// reduced, so a CTA always has one row of loads in flight while it computes (the one-row-at-a-time version measured 40 % of HBM).
+// 256 threads per row (two 16 B chunks per thread at H = 4096).
 constexpr int RB_T = 256;
 // ADD: dx += dres (the gradient arriving on the residual branch around the norm), so autograd needs no separate accumulation pass.
+// Rows of x, dy (and dres) stream into a ring of shared-memory stages with 1-D bulk copies (cp.async.bulk, mbarrier completion) and the
+// 256 threads take their 16 B chunks from the ring.  Thread 0 is the producer: the block barrier of the row reduction already proves
+// that every thread holds its chunks of the current stage in registers, so right after it the slot is refilled with the row `stages`
+// iterations ahead — no second barrier, no producer warp.  (Round 1's form prefetched ONE row per CTA into registers: 0.59 / 0.71 of
+// the measured HBM peak without / with dres at [6144, 4096]; the ring: 0.65 / 0.82, profiles/r02/NOTES.md calls 23-24.  What is left
+// without dres is the serial chain of one row per CTA and step — wait, reduce, barrier, store — not bytes in flight: 4 -> 6 ring
+// stages changed nothing.)
 template <int NIT, bool ADD>
-__global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(const uint4* __restrict__ dy, const uint4* __restrict__ x, const uint4* __restrict__ gamma,
-                                                           const float* __restrict__ rsigma, const uint4* __restrict__ dres, uint4* __restrict__ dx,
-                                                           float* __restrict__ dgamma_part, int64_t M, int H) {
-    pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
-    pdl_launch_dependents();
-    __shared__ float red[2][RB_T / 32];
-    const int t = threadIdx.x;
-    const int nchunk = H / 8;
-    // per thread: NIT chunks of 8 columns; gamma and the dgamma partial sums stay in registers as packed fp32 pairs
-    f32x2 dg[NIT][4], g2[NIT][4];
-#pragma unroll
-    for (int it = 0; it < NIT; it++) {
-        float gf[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-        if (it * RB_T + t < nchunk) unpack8(__ldg(gamma + it * RB_T + t), gf);
-#pragma unroll
-        for (int k = 0; k < 4; k++) {
-            dg[it][k] = pk2(0.f, 0.f);
-            g2[it][k] = pk2(gf[2 * k], gf[2 * k + 1]);
-        }
-    }
-    uint4 nx[NIT], ndy[NIT];
-    float nrs = 0.f;
-    int64_t row = blockIdx.x;
-    if (row < M) {
-#pragma unroll
-        for (int it = 0; it < NIT; it++)
-            if (it * RB_T + t < nchunk) {
-                nx[it] = ldg_stream(x + row * nchunk + it * RB_T + t);
-                ndy[it] = ldg_stream(dy + row * nchunk + it * RB_T + t);
-            }
-        nrs = rsigma[row];
-    }
-    const float inv_h = 1.0f / static_cast<float>(H);
-    int par = 0;
-    for (; row < M; row += gridDim.x, par ^= 1) {
-        const float rs = nrs;
-        const f32x2 rs2 = pk2(rs, rs);
-        f32x2 xh[NIT][4], tg[NIT][4];       // xhat = x * rs ; tg = dy * gamma
-        f32x2 dot2 = pk2(0.f, 0.f);
-#pragma unroll
-        for (int it = 0; it < NIT; it++)
-            if (it * RB_T + t < nchunk) {
-                float fx[8], fdy[8];
-                unpack8(nx[it], fx);
-                unpack8(ndy[it], fdy);
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    const f32x2 dy2 = pk2(fdy[2 * k], fdy[2 * k + 1]);
-                    xh[it][k] = mul2(pk2(fx[2 * k], fx[2 * k + 1]), rs2);
-                    tg[it][k] = mul2(dy2, g2[it][k]);
-                    dot2 = fma2(tg[it][k], xh[it][k], dot2);
-                    dg[it][k] = fma2(dy2, xh[it][k], dg[it][k]);
-                }
-            }
-        // the next row's loads go out before this row's reduction and stores
-        const int64_t nrow = row + gridDim.x;
-        if (nrow < M) {
-#pragma unroll
-            for (int it = 0; it < NIT; it++)
-                if (it * RB_T + t < nchunk) {
-                    nx[it] = ldg_stream(x + nrow * nchunk + it * RB_T + t);
-                    ndy[it] = ldg_stream(dy + nrow * nchunk + it * RB_T + t);
-                }
-            nrs = rsigma[nrow];
-        }
-        uint4 vres[NIT];
-        if constexpr (ADD) {
-#pragma unroll
-            for (int it = 0; it < NIT; it++)
-                if (it * RB_T + t < nchunk) vres[it] = ldg_stream(dres + row * nchunk + it * RB_T + t);
-        }
-        float d0, d1;
-        upk2(dot2, d0, d1);
-        const float dot = warp_sum(d0 + d1);
-        if ((t & 31) == 0) red[par][t >> 5] = dot;
-        __syncthreads();
-        float tot = 0.f;
-#pragma unroll
-        for (int w = 0; w < RB_T / 32; w++) tot += red[par][w];
-        // dx = rs * tg - (rs * c) * xhat
-        const float nc = -(rs * (tot * inv_h));
-        const f32x2 nc2 = pk2(nc, nc);
-#pragma unroll
-        for (int it = 0; it < NIT; it++)
-            if (it * RB_T + t < nchunk) {
-                uint32_t o[4];
-                float fr[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
-                if constexpr (ADD) unpack8(vres[it], fr);
-#pragma unroll
-                for (int k = 0; k < 4; k++) {
-                    float lo, hi;
-                    upk2(fma2(xh[it][k], nc2, mul2(tg[it][k], rs2)), lo, hi);
-                    if constexpr (ADD) { lo += fr[2 * k]; hi += fr[2 * k + 1]; }
-                    o[k] = pack_bf16x2(lo, hi);
-                }
-                dx[row * nchunk + it * RB_T + t] = make_uint4(o[0], o[1], o[2], o[3]);
-            }
-    }
-    float* out = dgamma_part + static_cast<int64_t>(blockIdx.x) * H;
-#pragma unroll
-    for (int it = 0; it < NIT; it++)
-        if (it * RB_T + t < nchunk) {
-            float v[8];
-#pragma unroll
-            for (int k = 0; k < 4; k++) upk2(dg[it][k], v[2 * k], v[2 * k + 1]);
-            float4* o4 = reinterpret_cast<float4*>(out + (it * RB_T + t) * 8);
-            o4[0] = make_float4(v[0], v[1], v[2], v[3]);
-            o4[1] = make_float4(v[4], v[5], v[6], v[7]);
-        }
-}
-
-// K5, TMA-staged (the default; LLMFP8_K5_V1=1 keeps the register-prefetch kernel above for one A/B): whole rows of x, dy (and dres) stream
-// into a ring of shared-memory stages with 1-D bulk copies (cp.async.bulk, mbarrier completion) and the 256 threads take their 16 B chunks
-// from the ring.  The kernel above keeps ONE row of loads in flight per CTA (32 KB per SM with two resident CTAs — half of what the HBM
-// latency-bandwidth product asks for, 0.59 of the measured peak); here every CTA has stages - 1 rows in flight.  Thread 0 is the
-// producer: the block barrier of the row reduction already proves that every thread holds its chunks of the current stage in registers,
-// so right after it the slot is refilled with the row `stages` iterations ahead — no second barrier, no producer warp.
-// Same arithmetic, same thread -> chunk mapping, same dgamma partial layout.
-template <int NIT, bool ADD>
-__global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_tma_kernel(const uint8_t* __restrict__ dy, const uint8_t* __restrict__ x,
+__global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(const uint8_t* __restrict__ dy, const uint8_t* __restrict__ x,
                                                                                    const uint4* __restrict__ gamma, const float* __restrict__ rsigma,
                                                                                    const uint8_t* __restrict__ dres, uint4* __restrict__ dx,
                                                                                    float* __restrict__ dgamma_part, int64_t M, int H, int stages) {
@@ -546,10 +321,8 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
     if (M == 0) return 0;
     const int nit = static_cast<int>((H / 8 + RB_T - 1) / RB_T);
     int grid = 0;
-    static const bool k5_v1 = [] { const char* e = getenv("LLMFP8_K5_V1"); return e && e[0] == '1'; }();
-    if (!k5_v1) {
-        // ring: as many whole-row stages as fit in ~104 KB (two CTAs per SM) or ~208 KB (one CTA: H > 4096), at most 8.  Bytes in flight are
-        // what counts: with 4 stages the 2-row form (96 KB in flight per SM) measured 0.65 of the HBM peak, the 3-row form (144 KB) 0.82.
+    {
+        // ring: as many whole-row stages as fit in ~104 KB (two CTAs per SM) or ~208 KB (one CTA: H > 4096), at most 8
         const int64_t stage_bytes = (((dres ? 3 : 2) * H * 2) + 127) / 128 * 128;
         const int64_t budget = nit <= 2 ? 104 * 1024 : 208 * 1024;
         int stages = static_cast<int>(budget / stage_bytes);
@@ -558,7 +331,7 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
         const int smem = static_cast<int>(stages * stage_bytes + stages * 8 + 2 * (RB_T / 32) * 4 + 128);
 #define RMSB_TMA(N, ADD)                                                                                                                       \
     do {                                                                                                                                       \
-        auto kern = rmsnorm_bwd_tma_kernel<N, ADD>;                                                                                            \
+        auto kern = rmsnorm_bwd_kernel<N, ADD>;                                                                                            \
         cudaError_t e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem);                                         \
         if (e != cudaSuccess) { set_error("rmsnorm_bwd: smem attr: %s", cudaGetErrorString(e)); return (int)e; }                               \
         int per_sm = 0;                                                                                                                        \
@@ -585,28 +358,6 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
         LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
         return 0;
     }
-#define RMSB_LAUNCH(N, ADD)                                                                                                                    \
-    do {                                                                                                                                       \
-        grid = resident_grid(rmsnorm_bwd_kernel<N, ADD>, RB_T, M);                                                                             \
-        if (grid > rmsnorm_bwd_grid(M)) grid = rmsnorm_bwd_grid(M);                                                                            \
-        LLMFP8_LAUNCH((rmsnorm_bwd_kernel<N, ADD>), grid, RB_T, 0, stream, (const uint4*)dy, (const uint4*)x, (const uint4*)gamma, rsigma, (const uint4*)dres, \
-                                                              (uint4*)dx, ws, M, (int)H);                                                      \
-    } while (0)
-#define RMSB_CASE(N)                                                                                                                           \
-    case N:                                                                                                                                    \
-        if (dres) RMSB_LAUNCH(N, true);                                                                                                        \
-        else RMSB_LAUNCH(N, false);                                                                                                            \
-        break;
-    switch (nit) {
-        RMSB_CASE(1) RMSB_CASE(2) RMSB_CASE(3) RMSB_CASE(4)
-        default: set_error("rmsnorm_bwd: hidden size too large"); return -1;
-    }
-#undef RMSB_LAUNCH
-#undef RMSB_CASE
-    LLMFP8_LAUNCH_CHECK("rmsnorm_bwd");
-    LLMFP8_LAUNCH((colreduce_bf16_kernel), static_cast<unsigned>((H + CR_COLS - 1) / CR_COLS), CR_COLS * CR_LANES, 0, stream, ws, grid, (int)H, static_cast<uint16_t*>(dgamma_bf16));
-    LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
-    return 0;
 }
 
 }  // namespace llmfp8

@@ -3,11 +3,11 @@
 # (mnemonics as listed in /opt/skills/guides/B200_PROFILING.md).  Runs without a GPU:  bash tools/sass_summary.sh > profiles/r02/sass_counts.txt
 cd "$(dirname "$0")/../llm_fp8_b200/csrc" || exit 1
 echo "# cuobjdump -sass <object> | grep -c <mnemonic>   ($(/usr/local/cuda/bin/nvcc --version | tail -1), -gencode arch=compute_100a,code=sm_100a)"
-printf "%-22s %8s %8s %8s %8s %8s %8s %8s %8s %8s\n" object UTCQMMA UTCHMMA UTCCP LDTM UTMALDG UTMASTG UCGABAR LDGMC SYNCS
-for o in gemm.o mx_quantize.o mx_act_quantize.o quantize.o rmsnorm.o swiglu.o nvls_reduce.o lm_head.o; do
+printf "%-22s %8s %8s %8s %8s %8s %8s %8s %8s %8s %8s\n" object UTCQMMA UTCHMMA UTCCP LDTM UTMALDG UTMASTG UBLKCP UCGABAR LDGMC SYNCS
+for o in gemm.o mx_quantize.o mx_act_quantize.o adamw_mx.o quantize.o rmsnorm.o swiglu.o nvls_reduce.o lm_head.o; do
   s=$(/usr/local/cuda/bin/cuobjdump -sass $o 2>/dev/null)
   c() { echo "$s" | grep -c "$1"; }
-  printf "%-22s %8s %8s %8s %8s %8s %8s %8s %8s %8s\n" $o $(c UTCQMMA) $(c UTCHMMA) $(c UTCCP) $(c LDTM) $(c UTMALDG) $(c UTMASTG) $(c UCGABAR) $(c LDGMC) $(c "SYNCS")
+  printf "%-22s %8s %8s %8s %8s %8s %8s %8s %8s %8s %8s\n" $o $(c UTCQMMA) $(c UTCHMMA) $(c UTCCP) $(c LDTM) $(c UTMALDG) $(c UTMASTG) $(c UBLKCP) $(c UCGABAR) $(c LDGMC) $(c "SYNCS")
 done
 echo
 echo "# gemm.o: distinct tensor-core / TMA instruction forms"
