@@ -66,6 +66,17 @@ int llmfp8_rmsnorm_bwd_ws_rows(int64_t M);
 int llmfp8_rmsnorm_bwd_add(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma, float* ws,
                            int64_t M, int64_t H, void* stream);
 
+/* K5 for callers that cannot allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the
+ * reference.  Same results as llmfp8_rmsnorm_bwd (dres == NULL) / llmfp8_rmsnorm_bwd_add (dres != NULL), but
+ * the fp32 workspace is a static device array inside the library (llmfp8_rmsnorm_bwd_noalloc_max_floats() = 592 * 4096 floats, 9.25 MiB, held by every GPU
+ * that loads the library until exit) instead of a caller buffer, and the call performs no cudaMalloc / cudaFree / allocating library call.
+ * Limit: llmfp8_rmsnorm_bwd_ws_rows(M) * H <= that maximum (any M at H <= 4096); larger problems return -1 with a message in llmfp8_last_error().
+ * The device of `stream` must be the calling thread's current device.  All calls on a device share the array: calls that OVERLAP on the GPU (different
+ * streams) race on it and must be serialised by the caller; the array keeps the previous call's partial sums, which the kernel overwrites before reading. */
+int llmfp8_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma, int64_t M,
+                               int64_t H, void* stream);
+int64_t llmfp8_rmsnorm_bwd_noalloc_max_floats(void);
+
 /* K3: a = silu(gate) * up over fc1_out bf16 [M, 2I] (gate = [:, :I], up = [:, I:]); q u8 [M, I].   [tex.swiglu + cast] */
 int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream);
 

@@ -32,6 +32,8 @@ _PROTOTYPES = {
     "llmfp8_rmsnorm_bwd": [vp, vp, vp, vp, vp, vp, vp, i64, i64, vp],
     "llmfp8_rmsnorm_bwd_ws_rows": [i64],
     "llmfp8_rmsnorm_bwd_add": [vp, vp, vp, vp, vp, vp, vp, vp, i64, i64, vp],
+    "llmfp8_rmsnorm_bwd_noalloc": [vp, vp, vp, vp, vp, vp, vp, i64, i64, vp],
+    "llmfp8_rmsnorm_bwd_noalloc_max_floats": [],
     "llmfp8_swiglu_quant_fwd": [vp, vp, i64, i64, i32, vp, vp, vp],
     "llmfp8_dswiglu_quant_bwd": [vp, vp, vp, i64, i64, i32, vp, vp, vp, vp, vp],
     "llmfp8_amax_scale_update": [vp, vp, vp, vp, i32, i32, i32, vp],
@@ -69,7 +71,7 @@ _PROTOTYPES = {
     "llmfp8_nvls_reset": [],
     "llmfp8_mxfp8_gemm_res": [vp, i64, i32, vp, vp, i64, i32, vp, vp, i64, i32, i32, i32, vp, vp, i64, i32, vp],
 }
-_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_trace": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
+_RESTYPES = {"llmfp8_last_error": C.c_char_p, "llmfp8_mx_scale_bytes": i64, "llmfp8_rmsnorm_bwd_noalloc_max_floats": i64, "llmfp8_launch_count": C.c_uint64, "llmfp8_gemm_force_bn": None, "llmfp8_gemm_trace": None, "llmfp8_gemm_force_cg": None, "llmfp8_gemm_debug": None}
 EXPORTS = tuple(_PROTOTYPES)
 
 
@@ -123,6 +125,8 @@ def _work(name: str, a):
         return "byte", 6.0 * a[7] * a[8]
     if name == "llmfp8_rmsnorm_bwd_add":
         return "byte", 8.0 * a[8] * a[9]
+    if name == "llmfp8_rmsnorm_bwd_noalloc":
+        return "byte", (8.0 if a[4] is not None else 6.0) * a[7] * a[8]
     if name == "llmfp8_rmsnorm_rsigma":
         return "byte", 2.0 * a[2] * a[3]
     if name == "llmfp8_swiglu_quant_fwd":
@@ -163,7 +167,7 @@ class _Profiled:
     def __getattr__(self, name):
         fn = getattr(self._lib, name)
         if name in ("llmfp8_gemm_trace", "llmfp8_gemm_force_bn", "llmfp8_gemm_force_cg", "llmfp8_gemm_debug", "llmfp8_last_error", "llmfp8_abi_version", "llmfp8_sm_count", "llmfp8_launch_count", "llmfp8_mx_scale_bytes",
-                    "llmfp8_rmsnorm_bwd_ws_rows", "llmfp8_lm_head_partials", "llmfp8_ce_reduce_ws_floats") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
+                    "llmfp8_rmsnorm_bwd_ws_rows", "llmfp8_rmsnorm_bwd_noalloc_max_floats", "llmfp8_lm_head_partials", "llmfp8_ce_reduce_ws_floats") or name.startswith(("llmfp8_nccl_", "llmfp8_nvls_")):
             return fn
         import torch
 

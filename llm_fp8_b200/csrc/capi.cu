@@ -115,6 +115,8 @@ int launch_rmsnorm_quant_fwd(const void*, const void*, void*, float*, int64_t, i
 int launch_rmsnorm_rsigma(const void*, float*, int64_t, int64_t, float, cudaStream_t);
 int launch_rmsnorm_bwd(const void*, const void*, const void*, const float*, const void*, void*, void*, float*, int64_t, int64_t, cudaStream_t);
 int rmsnorm_bwd_grid(int64_t);
+int launch_rmsnorm_bwd_noalloc(const void*, const void*, const void*, const float*, const void*, void*, void*, int64_t, int64_t, cudaStream_t);
+int64_t rmsnorm_bwd_noalloc_max_floats();
 int launch_swiglu_quant_fwd(const void*, void*, int64_t, int64_t, int, const float*, float*, cudaStream_t);
 int launch_dswiglu_quant_bwd(const void*, const void*, void*, int64_t, int64_t, int, const float*, float*, float*, void*, cudaStream_t);
 int launch_mx_quantize(const void*, int64_t, int64_t, int64_t, void*, void*, void*, void*, const float*, const void*, float*, void*, cudaStream_t);
@@ -178,6 +180,11 @@ int llmfp8_rmsnorm_bwd_add(const void* dy, const void* x, const void* gamma, con
     return launch_rmsnorm_bwd(dy, x, gamma, rsigma, dres, dx, dgamma, ws, M, H, S(stream));
 }
 int llmfp8_rmsnorm_bwd_ws_rows(int64_t M) { return rmsnorm_bwd_grid(M); }
+int llmfp8_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma, int64_t M,
+                               int64_t H, void* stream) {
+    return launch_rmsnorm_bwd_noalloc(dy, x, gamma, rsigma, dres, dx, dgamma, M, H, S(stream));
+}
+int64_t llmfp8_rmsnorm_bwd_noalloc_max_floats(void) { return rmsnorm_bwd_noalloc_max_floats(); }
 int llmfp8_swiglu_quant_fwd(const void* fc1_out, void* q, int64_t M, int64_t I, int fmt, const float* scale, float* amax, void* stream) {
     return launch_swiglu_quant_fwd(fc1_out, q, M, I, fmt, scale, amax, S(stream));
 }

@@ -7,6 +7,7 @@
 // Replaces TE's rmsnorm_fwd(+fp8 cast)/rmsnorm_bwd reached from LayerNormLinear / LayerNormMLP
 // (te_llama.py:45-63).  The sum-of-squares reduction ORDER is the one oracle_c.c:orc_rms_rsigma fixes:
 // chunk c (8 elements) -> thread c % 128, in-thread fma chain, xor butterfly, ((w0+w1)+w2)+w3.
+#include <mutex>
 #include "common.cuh"
 #include "ptx.cuh"
 
@@ -358,6 +359,47 @@ int launch_rmsnorm_bwd(const void* dy, const void* x, const void* gamma, const f
         LLMFP8_LAUNCH_CHECK("rmsnorm_bwd.dgamma");
         return 0;
     }
+}
+
+// ------------------------------------------------------------------------------------------- K5 without caller-provided scratch
+// llmfp8_rmsnorm_bwd_noalloc: K5 for callers that cannot allocate (CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).
+// The dgamma partial rows ([launched CTAs, H] fp32, every element written by the kernel before the column reduce reads it: nothing has
+// to start at zero) live in a file-scope device array instead of a caller workspace.  Every GPU that loads the library holds the array
+// until exit; every call on a device shares it, so calls that overlap on that GPU (two streams) race on it — serialise them.
+// In host code `g_k5_scratch` is a host-side stand-in, not a device address: the address the kernel gets comes from
+// cudaGetSymbolAddress, taken once per device with that device current.  This path calls no cudaMalloc / cudaFree / allocating routine.
+constexpr int64_t K5_SCRATCH_FLOATS = 592ll * 4096;                  // 9.25 MiB: rmsnorm_bwd_grid(M) = 4 x 148 partial rows of H <= 4096
+static __device__ __align__(256) float g_k5_scratch[K5_SCRATCH_FLOATS];
+constexpr int K5_MAX_DEVICES = 64;
+
+int64_t rmsnorm_bwd_noalloc_max_floats() { return K5_SCRATCH_FLOATS; }
+
+int launch_rmsnorm_bwd_noalloc(const void* dy, const void* x, const void* gamma, const float* rsigma, const void* dres, void* dx, void* dgamma_bf16,
+                               int64_t M, int64_t H, cudaStream_t stream) {
+    LLMFP8_REQUIRE(M >= 0 && H > 0, "rmsnorm_bwd_noalloc: bad sizes M=%lld H=%lld", (long long)M, (long long)H);
+    const int64_t need = static_cast<int64_t>(rmsnorm_bwd_grid(M)) * H;
+    LLMFP8_REQUIRE(need <= K5_SCRATCH_FLOATS,
+                   "rmsnorm_bwd_noalloc: %lld partial rows x H = %lld need %lld floats of scratch, the built-in array holds %lld "
+                   "(H <= 4096 at any M; larger H only while rows x H fits) - use llmfp8_rmsnorm_bwd with a caller workspace",
+                   (long long)rmsnorm_bwd_grid(M), (long long)H, (long long)need, (long long)K5_SCRATCH_FLOATS);
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) { set_error("rmsnorm_bwd_noalloc: cudaGetDevice: %s", cudaGetErrorString(e)); return (int)e; }
+    LLMFP8_REQUIRE(dev >= 0 && dev < K5_MAX_DEVICES, "rmsnorm_bwd_noalloc: device ordinal %d out of range", dev);
+    static std::mutex mu;
+    static float* dev_ptr[K5_MAX_DEVICES] = {};
+    float* ws = nullptr;
+    {
+        std::lock_guard<std::mutex> lock(mu);
+        if (!dev_ptr[dev]) {
+            float* p = nullptr;
+            e = cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_k5_scratch);      // this device's copy of the array
+            if (e != cudaSuccess || !p) { set_error("rmsnorm_bwd_noalloc: cudaGetSymbolAddress: %s", cudaGetErrorString(e)); return e != cudaSuccess ? (int)e : -1; }
+            dev_ptr[dev] = p;
+        }
+        ws = dev_ptr[dev];
+    }
+    return launch_rmsnorm_bwd(dy, x, gamma, rsigma, dres, dx, dgamma_bf16, ws, M, H, stream);
 }
 
 }  // namespace llmfp8
