@@ -178,7 +178,7 @@ void llmfp8_gemm_force_cg(int cg);
 /* experiments only: bit 0 skips the MX scale smem->TMEM copies, bit 1 the scale loads (results become wrong); bit 3 = static
  * persistent grid instead of cluster launch control, bit 4 = single TMEM accumulator for MXFP8 at 256-column tiles (results unchanged),
  * bit 5 = single accumulator under the fused-residual MXFP8 epilogue (default: overlapped accumulators there too), bit 6 = at most 5
- * ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier */
+ * ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier, bit 8 = overlapped MX accumulators 192 instead of 224 columns apart */
 void llmfp8_gemm_debug(int flags);
 /* experiments only (LLMFP8_ALLOW_TUNING=1): device buffer of 64 x 16 u64 that the first cluster of every following FP8 GEMM launch fills with clock64
  * stamps of its MMA thread (slots 0-4: tile start, accumulator free, shared columns free, first stage full, last MMA issued) and of two epilogue

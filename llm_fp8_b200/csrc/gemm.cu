@@ -65,10 +65,13 @@ struct GemmParams {
     int acc_stages;             // TMEM accumulator buffers (2; 1 for MX with bn > 192 when acc_overlap is off)
     int debug;                  // experiments only: bit 0 = skip the per-stage scale copies (smem -> TMEM), bit 1 = skip the scale TMA loads,
                                 // bit 3 = static persistent grid, bit 4 = single accumulator for MX at 256 columns (no OVL),
-                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier
+                                // bit 5 = single accumulator for the fused-residual MX kernel (no RES + OVL), bit 6 = at most 5 ring stages, bit 7 = epilogue warps sleep between polls of their accumulator barrier,
+                                // bit 8 = overlapped accumulators 192 columns apart (64 shared) instead of 224 (32 shared)
     int dynamic;                // 1: tiles handed out by cluster launch control (grid = one cluster per tile); 0: static round-robin over a persistent grid
     int sf_tiles;               // MX: 512 B scale tiles per stage = 1 (SFA) + 2 or 3 (SFB)
-    int acc_overlap;            // MX at 256 columns: two accumulators that share 64 TMEM columns (OVL kernels); debug bit 4 turns it off
+    int acc_overlap;            // MX at 256 columns: two accumulators that share TMEM columns (OVL kernels); debug bit 4 turns it off
+    int ovl_stride;             // OVL kernels: column distance of the two accumulators — 224 (32 shared columns, two scale buffers at 480..511; the default) or,
+                                // debug bit 8, 192 (64 shared columns, four scale buffers at 448..511: the first form)
     // cross-entropy epilogues of the bf16 lm_head GEMM (EPI 1 / 2)
     const int64_t* ce_labels;   // [M] class index per row
     const float* ce_lse;        // EPI 2: [M] log-sum-exp of each row's logits
@@ -140,11 +143,13 @@ __device__ __forceinline__ void tma3d(const CUtensorMap* m, uint64_t* bar, uint3
 
 // RES: fused residual add in the staged bf16 epilogue (fprop layouts only) — a separate instantiation so the 32 prefetch registers
 // it needs never weigh on the plain kernels.
-// OVL (MX at 256 columns without accumulate / residual; debug bit 4 selects the single-accumulator kernel instead): two accumulators
-// of 256 columns laid 192 apart — [0, 256) and [192, 448) — instead of one, in the 448 TMEM columns the scale factors leave.  They share columns [192, 256); the epilogue of a
-// tile drains that shared chunk first and signals `ovl_free`, after which the MMAs of the next tile may start while the rest of the
-// previous accumulator is still being read: the exposed epilogue shrinks from a whole tile's read-out to one 64-column chunk.
-constexpr int OVL_STRIDE = 192;
+// OVL (MX at 256 columns without accumulate; debug bit 4 selects the single-accumulator kernel instead): two accumulators of 256 columns
+// laid p.ovl_stride apart instead of one.  224 apart (the default): [0, 256) and [224, 480) share columns [224, 256), two rotating 16-column
+// scale buffers live in [480, 512).  192 apart (debug bit 8, the first form): [0, 256) / [192, 448), four scale buffers in [448, 512).  The
+// epilogue of a tile drains the shared columns first and signals `ovl_free`, after which the MMAs of the next tile may start while the
+// rest of the previous accumulator is still being read: the exposed epilogue shrinks from a whole tile's read-out to the shared chunk —
+// 32 lanes x 32 columns x 4 B per warp at the 16 B per cycle a TMEM lane quarter delivers = 256 cycles (64 columns: 512).  Measured, same
+// box: qkv fprop 2476 -> 2505 TF, proj 2092 -> 2104, fc1 2987 -> 2994, in-step GEMM launches 277.1 -> 275.9 us (profiles/r02/NOTES.md, call 28).
 // BF: bf16 operands (kind::f16, fp32 accumulate) through the same pipeline — a stage still holds 128 B of k per row, i.e. 64 k-elements,
 // one tcgen05.mma covers 16 of them (32 B), MN-major operands come in 64-element (128 B) swizzle atoms.  The lm_head of the reference
 // (HF nn.Linear in bf16, outside TE: train_fp8.py:278) runs on it.  EPI selects what the epilogue does with the fp32 accumulator:
@@ -201,7 +206,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
             ptx::mbar_init(&tmem_full[s], 1);
             ptx::mbar_init(&tmem_empty[s], EPI_WARPS * CG);
         }
-        if constexpr (OVL) ptx::mbar_init(&ctrl->ovl_free, (p.out_fp32 ? EPI_WARPS : EPI_WARPS / 2) * CG);   // the warps that own a shared chunk
+        if constexpr (OVL) ptx::mbar_init(&ctrl->ovl_free, ((p.out_fp32 && p.ovl_stride == 192) ? EPI_WARPS : EPI_WARPS / 2) * CG);   // the warps that own a shared chunk
         for (int s = 0; s < CLC_ST; s++) {
             ptx::mbar_init(&ctrl->clc_full[s], 1);
             ptx::mbar_init(&ctrl->clc_empty[s], CG);                 // the scheduler warp of every CTA of the pair reads each response
@@ -306,14 +311,16 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 }
                 if (tr && lane == 0) tr[2] = clock64();
                 ptx::tc_fence_after();
-                const uint32_t tmem_d = tmem_base + acc * (OVL ? OVL_STRIDE : BN);
+                const uint32_t tmem_d = tmem_base + acc * (OVL ? p.ovl_stride : BN);
+                const uint32_t sf_col0 = (OVL && p.ovl_stride == 224) ? 480u : static_cast<uint32_t>(SF_COL0);
+                const int sf_mask = (OVL && p.ovl_stride == 224) ? 1 : SF_BUFS - 1;     // 32 columns hold two 16-column scale buffers
                 for (int kb = 0; kb < num_kb; kb++) {
                     ptx::mbar_wait(&full_bar[stage], phase);
                     if (tr && lane == 0 && kb == 0) tr[3] = clock64();
                     ptx::tc_fence_after();
                     const uint32_t sa = ptx::smem_u32(smem + stage * stage_bytes);
                     const uint32_t sb = sa + A_BYTES;
-                    const uint32_t tmem_sf = tmem_base + SF_COL0 + 16 * sfi;
+                    const uint32_t tmem_sf = tmem_base + sf_col0 + 16 * sfi;
                     if (ptx::elect_one_sync()) {
                     if (MX && !((p.debug & 1) && (kb | tile) != 0)) {
                         const uint32_t ssf = ptx::smem_u32(sf_base + stage * sf_stage_bytes);
@@ -339,7 +346,7 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                     ptx::tc_commit_cg<CG>(&empty_bar[stage]);   // smem slot (in both CTAs) reusable once these MMAs have read it
                     }
                     __syncwarp();
-                    if (MX && !(p.debug & 4)) sfi = (sfi + 1) & (SF_BUFS - 1);
+                    if (MX && !(p.debug & 4)) sfi = (sfi + 1) & sf_mask;
                     if (++stage == STAGES) { stage = 0; phase ^= 1; }
                 }
                 if (tr && lane == 0) tr[4] = clock64();
@@ -452,30 +459,46 @@ fp8_gemm_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant
                 else ptx::mbar_wait(&tmem_full[acc], acc_phase);
                 ptx::tc_fence_after();
                 if (etr && lane == 0) etr[0] = clock64();
-                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? OVL_STRIDE : BN);
+                const uint32_t taddr = tmem_base + (static_cast<uint32_t>(quad * 32) << 16) + acc * (OVL ? p.ovl_stride : BN);
                 // OVL: this warp's chunks are walked so that the one lying in the shared columns [192, 256) comes first — the LAST chunk of
                 // the accumulator at column 0 (walk down), the FIRST chunk of the one at column 192 (walk up).  bf16 output: 64-column
                 // chunks, the shared one belongs to one `half`; fp32 output: 32-column chunks, each half owns one of the two shared chunks.
                 const int nmine = (nchunks - half + 1) >> 1;
                 const bool walk_down = OVL && acc == 0;
-                const bool owns_shared = OVL && (p.out_fp32 || half == (acc == 0 ? 1 : 0));
+                const bool narrow = OVL && p.ovl_stride == 224;     // 32 shared columns: half of a bf16 chunk, or one fp32 chunk
+                const bool owns_shared = OVL && ((p.out_fp32 && !narrow) || half == (acc == 0 ? 1 : 0));
 #pragma unroll 1
                 for (int c = walk_down ? half + 2 * (nmine - 1) : half, n = 0; OVL ? (n < nmine) : (c < nchunks); c += walk_down ? -2 : 2, n++) {
                     const int col = n0 + coff(c);
                     uint32_t r0[32], r1[32];
-                    ptx::tmem_ld_32x32b_x32(taddr + coff(c), r0);
-                    if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + coff(c) + 32, r1);
-                    if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
-                    ptx::tmem_ld_wait();
-                    if (etr && lane == 0 && n < 2) etr[1 + n] = clock64();
-                    if constexpr (OVL) {
-                        if (n == 0 && owns_shared) {                    // the shared columns are in registers: the next tile's MMAs may overwrite them
-                            ptx::tc_fence_before();
-                            __syncwarp();
-                            if (lane == 0) {
-                                if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ctrl->ovl_free), 0));
-                                else ptx::mbar_arrive(&ctrl->ovl_free);
-                            }
+                    auto free_shared = [&]() {                          // the shared columns are in registers: the next tile's MMAs may overwrite them
+                        ptx::tc_fence_before();
+                        __syncwarp();
+                        if (lane == 0) {
+                            if constexpr (CG == 2) ptx::mbar_arrive_cluster(ptx::mapa(ptx::smem_u32(&ctrl->ovl_free), 0));
+                            else ptx::mbar_arrive(&ctrl->ovl_free);
+                        }
+                    };
+                    if (OVL && narrow && n == 0 && owns_shared && !p.out_fp32) {
+                        // the shared 32 columns are ONE half of this 64-column chunk (the upper half of the accumulator at column 0, the lower
+                        // half of the one at column 224): pull that half alone, hand the columns over, then fetch the other half
+                        if (walk_down) ptx::tmem_ld_32x32b_x32(taddr + coff(c) + 32, r1);
+                        else ptx::tmem_ld_32x32b_x32(taddr + coff(c), r0);
+                        ptx::tmem_ld_wait();
+                        free_shared();
+                        if (walk_down) ptx::tmem_ld_32x32b_x32(taddr + coff(c), r0);
+                        else ptx::tmem_ld_32x32b_x32(taddr + coff(c) + 32, r1);
+                        if (lane == 0) ptx::tma_store_wait_read<0>();
+                        ptx::tmem_ld_wait();
+                        if (etr && lane == 0) etr[1] = clock64();
+                    } else {
+                        ptx::tmem_ld_32x32b_x32(taddr + coff(c), r0);
+                        if (!p.out_fp32) ptx::tmem_ld_32x32b_x32(taddr + coff(c) + 32, r1);
+                        if (lane == 0) ptx::tma_store_wait_read<0>();      // the box previously stored from this warp's buffer has been read
+                        ptx::tmem_ld_wait();
+                        if (etr && lane == 0 && n < 2) etr[1 + n] = clock64();
+                        if constexpr (OVL) {
+                            if (n == 0 && owns_shared) free_shared();
                         }
                     }
                     if (OVL ? (n + 1 == nmine) : (c + 2 >= nchunks)) release_acc(acc);           // this warp's share of the accumulator is in registers
@@ -824,6 +847,7 @@ int launch_fp8_gemm(const void* a, int64_t lda, int a_fmt, int a_mn, const void*
     // MX at 256 columns, staged epilogue, no fused residual: two overlapped accumulators (OVL kernels); debug bit 4 falls back to one
     // (debug bit 5 keeps the fused-residual kernel on a single accumulator)
     p.acc_overlap = (!(g_debug & 16) && mx && BN == 256 && !accumulate && (!residual || !(g_debug & 32))) ? 1 : 0;
+    p.ovl_stride = p.acc_overlap ? ((g_debug & 256) ? 192 : 224) : 0;
     p.acc_stages = (mx && BN > 224 && !p.acc_overlap) ? 1 : 2;      // 224 columns: two whole accumulators beside the scale factors
     p.sf_tiles = mx ? (BN == 224 ? 4 : 3) : 0;
     const int stage_bytes = BM * BK + p.b_rows_cta * BK + 512 * p.sf_tiles;
@@ -911,6 +935,7 @@ int launch_bf16_gemm(const void* a, int64_t lda, int a_mn, const void* b, int64_
     const int bn_cta = BN / cg;
     p.b_rows_cta = b_mn ? (bn_cta + 63) / 64 * 64 : bn_cta;
     p.acc_overlap = 0;
+    p.ovl_stride = 0;
     p.acc_stages = 2;
     p.ce_labels = ce_labels; p.ce_lse = ce_lse; p.ce_gscale = ce_gscale; p.ce_partials = static_cast<float2*>(ce_partials); p.ce_label_logit = ce_label_logit;
     p.ce_ignore = ce_ignore;

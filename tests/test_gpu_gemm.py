@@ -251,7 +251,7 @@ def test_gemm_full_shape_checksum(cg, force):
 @pytest.mark.parametrize("M,N,K", [(6144, 28672, 4096), (992, 1344, 992), (512, 768, 4096)])
 @pytest.mark.parametrize("layout", ["fprop", "dgrad", "wgrad"])
 def test_mxfp8_gemm_overlapped_accumulators_identical(M, N, K, layout, force):
-    """MX at 256 columns runs two TMEM accumulators that share 64 columns (gemm.cu: OVL); debug bit 4 selects the single-accumulator
+    """MX at 256 columns runs two TMEM accumulators that share 32 columns (gemm.cu: OVL; 64 columns with debug bit 8); debug bit 4 selects the single-accumulator
     kernel.  Both issue the same MMAs in the same order, so bf16 and fp32 outputs must be bit-identical — on the Llama-3.1-8B fc1 shape
     (36 tiles per CTA pair), a ragged shape and a single-CTA shape.  Same calls as tools/gemm_ovl_check.py
     (profiles/r01c_gemm_ovl_check.txt)."""
@@ -278,9 +278,12 @@ def test_mxfp8_gemm_overlapped_accumulators_identical(M, N, K, layout, force):
             single = run(dt)
             lib.llmfp8_gemm_debug(0)
             ovl = run(dt)
+            lib.llmfp8_gemm_debug(256)                    # accumulators 192 apart: 64 shared columns, four scale buffers (the first form)
+            narrow = run(dt)
             torch.cuda.synchronize()
             assert torch.isfinite(ovl.float()).all()
             assert torch.equal(single, ovl), f"{layout} {dt}"
+            assert torch.equal(single, narrow), f"{layout} {dt} (64 shared columns)"
     finally:
         lib.llmfp8_gemm_debug(0)
 
@@ -307,8 +310,11 @@ def test_mxfp8_gemm_residual_overlapped_accumulators_identical(M, N, K, force):
         want = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res)
         lib.llmfp8_gemm_debug(0)
         got = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res)
+        lib.llmfp8_gemm_debug(256)                        # accumulators 192 apart (64 shared columns: the first form)
+        narrow = ops.mxfp8_gemm(x, sx, False, w, sw, False, M, N, K, bias=bias, residual=res)
         torch.cuda.synchronize()
         assert torch.equal(want, got)
+        assert torch.equal(want, narrow)
     finally:
         lib.llmfp8_gemm_debug(0)
 
