@@ -276,9 +276,9 @@ __global__ void __launch_bounds__(RB_T, (NIT <= 2 ? 2 : 1)) rmsnorm_bwd_kernel(c
         }
 }
 
-// dgamma[c] = sum over the per-CTA partial rows.  CTA = 32 columns x 8 partial-row lanes: every warp reads 128 B rows, each thread
+// dgamma[c] = sum over the per-CTA partial rows.  CTA = 32 columns x 32 partial-row lanes: every warp reads 128 B rows, each thread
 // keeps four independent accumulators (the one-thread-per-column chain this replaces spent ~30 us on 444 dependent loads).
-constexpr int CR_COLS = 32, CR_LANES = 8;
+constexpr int CR_COLS = 32, CR_LANES = 32;     // 1024 threads: <= 10 partial rows per thread at 296 CTAs' worth of partials (8 lanes: 37 rows, 13.8 us)
 __global__ void __launch_bounds__(CR_COLS * CR_LANES) colreduce_bf16_kernel(const float* __restrict__ part, int nparts, int H,
                                                                             uint16_t* __restrict__ out) {
     pdl_wait();                // LLMFP8_PDL build only (common.cuh); empty otherwise
